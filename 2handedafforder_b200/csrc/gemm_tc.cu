@@ -1,0 +1,476 @@
+// tcgen05 GEMM family for the SAM branch (B200 / sm_100a).
+//
+// One persistent, warp-specialised kernel: warp 0 = TMA producer (cp.async.bulk.tensor, SWIZZLE_128B tiles
+// into a 4-6 stage shared-memory ring), warp 1 = single-thread tcgen05.mma issuer (M=128 x N=BN x K=16/8,
+// fp32 accumulators in TMEM, two accumulator buffers so the epilogue of tile i overlaps the MMAs of tile
+// i+1), warp 2 = TMEM allocator, warps 4-7 = epilogue (tcgen05.ld -> registers -> fused epilogue -> global).
+//
+// The epilogues are the fusions the reference executes as separate ATen ops:
+//   GM_BIAS_BF16       qkv Linear                      image_encoder.py:238
+//   GM_BIAS_GELU_BF16  MLPBlock.lin1 + nn.GELU (erf)   common.py:25-26
+//   GM_F32             patch-embed bias + pos_embed    image_encoder.py:111-113,
+//                      attn.proj + window_unpartition + residual  image_encoder.py:187-190,258,
+//                      MLPBlock.lin2 + residual        image_encoder.py:191,
+//                      decoder k/v/q projections with the constant positional part folded into a table
+//                                                      transformer.py:220-225
+//   GM_LN              neck conv + LayerNorm2d         image_encoder.py:92-108, common.py:38-43,
+//                      cross_attn_image_to_token out_proj + residual + norm4  transformer.py:176-180
+//   GM_UPS1 / GM_UPS2  output_upscaling ConvT/LN2d/GELU/ConvT/GELU and the hypernetwork mask product
+//                                                      mask_decoder.py:54-64,154-165
+#include "gemm_tc.cuh"
+
+#include <cudaTypedefs.h>
+#include <stdio.h>
+
+#include "common.cuh"
+
+namespace b200sam {
+
+namespace {
+
+constexpr int kBM = 128;
+constexpr int kThreads = 256;
+
+template <int BN>
+struct TileCfg {
+  static constexpr int kStageBytes = kBM * 128 + BN * 128;
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct TmemSrc {
+  uint32_t taddr;  // lane offset | first column of this accumulator buffer
+  __device__ __forceinline__ void load(int chunk, float (&v)[32]) const {
+    uint32_t r[32];
+    tmem_ld_32x32(taddr + chunk * 32, r);
+    tmem_wait_ld();
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+  }
+};
+
+template <bool kTf32>
+struct SimtSrc {
+  const void* A;
+  const void* W;
+  int lda, ldw, K, N, n0;
+  long row;
+  bool row_ok;
+  __device__ void load(int chunk, float (&v)[32]) const {
+#pragma unroll 1
+    for (int j = 0; j < 32; ++j) {
+      int col = n0 + chunk * 32 + j;
+      float acc = 0.f;
+      if (row_ok && col < N) {
+        if constexpr (kTf32) {
+          const float* a = reinterpret_cast<const float*>(A) + row * lda;
+          const float* w = reinterpret_cast<const float*>(W) + (long)col * ldw;
+          for (int k = 0; k < K; ++k) acc += a[k] * w[k];
+        } else {
+          const __nv_bfloat16* a = reinterpret_cast<const __nv_bfloat16*>(A) + row * lda;
+          const __nv_bfloat16* w = reinterpret_cast<const __nv_bfloat16*>(W) + (long)col * ldw;
+          for (int k = 0; k < K; ++k) acc += __bfloat162float(a[k]) * __bfloat162float(w[k]);
+        }
+      }
+      v[j] = acc;
+    }
+  }
+};
+
+__device__ __forceinline__ void add_vec32(float (&v)[32], const float* __restrict__ p) {
+  const float4* p4 = reinterpret_cast<const float4*>(p);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    float4 t = __ldg(p4 + j);
+    v[4 * j + 0] += t.x;
+    v[4 * j + 1] += t.y;
+    v[4 * j + 2] += t.z;
+    v[4 * j + 3] += t.w;
+  }
+}
+// plain (coherent) loads: the addend may alias the output (in-place residual update)
+__device__ __forceinline__ void add_vec32_plain(float (&v)[32], const float* p) {
+  const float4* p4 = reinterpret_cast<const float4*>(p);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    float4 t = p4[j];
+    v[4 * j + 0] += t.x;
+    v[4 * j + 1] += t.y;
+    v[4 * j + 2] += t.z;
+    v[4 * j + 3] += t.w;
+  }
+}
+__device__ __forceinline__ void store_f32x32(float* o, const float (&v)[32]) {
+  float4* o4 = reinterpret_cast<float4*>(o);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) o4[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+}
+__device__ __forceinline__ void store_bf16x32(__nv_bfloat16* o, const float (&v)[32]) {
+  uint4* o4 = reinterpret_cast<uint4*>(o);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint4 t;
+    t.x = pack_bf16(v[8 * j + 0], v[8 * j + 1]);
+    t.y = pack_bf16(v[8 * j + 2], v[8 * j + 3]);
+    t.z = pack_bf16(v[8 * j + 4], v[8 * j + 5]);
+    t.w = pack_bf16(v[8 * j + 6], v[8 * j + 7]);
+    o4[j] = t;
+  }
+}
+
+// One output row (row of the 128-row tile owned by this thread), columns [n0, n0 + BN).
+// `src.load` is warp-collective for the TMEM source: every lane must call it the same number of times.
+template <int MODE, int BN, class Src>
+__device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, long row, int M, int N, int n0) {
+  const bool row_in = row < M;
+  const int ncols = min(BN, N - n0);
+  const int nchunks = ncols / 32;
+  float v[32];
+
+  if constexpr (MODE == GM_BIAS_BF16 || MODE == GM_BIAS_GELU_BF16) {
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + row * (long)e.ld_out + n0;
+    for (int c = 0; c < nchunks; ++c) {
+      src.load(c, v);
+      if (row_in) {
+        add_vec32(v, e.bias + n0 + c * 32);
+        if constexpr (MODE == GM_BIAS_GELU_BF16) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+        }
+        store_bf16x32(o + c * 32, v);
+      }
+    }
+  } else if constexpr (MODE == GM_F32) {
+    long orow = row;
+    bool ok = row_in;
+    if (e.rowmap == RM_WINDOW_TO_TOKEN) {
+      long b = row / kWinRowsPerFrame;
+      int rem = (int)(row - b * kWinRowsPerFrame);
+      int win = rem / kWinTokens, t = rem - win * kWinTokens;
+      int y = (win / kWinPerSide) * kWin + t / kWin;
+      int x = (win % kWinPerSide) * kWin + t % kWin;
+      ok = ok && (y < kGrid) && (x < kGrid);
+      orow = b * kTokens + y * kGrid + x;
+    }
+    float* o = reinterpret_cast<float*>(e.out) + orow * (long)e.ld_out + n0;
+    const float* a = nullptr;
+    if (e.addend) {
+      long arow = e.add_mod > 0 ? (orow % e.add_mod) : orow;
+      a = e.addend + arow * (long)e.ld_add + n0;
+    }
+    for (int c = 0; c < nchunks; ++c) {
+      src.load(c, v);
+      if (ok) {
+        if (e.bias) add_vec32(v, e.bias + n0 + c * 32);
+        if (a) add_vec32_plain(v, a + c * 32);
+        store_f32x32(o + c * 32, v);
+      }
+    }
+  } else if constexpr (MODE == GM_LN) {
+    // N == BN == 256; shifted single-pass statistics, then a second pass over TMEM to normalise.
+    const float* a = e.addend ? e.addend + row * (long)e.ld_add : nullptr;
+    float shift = 0.f, s1 = 0.f, s2 = 0.f;
+    for (int c = 0; c < 8; ++c) {
+      src.load(c, v);
+      if (row_in) {
+        if (e.bias) add_vec32(v, e.bias + c * 32);
+        if (a) add_vec32_plain(v, a + c * 32);
+        if (c == 0) shift = v[0];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float d = v[j] - shift;
+          s1 += d;
+          s2 += d * d;
+        }
+      }
+    }
+    const float md = s1 * (1.f / 256.f);
+    const float var = fmaxf(s2 * (1.f / 256.f) - md * md, 0.f);
+    const float mean = shift + md;
+    const float rstd = rsqrtf(var + e.ln_eps);
+    for (int c = 0; c < 8; ++c) {
+      src.load(c, v);
+      if (row_in) {
+        if (e.bias) add_vec32(v, e.bias + c * 32);
+        if (a) add_vec32_plain(v, a + c * 32);
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          v[j] = (v[j] - mean) * rstd * __ldg(e.ln_g + c * 32 + j) + __ldg(e.ln_b + c * 32 + j);
+        if (e.out) store_f32x32(reinterpret_cast<float*>(e.out) + row * (long)e.ld_out + c * 32, v);
+        if (e.out2)
+          store_bf16x32(reinterpret_cast<__nv_bfloat16*>(e.out2) + row * (long)e.ld_out + c * 32, v);
+      }
+    }
+  } else if constexpr (MODE == GM_UPS1) {
+    // row = p*4096 + y*64 + x; columns (ky, kx, c64).  Output (P,128,128,64) token-major fp32.
+    long p = row / kTokens;
+    int t = (int)(row - p * kTokens);
+    int y = t / kGrid, x = t % kGrid;
+    float w[32];
+    for (int g = 0; g < 4; ++g) {
+      src.load(2 * g, v);
+      src.load(2 * g + 1, w);
+      if (row_in) {
+        add_vec32(v, e.bias + g * 64);
+        add_vec32(w, e.bias + g * 64 + 32);
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) s += v[j] + w[j];
+        const float mean = s * (1.f / 64.f);
+        float q = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float d0 = v[j] - mean, d1 = w[j] - mean;
+          q += d0 * d0 + d1 * d1;
+        }
+        const float rstd = rsqrtf(q * (1.f / 64.f) + e.ln_eps);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          v[j] = gelu_erf((v[j] - mean) * rstd * __ldg(e.ln_g + j) + __ldg(e.ln_b + j));
+          w[j] = gelu_erf((w[j] - mean) * rstd * __ldg(e.ln_g + 32 + j) + __ldg(e.ln_b + 32 + j));
+        }
+        int ky = g >> 1, kx = g & 1;
+        float* o = reinterpret_cast<float*>(e.out) + ((p * 128 + 2 * y + ky) * 128 + 2 * x + kx) * 64;
+        store_f32x32(o, v);
+        store_f32x32(o + 32, w);
+      }
+    }
+  } else if constexpr (MODE == GM_UPS2) {
+    // row = (p*128 + y)*128 + x; columns (ky, kx, c32).  Output mask logits (P,256,256) fp32.
+    long p = row / (128 * 128);
+    int t = (int)(row - p * 128 * 128);
+    int y = t / 128, x = t % 128;
+    const float* h = e.hyper + p * 32;
+    for (int g = 0; g < 4; ++g) {
+      src.load(g, v);
+      if (row_in) {
+        add_vec32(v, e.bias + g * 32);
+        float dot = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) dot += gelu_erf(v[j]) * __ldg(h + j);
+        int ky = g >> 1, kx = g & 1;
+        reinterpret_cast<float*>(e.out)[p * 65536 + (2 * y + ky) * 256 + 2 * x + kx] = dot;
+      }
+    }
+  }
+}
+
+template <bool kTf32, int MODE, int BN>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
+               GemmEpi e) {
+  using Cfg = TileCfg<BN>;
+  constexpr int kStages = Cfg::kStages;
+  constexpr int kBK = kTf32 ? 32 : 64;                 // elements per 128-byte row
+  constexpr uint32_t kIdesc = (1u << 4) /*D=f32*/ | ((kTf32 ? 2u : 1u) << 7) | ((kTf32 ? 2u : 1u) << 10) |
+                              (uint32_t(BN >> 3) << 17) | (uint32_t(kBM >> 4) << 24);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + kStages;
+  uint64_t* tmem_full = bars + 2 * kStages;
+  uint64_t* tmem_empty = bars + 2 * kStages + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int m_tiles = (M + kBM - 1) / kBM;
+  const int n_tiles = (N + BN - 1) / BN;
+  const int num_tiles = m_tiles * n_tiles;
+  const int kblocks = (K + kBK - 1) / kBK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 128);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 2 * BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sA = smem + stage * Cfg::kStageBytes;
+          uint8_t* sB = sA + kBM * 128;
+          mbar_expect_tx(&full[stage], Cfg::kStageBytes);
+          tma_load_2d(sA, &tmA, &full[stage], kb * kBK, m_blk * kBM);
+          tma_load_2d(sB, &tmB, &full[stage], kb * kBK, n_blk * BN);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int as = it & 1;
+        const uint32_t aph = (it >> 1) & 1;
+        mbar_wait(&tmem_empty[as], aph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a0 = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t b0 = a0 + kBM * 128;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {   // 4 MMAs of K=16 (bf16) / K=8 (tf32): 32 bytes of K each
+            umma_ss<kTf32>(d_tmem, umma_desc_sw128(a0 + k * 32), umma_desc_sw128(b0 + k * 32), kIdesc,
+                           (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty[stage]);     // frees the smem slot when these MMAs retire
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tmem_full[as]);      // accumulator complete -> epilogue
+      }
+    }
+  } else if (warp >= 4) {
+    const int ew = warp & 3;              // TMEM lane quadrant this warp may access
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+      const int as = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      mbar_wait(&tmem_full[as], aph);
+      tc_fence_after();
+      TmemSrc src{tmem_base + (uint32_t(ew * 32) << 16) + uint32_t(as * BN)};
+      const long row = (long)m_blk * kBM + ew * 32 + lane;
+      epilogue_row<MODE, BN>(e, src, row, M, N, n_blk * BN);
+      tc_fence_before();
+      mbar_arrive(&tmem_empty[as]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 2) tmem_dealloc(tmem_base, 2 * BN);
+}
+
+// Debug-only SIMT evaluation of the same contract (one thread per output row); selected explicitly by the
+// caller to bisect tcgen05/TMA problems.  Never used unless requested.
+template <bool kTf32, int MODE, int BN>
+__global__ void gemm_simt_debug_kernel(const void* A, int lda, const void* W, int ldw, int M, int N, int K,
+                                       GemmEpi e) {
+  const long row = (long)blockIdx.x * kBM + threadIdx.x;
+  const int n0 = blockIdx.y * BN;
+  SimtSrc<kTf32> src{A, W, lda, ldw, K, N, n0, row, row < M};
+  epilogue_row<MODE, BN>(e, src, row, M, N, n0);
+}
+
+PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+int g_num_sms = 148;
+
+cudaError_t make_tmap(CUtensorMap* tm, const void* ptr, bool f32, long rows, long cols, long ld, int box_rows) {
+  const int esz = f32 ? 4 : 2;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * esz};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / esz), (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (strides[0] & 15)) return cudaErrorInvalidValue;
+  CUresult r = g_encode(tm, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                        const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
+template <bool kTf32, int MODE, int BN>
+cudaError_t launch(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const GemmEpi& e,
+                   cudaStream_t stream, bool debug_simt) {
+  if (M <= 0) return cudaSuccess;
+  if (debug_simt) {
+    dim3 grid((M + kBM - 1) / kBM, (N + BN - 1) / BN);
+    gemm_simt_debug_kernel<kTf32, MODE, BN><<<grid, kBM, 0, stream>>>(A, lda, W, ldw, M, N, K, e);
+    return cudaGetLastError();
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t err = cudaFuncSetAttribute(gemm_tc_kernel<kTf32, MODE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           TileCfg<BN>::kSmemBytes);
+    if (err != cudaSuccess) return err;
+    attr_set = true;
+  }
+  CUtensorMap tmA, tmB;
+  cudaError_t err = make_tmap(&tmA, A, kTf32, M, K, lda, kBM);
+  if (err != cudaSuccess) return err;
+  err = make_tmap(&tmB, W, kTf32, N, K, ldw, BN);
+  if (err != cudaSuccess) return err;
+  const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN);
+  const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+  gemm_tc_kernel<kTf32, MODE, BN><<<grid, kThreads, TileCfg<BN>::kSmemBytes, stream>>>(tmA, tmB, M, N, K, e);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t gemm_tc_init(int device) {
+  if (g_encode) return cudaSuccess;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t err = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (err != cudaSuccess) return err;
+  if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
+  g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+  int sms = 0;
+  err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  if (err != cudaSuccess) return err;
+  g_num_sms = sms;
+  return cudaSuccess;
+}
+
+cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, int ldw, int M, int N, int K,
+                    const GemmEpi& e, cudaStream_t s, bool dbg) {
+  if (!g_encode && !dbg) return cudaErrorInitializationError;
+  if (N % 32 != 0 || K % 8 != 0) return cudaErrorInvalidValue;
+  if ((mode == GM_LN || mode == GM_UPS1) && N != 256) return cudaErrorInvalidValue;
+  if (mode == GM_UPS2 && N != 128) return cudaErrorInvalidValue;
+  if (!tf32) {
+    switch (mode) {
+      case GM_BIAS_BF16: return launch<false, GM_BIAS_BF16, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
+      case GM_BIAS_GELU_BF16: return launch<false, GM_BIAS_GELU_BF16, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
+      case GM_F32: return launch<false, GM_F32, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
+      case GM_LN: return launch<false, GM_LN, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
+      default: return cudaErrorInvalidValue;
+    }
+  }
+  switch (mode) {
+    case GM_F32:
+      if (N <= 128) return launch<true, GM_F32, 128>(A, lda, W, ldw, M, N, K, e, s, dbg);
+      return launch<true, GM_F32, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
+    case GM_LN: return launch<true, GM_LN, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
+    case GM_UPS1: return launch<true, GM_UPS1, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
+    case GM_UPS2: return launch<true, GM_UPS2, 128>(A, lda, W, ldw, M, N, K, e, s, dbg);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+}  // namespace b200sam

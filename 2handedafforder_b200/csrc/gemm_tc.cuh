@@ -1,0 +1,49 @@
+// Interface of the tcgen05 GEMM family (gemm_tc.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200sam {
+
+// Epilogue selector.  C[m, n] = sum_k A[m, k] * W[n, k]  (both operands K-major, i.e. nn.Linear layout),
+// then per mode:
+enum GemmMode : int {
+  GM_BIAS_BF16 = 0,       // out_bf16[m, n] = acc + bias[n]
+  GM_BIAS_GELU_BF16 = 1,  // out_bf16[m, n] = gelu_erf(acc + bias[n])
+  GM_F32 = 2,             // out_f32[orow(m), n] = acc (+ bias[n]) (+ addend[arow, n]); row maps below
+  GM_LN = 3,              // N == 256: y = LayerNorm_n(acc (+bias) (+addend[m])) * g + b -> out_f32 and/or out2_bf16
+  GM_UPS1 = 4,            // N == 256 = 4 x 64: per 64-group LN (eps) -> GELU -> pixel-shuffle store (ConvT k2 s2)
+  GM_UPS2 = 5,            // N == 128 = 4 x 32: GELU -> dot with hyper[p, 0:32] -> pixel-shuffle store of the mask logit
+};
+
+enum RowMap : int {
+  RM_IDENT = 0,
+  RM_WINDOW_TO_TOKEN = 1,  // input rows are in 14x14-window order (25 windows x 196 per frame, pad rows skipped)
+};
+
+struct GemmEpi {
+  const float* bias = nullptr;    // [N] (for UPS1/UPS2 already expanded over the 4 (ky,kx) groups)
+  const float* addend = nullptr;  // fp32 [*, ld_add]
+  int ld_add = 0;
+  int add_mod = 0;                // >0: addend row = orow % add_mod (broadcast tables), else addend row = orow
+  void* out = nullptr;            // bf16 or fp32 depending on mode
+  void* out2 = nullptr;           // GM_LN: optional bf16 copy
+  int ld_out = 0;
+  int rowmap = RM_IDENT;
+  const float* ln_g = nullptr;
+  const float* ln_b = nullptr;
+  float ln_eps = 0.f;
+  const float* hyper = nullptr;   // GM_UPS2: (P, 32) mask-0 hypernetwork vector per prompt
+};
+
+// A: (M, K) row-major with leading dimension lda (elements); W: (N, K) row-major, ldw.
+// tf32 == false: A, W are bf16.  tf32 == true: A, W are fp32, multiplied as TF32.
+// Requirements: K % 8 == 0 (tf32) / K % 8 == 0 (bf16) and 16-byte aligned rows; N % 32 == 0.
+// Returns cudaSuccess or an error; never falls back to another implementation.
+cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, int ldw, int M, int N, int K,
+                    const GemmEpi& epi, cudaStream_t stream, bool debug_simt = false);
+
+// Must be called once per process before gemm_tc (resolves cuTensorMapEncodeTiled, sets smem attributes).
+cudaError_t gemm_tc_init(int device);
+
+}  // namespace b200sam

@@ -1,0 +1,42 @@
+// Launchers of the non-GEMM kernels of the SAM branch (elementwise.cu, attn.cu, decoder.cu, postprocess.cu).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200sam {
+
+enum DType : int { DT_F32 = 0, DT_BF16 = 1, DT_F16 = 2 };
+
+// ---- elementwise.cu
+cudaError_t launch_layernorm_bf16(const float* x, long rows, int D, const float* g, const float* b, float eps,
+                                  __nv_bfloat16* out, bool windowed, cudaStream_t s);
+cudaError_t launch_im2col_patch(const void* frames, int dtype, int B, __nv_bfloat16* out, cudaStream_t s);
+cudaError_t launch_im2col_3x3(const __nv_bfloat16* z, int B, __nv_bfloat16* out, cudaStream_t s);
+cudaError_t launch_tokens_to_nchw(const float* tok, int B, void* out, int dtype, cudaStream_t s);
+cudaError_t launch_nchw_to_tokens(const void* in, int dtype, int B, float* tok, cudaStream_t s);
+cudaError_t launch_cast_f32_bf16(const float* in, __nv_bfloat16* out, long n, cudaStream_t s);
+cudaError_t launch_to_f32(const void* in, int dtype, float* out, long n, cudaStream_t s);
+cudaError_t launch_dense_pe(const float* gauss, float* pe_tok, cudaStream_t s);
+cudaError_t launch_keys_init(const float* emb_tok, const float* no_mask, const int* prompt_frame, int P, float* keys,
+                             cudaStream_t s);
+// rel-pos table (2S-1, hd) f32 -> bf16 padded to RP rows (32 for S=14, 128 for S=64), extra rows zero
+cudaError_t launch_relpos_pack(const float* rel, int S, int hd, __nv_bfloat16* out, cudaStream_t s);
+
+// ---- attn.cu
+// qkv: (nbatch*S*S, 3*heads*hd) bf16 packed [q | k | v] per row, heads-major inside each; out (rows, heads*hd).
+// relh/relw: bf16 tables from launch_relpos_pack.
+cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int heads, int hd,
+                             const __nv_bfloat16* relh, const __nv_bfloat16* relw, __nv_bfloat16* out,
+                             cudaStream_t s);
+cudaError_t attention_init();
+
+// ---- decoder.cu
+struct DecSideWeights;   // device pointers of one mask decoder (api.cu owns it)
+struct DecoderWorkspace;
+
+// ---- postprocess.cu
+cudaError_t launch_postprocess(const float* lowres, int n, int in_h, int in_w, int out_h, int out_w, float* logits,
+                               uint8_t* mask, float thr, cudaStream_t s);
+
+}  // namespace b200sam

@@ -1,0 +1,115 @@
+// Handle of libb200sam: hyper-parameters, packed weights and the pre-allocated workspace.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "gemm_tc.cuh"
+#include "kernels.cuh"
+
+namespace b200sam {
+
+struct Tensor {
+  float* d = nullptr;               // fp32 master copy on the device
+  std::vector<int64_t> shape;
+  long numel = 0;
+};
+
+struct EncBlock {
+  bool global = false;
+  const float *ln1g, *ln1b, *ln2g, *ln2b;
+  const float *qkv_b, *proj_b, *lin1_b, *lin2_b;
+  __nv_bfloat16 *qkv_w, *proj_w, *lin1_w, *lin2_w;
+  __nv_bfloat16 *relh, *relw;       // padded bf16 rel-pos tables
+};
+
+// transformer.Attention weights (transformer.py:185-218), fp32 device pointers into the masters
+struct AttnW {
+  const float *qw, *qb, *kw, *kb, *vw, *vb, *ow, *ob;
+  int internal;                      // 256 (self) or 128 (cross)
+};
+
+struct DecLayer {
+  AttnW self_attn, t2i, i2t;
+  const float *n1g, *n1b, *n2g, *n2b, *n3g, *n3b, *n4g, *n4b;
+  const float *mlp1w, *mlp1b, *mlp2w, *mlp2b;
+  // derived (finalize): stacked K|V projection of the image side and its positional table, i2t query table
+  float* kv_w = nullptr;     // (256, 256): rows 0..127 = k_proj, 128..255 = v_proj        [t2i]
+  float* kv_tab = nullptr;   // (4096, 256): [pe @ Wk^T + bk | bv]
+  float* q_tab = nullptr;    // (4096, 128): pe @ Wq^T + bq                                 [i2t]
+};
+
+struct DecSide {
+  bool has_taxonomy = false;
+  const float *iou_token, *mask_tokens;
+  DecLayer layer[2];
+  AttnW final_attn;
+  const float *nfg, *nfb;
+  float* final_kv_w = nullptr;
+  float* final_kv_tab = nullptr;
+  const float *up1_lng, *up1_lnb;
+  float *up0_w = nullptr, *up0_b = nullptr;   // (256 = (ky,kx,c64), 256), expanded bias (256)
+  float *up3_w = nullptr, *up3_b = nullptr;   // (128 = (ky,kx,c32), 64), expanded bias (128)
+  const float* hyp_w[4][3];
+  const float* hyp_b[4][3];
+  const float* iou_w[3];
+  const float* iou_b[3];
+  const float* tax_w[3];
+  const float* tax_b[3];
+};
+
+}  // namespace b200sam
+
+struct b200sam {
+  int dim = 0, depth = 0, heads = 0, hd = 0;
+  std::vector<int> global_idx;
+  int device = 0, max_batch = 0, max_prompts = 0;
+  std::string err;
+  int64_t launches = 0;
+  bool debug_simt = false;
+  bool finalized = false;
+  bool have_emb = false;
+  int emb_batch = 0;
+
+  std::map<std::string, b200sam::Tensor> w;
+  std::vector<void*> owned;          // derived device buffers (freed in destroy)
+
+  // encoder
+  __nv_bfloat16* patch_w = nullptr;
+  const float* patch_b = nullptr;
+  const float* pos = nullptr;
+  std::vector<b200sam::EncBlock> blk;
+  __nv_bfloat16 *neck0_w = nullptr, *neck2_w = nullptr;
+  const float *neck1g, *neck1b, *neck3g, *neck3b;
+  // prompt encoder
+  float* pe_tok = nullptr;           // (4096, 256) dense positional encoding, token-major
+  const float* no_mask = nullptr;    // (256)
+  // decoders
+  b200sam::DecSide side[2];
+
+  // workspace (sized for max_batch / max_prompts)
+  float* X = nullptr;                // (B*4096, D) fp32 residual stream
+  __nv_bfloat16* ln_win = nullptr;   // (B*4900, D) windowed LN1 output, pad rows stay zero
+  __nv_bfloat16* ln_plain = nullptr; // (B*4096, D)
+  __nv_bfloat16* qkv = nullptr;      // (B*4900, 3D)
+  __nv_bfloat16* attn_o = nullptr;   // (B*4900, D)
+  __nv_bfloat16* hid = nullptr;      // (B*4096, 4D) MLP hidden; also im2col scratch
+  float* emb_tok = nullptr;          // (B*4096, 256) fp32 image embedding, token-major
+  // decoder workspace
+  int* prompt_frame = nullptr;       // (P) device
+  float* keys = nullptr;             // (P*4096, 256)
+  float* kv = nullptr;               // (P*4096, 256)  [k | v] of the image side
+  float* qimg = nullptr;             // (P*4096, 128)
+  float* oimg = nullptr;             // (P*4096, 128)
+  float* up1 = nullptr;              // (P*16384, 64)
+  float* tok_state = nullptr;        // (P, 6, 256) queries
+  float* tok_pe = nullptr;           // (P, 6, 256) initial tokens (= query PE)
+  float* tok_q = nullptr;            // (P, 6, 128) projected queries for t2i
+  float* tok_o = nullptr;            // (P, 6, 128) t2i attention output before out_proj
+  float* tok_kv = nullptr;           // (P, 6, 256) [k | v] of the tokens for i2t
+  float* hyper = nullptr;            // (P, 32) mask-0 hypernetwork output
+  float* emb_in = nullptr;           // (B*4096, 256) staging when decode() is given an external embedding
+};

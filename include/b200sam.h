@@ -1,0 +1,110 @@
+/* libb200sam — C ABI of the B200-native SAM segmentation branch of 2HandedAfforder.
+ *
+ * Drop-in boundary for the reference's `visual_model` submodule (2Haff/model/segment_anything/modeling/sam.py:18-55)
+ * as driven by 2Haff/model/LISA.py:157-168 (get_visual_embs), :284-325 (model_forward) and :487-532 (evaluate).
+ * Plain pointers and sizes only; no torch types.  All device work is enqueued on the caller's stream; no hidden
+ * synchronisation on the hot path.  Every function returns 0 on success or a negative b200sam_status; the message is
+ * available from b200sam_last_error().  There is no CPU fallback: a missing GPU / wrong architecture is an error.
+ *
+ * Pointers are DEVICE pointers unless the parameter name starts with `host_`.
+ */
+#ifndef B200SAM_H_
+#define B200SAM_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200sam b200sam_t;
+
+enum b200sam_status {
+  B200SAM_OK = 0,
+  B200SAM_ERR_INVALID = -1,      /* bad argument (shape, dtype, batch > max, unknown weight name) */
+  B200SAM_ERR_CUDA = -2,         /* a CUDA call failed; see last_error */
+  B200SAM_ERR_STATE = -3,        /* weights missing / not finalised */
+  B200SAM_ERR_UNSUPPORTED = -4   /* device is not sm_100 */
+};
+
+enum b200sam_dtype { B200SAM_F32 = 0, B200SAM_BF16 = 1, B200SAM_F16 = 2 };
+
+/* build_sam.py:15-48 hyper-parameter table. */
+enum b200sam_arch { B200SAM_VIT_B = 0, B200SAM_VIT_L = 1, B200SAM_VIT_H = 2 };
+
+/* Replaces build_sam_vit_{b,l,h}() (build_sam.py:15-48) + Sam.__init__ (sam.py:24-55).
+ * Workspace for `max_batch` frames and `max_prompts` [SEG] prompts (summed over the batch) is allocated here, so
+ * the hot path never allocates. */
+int b200sam_create(b200sam_t** out, int arch, int device, int max_batch, int max_prompts);
+
+/* Same, with explicit ViT hyper-parameters (_build_sam, build_sam.py:59-121); used for small test shapes.
+ * dim % 32 == 0, dim / heads in {64, 80}. */
+int b200sam_create_custom(b200sam_t** out, int dim, int depth, int heads, const int* host_global_idx, int n_global,
+                          int device, int max_batch, int max_prompts);
+
+void b200sam_destroy(b200sam_t* h);
+const char* b200sam_last_error(const b200sam_t* h);
+
+/* Replaces Sam.load_state_dict for one tensor.  `name` is the reference state_dict key relative to visual_model
+ * (e.g. "image_encoder.blocks.0.attn.qkv.weight"); `ptr` may be a host or a device pointer.
+ * The tensor is copied; the caller keeps ownership. */
+int b200sam_load_weight(b200sam_t* h, const char* name, const void* ptr, int dtype, const int64_t* host_shape,
+                        int ndim);
+/* Checks that every tensor of the manifest was loaded, repacks into kernel layouts (bf16 GEMM operands, permuted
+ * conv weights, positional tables).  Must be called after the last load_weight and before any compute call. */
+int b200sam_finalize_weights(b200sam_t* h);
+
+/* ImageEncoderViT.forward (image_encoder.py:110-125) for B frames at once (LISA.get_visual_embs loops B=1,
+ * LISA.py:157-168).  frames: (B,3,1024,1024) NCHW, normalised and zero padded, dtype f32/bf16.
+ * emb_out: (B,256,64,64) NCHW in `emb_dtype` (f32 or bf16); may be NULL, the fp32 embedding also stays in the
+ * handle for b200sam_decode(..., emb = NULL). */
+int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype, int B, void* emb_out, int emb_dtype,
+                   void* stream);
+
+/* PromptEncoder text path + both MaskDecoders (prompt_encoder.py:140-186, mask_decoder.py:79-178) for all prompts
+ * of a batch.  emb: (B,256,64,64) NCHW in emb_dtype, or NULL to use the embedding left by the last encode.
+ * seg_embeds: (P,256) f32, P = host_prompt_offsets[B]; prompts of frame i are rows [off[i], off[i+1]).
+ * Outputs (all f32, any may be NULL): lowres_left/right (P,256,256) = mask slot 0 (multimask_output=False,
+ * mask_decoder.py:110-115); iou_left/right (P,4) full IoU head; taxonomy (P,4) softmax (left decoder only). */
+int b200sam_decode(b200sam_t* h, const void* emb, int emb_dtype, int B, const float* seg_embeds,
+                   const int* host_prompt_offsets, float* lowres_left, float* lowres_right, float* iou_left,
+                   float* iou_right, float* taxonomy, void* stream);
+
+/* Sam.postprocess_masks (sam.py:155-189) + the callers' threshold (chat.py:231, train_ds.py:662).
+ * lowres: (n,256,256) f32.  Every mask uses the same input_size (h,w) and original_size (H,W).
+ * logits_out: (n,H,W) f32 or NULL; mask_out: (n,H,W) u8 {0,1} = logit > threshold, or NULL. */
+int b200sam_postprocess(b200sam_t* h, const float* lowres, int n_masks, int in_h, int in_w, int out_h, int out_w,
+                        float* logits_out, uint8_t* mask_out, float threshold, void* stream);
+
+/* PromptEncoder.get_dense_pe (prompt_encoder.py:67-76): writes (1,256,64,64) f32. */
+int b200sam_dense_pe(b200sam_t* h, float* out, void* stream);
+
+/* Number of kernels this library has launched on behalf of handle h since creation (bench.py's gpu_launches). */
+int64_t b200sam_launch_count(const b200sam_t* h);
+
+/* Debug switch: 1 = evaluate every GEMM with the SIMT debug kernel instead of tcgen05 (bisecting only). */
+int b200sam_set_debug_simt_gemm(b200sam_t* h, int on);
+
+/* ---- operator-level entry points (used by the per-op parity tests; same kernels the path uses) ---- */
+
+/* C = A(M,K) * W(N,K)^T with fused epilogue.  mode: 0 bias->bf16, 1 bias+GELU->bf16, 2 (+bias)(+addend)->f32,
+ * 3 (+bias)(+addend)->LayerNorm(N=256)->f32.  tf32: 0 = bf16 operands, 1 = fp32 operands multiplied as TF32. */
+int b200sam_op_gemm(int device, int tf32, int mode, const void* A, int lda, const void* W, int ldw, int M, int N,
+                    int K, const float* bias, const float* addend, int ld_add, int add_mod, const float* ln_g,
+                    const float* ln_b, float ln_eps, void* out, int ld_out, int rowmap, int debug_simt, void* stream);
+
+/* LayerNorm over the last dim of x (rows, D) f32 -> bf16; windowed != 0 scatters rows into 14x14-window order
+ * (rows must then be B*4096; out has B*4900 rows whose pad rows are left untouched). */
+int b200sam_op_layernorm(const float* x, int rows, int D, const float* g, const float* b, float eps, void* out_bf16,
+                         int windowed, void* stream);
+
+/* Attention with decomposed rel-pos (image_encoder.py:235-260,354-392) on a packed qkv buffer
+ * (rows, 3*heads*hd) bf16; S = 14 (rows = nbatch*196) or 64 (rows = nbatch*4096); rel_h / rel_w: (2S-1, hd) f32.
+ * out: (rows, heads*hd) bf16. */
+int b200sam_op_attention(const void* qkv_bf16, int nbatch, int S, int heads, int hd, const float* rel_h,
+                         const float* rel_w, void* out_bf16, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SAM_H_ */
