@@ -1,0 +1,894 @@
+// libb200sam C ABI (include/b200sam.h): handle, weight ingestion/repacking, and the launch sequences of
+// ImageEncoderViT.forward (image_encoder.py:110-125), PromptEncoder text path + both MaskDecoders
+// (prompt_encoder.py:140-186, mask_decoder.py:79-178) and Sam.postprocess_masks (sam.py:155-189).
+//
+// No work is done on the host per element and nothing is allocated on the hot path: the workspace is sized at
+// create() and every compute entry point only enqueues kernels on the caller's stream.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/b200sam.h"
+#include "common.cuh"
+#include "decoder.cuh"
+#include "gemm_tc.cuh"
+#include "kernels.cuh"
+#include "model.cuh"
+
+using namespace bsam;
+
+namespace {
+
+int fail(b200sam_t* h, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (h) h->err = buf;
+  return code;
+}
+
+#define CU(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess)                                                                         \
+      return fail(h, B200SAM_ERR_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+  } while (0)
+
+// kernel launch through one of the launch_* helpers: counts it
+#define KL(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess)                                                                         \
+      return fail(h, B200SAM_ERR_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+    ++h->launches;                                                                                 \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+template <typename T>
+cudaError_t dalloc(b200sam_t* h, T** p, size_t count, bool zero = false) {
+  void* q = nullptr;
+  cudaError_t e = cudaMalloc(&q, count * sizeof(T) + 256);
+  if (e != cudaSuccess) return e;
+  if (zero) {
+    e = cudaMemset(q, 0, count * sizeof(T));
+    if (e != cudaSuccess) return e;
+  }
+  h->owned.push_back(q);
+  *p = reinterpret_cast<T*>(q);
+  return cudaSuccess;
+}
+
+struct ManifestEntry {
+  std::string name;
+  std::vector<int64_t> shape;
+  bool required;
+};
+
+void add(std::vector<ManifestEntry>& m, const std::string& n, std::vector<int64_t> s, bool req = true) {
+  m.push_back({n, std::move(s), req});
+}
+void add_lin(std::vector<ManifestEntry>& m, const std::string& p, int64_t out, int64_t in) {
+  add(m, p + ".weight", {out, in});
+  add(m, p + ".bias", {out});
+}
+void add_ln(std::vector<ManifestEntry>& m, const std::string& p, int64_t n, bool req = true) {
+  add(m, p + ".weight", {n}, req);
+  add(m, p + ".bias", {n}, req);
+}
+void add_attn(std::vector<ManifestEntry>& m, const std::string& p, int64_t internal) {
+  add_lin(m, p + ".q_proj", internal, 256);
+  add_lin(m, p + ".k_proj", internal, 256);
+  add_lin(m, p + ".v_proj", internal, 256);
+  add_lin(m, p + ".out_proj", 256, internal);
+}
+
+// every tensor of visual_model.state_dict().  `required == false` marks tensors that must be
+// accepted by load_weight but are not on the text-prompt path (point / box / mask prompt embeddings).
+std::vector<ManifestEntry> build_manifest(const b200sam_t* h) {
+  std::vector<ManifestEntry> m;
+  const int64_t D = h->dim, hd = h->hd;
+  const std::string e = "image_encoder.";
+  add(m, e + "pos_embed", {1, kGrid, kGrid, D});
+  add(m, e + "patch_embed.proj.weight", {D, 3, kPatch, kPatch});
+  add(m, e + "patch_embed.proj.bias", {D});
+  for (int i = 0; i < h->depth; ++i) {
+    const std::string b = e + "blocks." + std::to_string(i) + ".";
+    bool glob = false;
+    for (int g : h->global_idx) glob |= (g == i);
+    const int64_t S = glob ? kGrid : kWin;
+    add_ln(m, b + "norm1", D);
+    add(m, b + "attn.rel_pos_h", {2 * S - 1, hd});
+    add(m, b + "attn.rel_pos_w", {2 * S - 1, hd});
+    add_lin(m, b + "attn.qkv", 3 * D, D);
+    add_lin(m, b + "attn.proj", D, D);
+    add_ln(m, b + "norm2", D);
+    add_lin(m, b + "mlp.lin1", 4 * D, D);
+    add_lin(m, b + "mlp.lin2", D, 4 * D);
+  }
+  add(m, e + "neck.0.weight", {256, D, 1, 1});
+  add_ln(m, e + "neck.1", 256);
+  add(m, e + "neck.2.weight", {256, 256, 3, 3});
+  add_ln(m, e + "neck.3", 256);
+  const std::string p = "prompt_encoder.";
+  add(m, p + "pe_layer.positional_encoding_gaussian_matrix", {2, 128});
+  add(m, p + "no_mask_embed.weight", {1, 256});
+  for (int k = 0; k < 4; ++k) add(m, p + "point_embeddings." + std::to_string(k) + ".weight", {1, 256}, false);
+  add(m, p + "not_a_point_embed.weight", {1, 256}, false);
+  add(m, p + "mask_downscaling.0.weight", {4, 1, 2, 2}, false);
+  add(m, p + "mask_downscaling.0.bias", {4}, false);
+  add_ln(m, p + "mask_downscaling.1", 4, false);
+  add(m, p + "mask_downscaling.3.weight", {16, 4, 2, 2}, false);
+  add(m, p + "mask_downscaling.3.bias", {16}, false);
+  add_ln(m, p + "mask_downscaling.4", 16, false);
+  add(m, p + "mask_downscaling.6.weight", {256, 16, 1, 1}, false);
+  add(m, p + "mask_downscaling.6.bias", {256}, false);
+  for (int s = 0; s < 2; ++s) {
+    const std::string d = s == 0 ? "mask_decoder_left." : "mask_decoder_right.";
+    add(m, d + "iou_token.weight", {1, 256});
+    add(m, d + "mask_tokens.weight", {4, 256});
+    for (int l = 0; l < 2; ++l) {
+      const std::string t = d + "transformer.layers." + std::to_string(l) + ".";
+      add_attn(m, t + "self_attn", 256);
+      add_ln(m, t + "norm1", 256);
+      add_attn(m, t + "cross_attn_token_to_image", 128);
+      add_ln(m, t + "norm2", 256);
+      add_lin(m, t + "mlp.lin1", 2048, 256);
+      add_lin(m, t + "mlp.lin2", 256, 2048);
+      add_ln(m, t + "norm3", 256);
+      add_ln(m, t + "norm4", 256);
+      add_attn(m, t + "cross_attn_image_to_token", 128);
+    }
+    add_attn(m, d + "transformer.final_attn_token_to_image", 128);
+    add_ln(m, d + "transformer.norm_final_attn", 256);
+    add(m, d + "output_upscaling.0.weight", {256, 64, 2, 2});
+    add(m, d + "output_upscaling.0.bias", {64});
+    add_ln(m, d + "output_upscaling.1", 64);
+    add(m, d + "output_upscaling.3.weight", {64, 32, 2, 2});
+    add(m, d + "output_upscaling.3.bias", {32});
+    for (int k = 0; k < 4; ++k) {
+      const std::string q = d + "output_hypernetworks_mlps." + std::to_string(k) + ".layers.";
+      add_lin(m, q + "0", 256, 256);
+      add_lin(m, q + "1", 256, 256);
+      add_lin(m, q + "2", 32, 256);
+    }
+    const std::string q = d + "iou_prediction_head.layers.";
+    add_lin(m, q + "0", 256, 256);
+    add_lin(m, q + "1", 256, 256);
+    add_lin(m, q + "2", 4, 256);
+    if (s == 0) {  // build_sam.py:103,116: taxonomy head only on the left decoder
+      const std::string x = d + "taxonomy_embed.layers.";
+      add_lin(m, x + "0", 1024, 1024);
+      add_lin(m, x + "1", 1024, 1024);
+      add_lin(m, x + "2", 4, 1024);
+    }
+  }
+  return m;
+}
+
+const float* W(b200sam_t* h, const std::string& name) { return h->w.at(name).d; }
+
+AttnW attn_w(b200sam_t* h, const std::string& p, int internal) {
+  AttnW a;
+  a.qw = W(h, p + ".q_proj.weight");
+  a.qb = W(h, p + ".q_proj.bias");
+  a.kw = W(h, p + ".k_proj.weight");
+  a.kb = W(h, p + ".k_proj.bias");
+  a.vw = W(h, p + ".v_proj.weight");
+  a.vb = W(h, p + ".v_proj.bias");
+  a.ow = W(h, p + ".out_proj.weight");
+  a.ob = W(h, p + ".out_proj.bias");
+  a.internal = internal;
+  return a;
+}
+
+AttnPtrs attn_ptrs(const AttnW& a) { return AttnPtrs{a.qw, a.qb, a.kw, a.kb, a.vw, a.vb, a.ow, a.ob}; }
+
+int make_bf16(b200sam_t* h, const float* src, long n, __nv_bfloat16** out) {
+  CU(dalloc(h, out, (size_t)n));
+  KL(launch_cast_f32_bf16(src, *out, n, 0));
+  return 0;
+}
+
+// Stacked [k_proj ; v_proj] weight of a token->image attention and its positional table:
+//   k = (keys + pe) Wk^T + bk = keys Wk^T + (pe Wk^T + bk),  v = keys Wv^T + bv      (transformer.py:163-165,220-225)
+// so one GEMM over the image side yields [k | v] with the constant part added from a (4096, 256) table.
+int make_kv_tables(b200sam_t* h, const AttnW& a, float** kv_w, float** kv_tab) {
+  CU(dalloc(h, kv_w, 256 * 256));
+  CU(cudaMemcpy(*kv_w, a.kw, 128 * 256 * 4, cudaMemcpyDeviceToDevice));
+  CU(cudaMemcpy(*kv_w + 128 * 256, a.vw, 128 * 256 * 4, cudaMemcpyDeviceToDevice));
+  CU(dalloc(h, kv_tab, (size_t)kTokens * 256));
+  // exact fp32 evaluation (SIMT) of pe @ Wk^T + bk: one-time cost at finalisation
+  GemmEpi e;
+  e.bias = a.kb;
+  e.out = *kv_tab;
+  e.ld_out = 256;
+  KL(gemm_tc(true, GM_F32, h->pe_tok, 256, a.kw, 256, kTokens, 128, 256, e, 0, /*debug_simt=*/true));
+  std::vector<float> bv(128);
+  CU(cudaMemcpy(bv.data(), a.vb, 128 * 4, cudaMemcpyDeviceToHost));
+  std::vector<float> rows((size_t)kTokens * 128);
+  for (int t = 0; t < kTokens; ++t) memcpy(&rows[(size_t)t * 128], bv.data(), 128 * 4);
+  CU(cudaMemcpy2D(*kv_tab + 128, 256 * 4, rows.data(), 128 * 4, 128 * 4, kTokens, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int finalize_side(b200sam_t* h, int s) {
+  DecSide& d = h->side[s];
+  const std::string p = s == 0 ? "mask_decoder_left." : "mask_decoder_right.";
+  d.has_taxonomy = (s == 0);
+  d.iou_token = W(h, p + "iou_token.weight");
+  d.mask_tokens = W(h, p + "mask_tokens.weight");
+  for (int l = 0; l < 2; ++l) {
+    DecLayer& L = d.layer[l];
+    const std::string t = p + "transformer.layers." + std::to_string(l) + ".";
+    L.self_attn = attn_w(h, t + "self_attn", 256);
+    L.t2i = attn_w(h, t + "cross_attn_token_to_image", 128);
+    L.i2t = attn_w(h, t + "cross_attn_image_to_token", 128);
+    L.n1g = W(h, t + "norm1.weight"); L.n1b = W(h, t + "norm1.bias");
+    L.n2g = W(h, t + "norm2.weight"); L.n2b = W(h, t + "norm2.bias");
+    L.n3g = W(h, t + "norm3.weight"); L.n3b = W(h, t + "norm3.bias");
+    L.n4g = W(h, t + "norm4.weight"); L.n4b = W(h, t + "norm4.bias");
+    L.mlp1w = W(h, t + "mlp.lin1.weight"); L.mlp1b = W(h, t + "mlp.lin1.bias");
+    L.mlp2w = W(h, t + "mlp.lin2.weight"); L.mlp2b = W(h, t + "mlp.lin2.bias");
+    if (int r = make_kv_tables(h, L.t2i, &L.kv_w, &L.kv_tab)) return r;
+    // image->token query table: q = (keys + pe) Wq^T + bq                                  (transformer.py:174-176)
+    CU(dalloc(h, &L.q_tab, (size_t)kTokens * 128));
+    GemmEpi e;
+    e.bias = L.i2t.qb;
+    e.out = L.q_tab;
+    e.ld_out = 128;
+    KL(gemm_tc(true, GM_F32, h->pe_tok, 256, L.i2t.qw, 256, kTokens, 128, 256, e, 0, true));
+  }
+  d.final_attn = attn_w(h, p + "transformer.final_attn_token_to_image", 128);
+  d.nfg = W(h, p + "transformer.norm_final_attn.weight");
+  d.nfb = W(h, p + "transformer.norm_final_attn.bias");
+  if (int r = make_kv_tables(h, d.final_attn, &d.final_kv_w, &d.final_kv_tab)) return r;
+
+  // output_upscaling (mask_decoder.py:54-64): ConvTranspose2d(k2,s2) == GEMM with N = (ky, kx, out) + pixel shuffle.
+  // ConvT weight layout is (in, out, ky, kx).
+  {
+    std::vector<float> w0(256 * 64 * 4), b0(64), w0p(256 * 256), b0p(256);
+    CU(cudaMemcpy(w0.data(), W(h, p + "output_upscaling.0.weight"), w0.size() * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(b0.data(), W(h, p + "output_upscaling.0.bias"), b0.size() * 4, cudaMemcpyDeviceToHost));
+    for (int ky = 0; ky < 2; ++ky)
+      for (int kx = 0; kx < 2; ++kx)
+        for (int o = 0; o < 64; ++o) {
+          const int n = (ky * 2 + kx) * 64 + o;
+          b0p[n] = b0[o];
+          for (int c = 0; c < 256; ++c) w0p[(size_t)n * 256 + c] = w0[((size_t)c * 64 + o) * 4 + ky * 2 + kx];
+        }
+    CU(dalloc(h, &d.up0_w, w0p.size()));
+    CU(dalloc(h, &d.up0_b, b0p.size()));
+    CU(cudaMemcpy(d.up0_w, w0p.data(), w0p.size() * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d.up0_b, b0p.data(), b0p.size() * 4, cudaMemcpyHostToDevice));
+    std::vector<float> w3(64 * 32 * 4), b3(32), w3p(128 * 64), b3p(128);
+    CU(cudaMemcpy(w3.data(), W(h, p + "output_upscaling.3.weight"), w3.size() * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(b3.data(), W(h, p + "output_upscaling.3.bias"), b3.size() * 4, cudaMemcpyDeviceToHost));
+    for (int ky = 0; ky < 2; ++ky)
+      for (int kx = 0; kx < 2; ++kx)
+        for (int o = 0; o < 32; ++o) {
+          const int n = (ky * 2 + kx) * 32 + o;
+          b3p[n] = b3[o];
+          for (int c = 0; c < 64; ++c) w3p[(size_t)n * 64 + c] = w3[((size_t)c * 32 + o) * 4 + ky * 2 + kx];
+        }
+    CU(dalloc(h, &d.up3_w, w3p.size()));
+    CU(dalloc(h, &d.up3_b, b3p.size()));
+    CU(cudaMemcpy(d.up3_w, w3p.data(), w3p.size() * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d.up3_b, b3p.data(), b3p.size() * 4, cudaMemcpyHostToDevice));
+  }
+  d.up1_lng = W(h, p + "output_upscaling.1.weight");
+  d.up1_lnb = W(h, p + "output_upscaling.1.bias");
+  for (int k = 0; k < 4; ++k)
+    for (int j = 0; j < 3; ++j) {
+      const std::string q = p + "output_hypernetworks_mlps." + std::to_string(k) + ".layers." + std::to_string(j);
+      d.hyp_w[k][j] = W(h, q + ".weight");
+      d.hyp_b[k][j] = W(h, q + ".bias");
+    }
+  for (int j = 0; j < 3; ++j) {
+    const std::string q = p + "iou_prediction_head.layers." + std::to_string(j);
+    d.iou_w[j] = W(h, q + ".weight");
+    d.iou_b[j] = W(h, q + ".bias");
+    if (s == 0) {
+      const std::string x = p + "taxonomy_embed.layers." + std::to_string(j);
+      d.tax_w[j] = W(h, x + ".weight");
+      d.tax_b[j] = W(h, x + ".bias");
+    } else {
+      d.tax_w[j] = nullptr;
+      d.tax_b[j] = nullptr;
+    }
+  }
+  return 0;
+}
+
+int alloc_workspace(b200sam_t* h) {
+  const size_t B = h->max_batch, P = h->max_prompts, D = h->dim;
+  CU(dalloc(h, &h->X, B * kTokens * D));
+  CU(dalloc(h, &h->ln_win, B * kWinRowsPerFrame * D, /*zero=*/true));   // pad rows stay zero forever
+  CU(dalloc(h, &h->ln_plain, B * kTokens * D));
+  CU(dalloc(h, &h->qkv, B * kWinRowsPerFrame * 3 * D));
+  CU(dalloc(h, &h->attn_o, B * kWinRowsPerFrame * D));
+  const size_t hid_cols = 4 * D > 9 * 256 ? 4 * D : 9 * 256;
+  CU(dalloc(h, &h->hid, B * kTokens * hid_cols));
+  CU(dalloc(h, &h->emb_tok, B * kTokens * 256));
+  CU(dalloc(h, &h->emb_in, B * kTokens * 256));
+  if (P > 0) {
+    CU(dalloc(h, &h->prompt_frame, P));
+    CU(dalloc(h, &h->keys, P * kTokens * 256));
+    CU(dalloc(h, &h->kv, P * kTokens * 256));
+    CU(dalloc(h, &h->qimg, P * kTokens * 128));
+    CU(dalloc(h, &h->oimg, P * kTokens * 128));
+    CU(dalloc(h, &h->up1, P * 16384 * 64));
+    CU(dalloc(h, &h->tok_state, P * 6 * 256));
+    CU(dalloc(h, &h->tok_pe, P * 6 * 256));
+    CU(dalloc(h, &h->tok_q, P * 6 * 128));
+    CU(dalloc(h, &h->tok_o, P * 6 * 128));
+    CU(dalloc(h, &h->tok_kv, P * 6 * 256));
+    CU(dalloc(h, &h->hyper, P * 32));
+  }
+  return 0;
+}
+
+int create_common(b200sam_t** out, int dim, int depth, int heads, const int* gidx, int ng, int device, int max_batch,
+                  int max_prompts) {
+  if (!out) return B200SAM_ERR_INVALID;
+  *out = nullptr;
+  b200sam_t* h = new b200sam();
+  *out = h;   // returned even on failure so the caller can read last_error, then destroy
+  if (dim <= 0 || depth <= 0 || heads <= 0 || dim % heads != 0 || dim % 64 != 0 || dim > 1280 || max_batch <= 0 ||
+      max_prompts < 0)
+    return fail(h, B200SAM_ERR_INVALID, "bad hyper-parameters dim=%d depth=%d heads=%d max_batch=%d max_prompts=%d", dim,
+                depth, heads, max_batch, max_prompts);
+  h->dim = dim;
+  h->depth = depth;
+  h->heads = heads;
+  h->hd = dim / heads;
+  if (h->hd != 64 && h->hd != 80) return fail(h, B200SAM_ERR_INVALID, "head dim %d not in {64, 80}", h->hd);
+  for (int i = 0; i < ng; ++i) {
+    if (gidx[i] < 0 || gidx[i] >= depth) return fail(h, B200SAM_ERR_INVALID, "global index %d out of range", gidx[i]);
+    h->global_idx.push_back(gidx[i]);
+  }
+  h->device = device;
+  h->max_batch = max_batch;
+  h->max_prompts = max_prompts;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail(h, B200SAM_ERR_UNSUPPORTED, "no CUDA device: libb200sam has no CPU fallback");
+  if (device < 0 || device >= ndev) return fail(h, B200SAM_ERR_INVALID, "device %d of %d", device, ndev);
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return fail(h, B200SAM_ERR_UNSUPPORTED, "device %d is sm_%d%d; libb200sam is built for sm_100a only", device,
+                prop.major, prop.minor);
+  DeviceGuard g(device);
+  CU(gemm_tc_init(device));
+  CU(attention_init());
+  CU(decoder_init());
+  return alloc_workspace(h);
+}
+
+int check_ready(b200sam_t* h) {
+  if (!h) return B200SAM_ERR_INVALID;
+  if (!h->finalized) return fail(h, B200SAM_ERR_STATE, "weights not finalised: call b200sam_finalize_weights first");
+  return 0;
+}
+
+int run_gemm(b200sam_t* h, bool tf32, int mode, const void* A, int lda, const void* Wt, int ldw, long M, int N, int K,
+             const GemmEpi& e, cudaStream_t s) {
+  if (M > 0x7fffffffL) return fail(h, B200SAM_ERR_INVALID, "GEMM M too large");
+  KL(gemm_tc(tf32, mode, A, lda, Wt, ldw, (int)M, N, K, e, s, h->debug_simt));
+  return 0;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------ lifecycle
+
+extern "C" int b200sam_create(b200sam_t** out, int arch, int device, int max_batch, int max_prompts) {
+  // build_sam.py:15-48
+  static const int gb[4] = {2, 5, 8, 11}, gl[4] = {5, 11, 17, 23}, gh[4] = {7, 15, 23, 31};
+  switch (arch) {
+    case B200SAM_VIT_B: return create_common(out, 768, 12, 12, gb, 4, device, max_batch, max_prompts);
+    case B200SAM_VIT_L: return create_common(out, 1024, 24, 16, gl, 4, device, max_batch, max_prompts);
+    case B200SAM_VIT_H: return create_common(out, 1280, 32, 16, gh, 4, device, max_batch, max_prompts);
+    default:
+      if (out) {
+        *out = new b200sam();
+        (*out)->err = "unknown arch id";
+      }
+      return B200SAM_ERR_INVALID;
+  }
+}
+
+extern "C" int b200sam_create_custom(b200sam_t** out, int dim, int depth, int heads, const int* host_global_idx,
+                                     int n_global, int device, int max_batch, int max_prompts) {
+  return create_common(out, dim, depth, heads, host_global_idx, n_global, device, max_batch, max_prompts);
+}
+
+extern "C" void b200sam_destroy(b200sam_t* h) {
+  if (!h) return;
+  {
+    DeviceGuard g(h->device);
+    for (void* p : h->owned) cudaFree(p);
+    for (auto& kv : h->w) cudaFree(kv.second.d);
+  }
+  delete h;
+}
+
+extern "C" const char* b200sam_last_error(const b200sam_t* h) { return h ? h->err.c_str() : "null handle"; }
+
+extern "C" int64_t b200sam_launch_count(const b200sam_t* h) { return h ? h->launches : 0; }
+
+extern "C" int b200sam_set_debug_simt_gemm(b200sam_t* h, int on) {
+  if (!h) return B200SAM_ERR_INVALID;
+  h->debug_simt = on != 0;
+  return 0;
+}
+
+extern "C" int b200sam_debug_stop_after_block(b200sam_t* h, int nblocks) {
+  if (!h) return B200SAM_ERR_INVALID;
+  h->debug_stop_block = nblocks;
+  return 0;
+}
+
+extern "C" int b200sam_debug_read_tokens(b200sam_t* h, float* out, int B, void* stream) {
+  if (!h || !out || B < 0 || B > h->max_batch) return B200SAM_ERR_INVALID;
+  DeviceGuard g(h->device);
+  CU(cudaMemcpyAsync(out, h->X, (size_t)B * kTokens * h->dim * sizeof(float), cudaMemcpyDeviceToDevice,
+                     reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ weights
+
+extern "C" int b200sam_load_weight(b200sam_t* h, const char* name, const void* ptr, int dtype,
+                                   const int64_t* host_shape, int ndim) {
+  if (!h) return B200SAM_ERR_INVALID;
+  if (!name || !ptr || !host_shape || ndim < 0 || ndim > 8) return fail(h, B200SAM_ERR_INVALID, "bad load_weight args");
+  DeviceGuard g(h->device);
+  std::vector<ManifestEntry> man = build_manifest(h);
+  const ManifestEntry* me = nullptr;
+  for (const auto& m : man)
+    if (m.name == name) me = &m;
+  if (!me) return fail(h, B200SAM_ERR_INVALID, "unknown weight name '%s'", name);
+  std::vector<int64_t> shape(host_shape, host_shape + ndim);
+  if (shape != me->shape) {
+    std::string got, want;
+    for (auto v : shape) got += std::to_string(v) + ",";
+    for (auto v : me->shape) want += std::to_string(v) + ",";
+    return fail(h, B200SAM_ERR_INVALID, "shape mismatch for '%s': got (%s) want (%s)", name, got.c_str(), want.c_str());
+  }
+  long n = 1;
+  for (auto v : shape) n *= v;
+  const int esz = dtype == B200SAM_F32 ? 4 : (dtype == B200SAM_BF16 || dtype == B200SAM_F16 ? 2 : 0);
+  if (!esz) return fail(h, B200SAM_ERR_INVALID, "bad dtype %d for '%s'", dtype, name);
+  Tensor& t = h->w[name];
+  if (!t.d) {
+    void* q = nullptr;
+    CU(cudaMalloc(&q, (size_t)n * 4 + 256));
+    t.d = reinterpret_cast<float*>(q);
+  }
+  t.shape = shape;
+  t.numel = n;
+  if (dtype == B200SAM_F32) {
+    CU(cudaMemcpy(t.d, ptr, (size_t)n * 4, cudaMemcpyDefault));
+  } else {
+    void* tmp = nullptr;
+    CU(cudaMalloc(&tmp, (size_t)n * 2 + 256));
+    cudaError_t e = cudaMemcpy(tmp, ptr, (size_t)n * 2, cudaMemcpyDefault);
+    if (e == cudaSuccess) e = launch_to_f32(tmp, dtype, t.d, n, 0);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    cudaFree(tmp);
+    CU(e);
+    ++h->launches;
+  }
+  h->finalized = false;
+  return 0;
+}
+
+extern "C" int b200sam_finalize_weights(b200sam_t* h) {
+  if (!h) return B200SAM_ERR_INVALID;
+  DeviceGuard g(h->device);
+  for (const auto& m : build_manifest(h))
+    if (m.required && !h->w.count(m.name)) return fail(h, B200SAM_ERR_STATE, "missing weight '%s'", m.name.c_str());
+  // free derived buffers of a previous finalize (workspace is kept: it is allocated first, see below)
+  // -> simplest correct policy: derived buffers are appended to `owned`; a second finalize leaks nothing on destroy.
+  const long D = h->dim;
+  const std::string e = "image_encoder.";
+  if (int r = make_bf16(h, W(h, e + "patch_embed.proj.weight"), D * 768, &h->patch_w)) return r;
+  h->patch_b = W(h, e + "patch_embed.proj.bias");
+  h->pos = W(h, e + "pos_embed");
+  h->blk.assign(h->depth, EncBlock());
+  for (int i = 0; i < h->depth; ++i) {
+    EncBlock& b = h->blk[i];
+    const std::string p = e + "blocks." + std::to_string(i) + ".";
+    for (int gi : h->global_idx) b.global |= (gi == i);
+    b.ln1g = W(h, p + "norm1.weight"); b.ln1b = W(h, p + "norm1.bias");
+    b.ln2g = W(h, p + "norm2.weight"); b.ln2b = W(h, p + "norm2.bias");
+    b.qkv_b = W(h, p + "attn.qkv.bias"); b.proj_b = W(h, p + "attn.proj.bias");
+    b.lin1_b = W(h, p + "mlp.lin1.bias"); b.lin2_b = W(h, p + "mlp.lin2.bias");
+    if (int r = make_bf16(h, W(h, p + "attn.qkv.weight"), 3 * D * D, &b.qkv_w)) return r;
+    if (int r = make_bf16(h, W(h, p + "attn.proj.weight"), D * D, &b.proj_w)) return r;
+    if (int r = make_bf16(h, W(h, p + "mlp.lin1.weight"), 4 * D * D, &b.lin1_w)) return r;
+    if (int r = make_bf16(h, W(h, p + "mlp.lin2.weight"), 4 * D * D, &b.lin2_w)) return r;
+    const int S = b.global ? kGrid : kWin;
+    const int RP = b.global ? 128 : 32;
+    CU(dalloc(h, &b.relh, (size_t)RP * h->hd));
+    CU(dalloc(h, &b.relw, (size_t)RP * h->hd));
+    KL(launch_relpos_pack(W(h, p + "attn.rel_pos_h"), S, h->hd, b.relh, 0));
+    KL(launch_relpos_pack(W(h, p + "attn.rel_pos_w"), S, h->hd, b.relw, 0));
+  }
+  if (int r = make_bf16(h, W(h, e + "neck.0.weight"), 256 * D, &h->neck0_w)) return r;
+  {
+    // neck.2 Conv2d 3x3 weight (out, in, dy, dx) -> (out, dy, dx, in): the K order of launch_im2col_3x3
+    std::vector<float> w((size_t)256 * 256 * 9), wp(w.size());
+    CU(cudaMemcpy(w.data(), W(h, e + "neck.2.weight"), w.size() * 4, cudaMemcpyDeviceToHost));
+    for (int o = 0; o < 256; ++o)
+      for (int c = 0; c < 256; ++c)
+        for (int t = 0; t < 9; ++t) wp[((size_t)o * 9 + t) * 256 + c] = w[((size_t)o * 256 + c) * 9 + t];
+    float* tmp = nullptr;
+    CU(dalloc(h, &tmp, wp.size()));
+    CU(cudaMemcpy(tmp, wp.data(), wp.size() * 4, cudaMemcpyHostToDevice));
+    if (int r = make_bf16(h, tmp, (long)wp.size(), &h->neck2_w)) return r;
+  }
+  h->neck1g = W(h, e + "neck.1.weight"); h->neck1b = W(h, e + "neck.1.bias");
+  h->neck3g = W(h, e + "neck.3.weight"); h->neck3b = W(h, e + "neck.3.bias");
+  // prompt encoder constants (prompt_encoder.py:67-76,182-184): dense PE once, in fp32
+  CU(dalloc(h, &h->pe_tok, (size_t)kTokens * 256));
+  KL(launch_dense_pe(W(h, "prompt_encoder.pe_layer.positional_encoding_gaussian_matrix"), h->pe_tok, 0));
+  h->no_mask = W(h, "prompt_encoder.no_mask_embed.weight");
+  for (int s = 0; s < 2; ++s)
+    if (int r = finalize_side(h, s)) return r;
+  CU(cudaDeviceSynchronize());
+  h->finalized = true;
+  h->have_emb = false;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ encode
+
+extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype, int B, void* emb_out, int emb_dtype,
+                              void* stream) {
+  if (int r = check_ready(h)) return r;
+  if (B < 0 || B > h->max_batch) return fail(h, B200SAM_ERR_INVALID, "batch %d exceeds max_batch %d", B, h->max_batch);
+  if (B == 0) return 0;
+  if (!frames) return fail(h, B200SAM_ERR_INVALID, "frames is NULL");
+  if (frames_dtype < 0 || frames_dtype > 2 || (emb_out && (emb_dtype < 0 || emb_dtype > 2)))
+    return fail(h, B200SAM_ERR_INVALID, "unsupported dtype");
+  DeviceGuard g(h->device);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int D = h->dim, heads = h->heads, hd = h->hd;
+  const long T = (long)B * kTokens, TW = (long)B * kWinRowsPerFrame;
+
+  // PatchEmbed + pos_embed (image_encoder.py:111-113): im2col index map, GEMM, bias + pos_embed in the epilogue
+  KL(launch_im2col_patch(frames, frames_dtype, B, h->hid, s));
+  {
+    GemmEpi e;
+    e.bias = h->patch_b;
+    e.addend = h->pos;
+    e.ld_add = D;
+    e.add_mod = kTokens;
+    e.out = h->X;
+    e.ld_out = D;
+    if (int r = run_gemm(h, false, GM_F32, h->hid, 768, h->patch_w, 768, T, D, 768, e, s)) return r;
+  }
+  const int nblocks = (h->debug_stop_block >= 0 && h->debug_stop_block < h->depth) ? h->debug_stop_block : h->depth;
+  for (int i = 0; i < nblocks; ++i) {
+    const EncBlock& b = h->blk[i];
+    // norm1 (+ window_partition folded into the store; pad rows of ln_win are zero = F.pad after the norm)
+    const __nv_bfloat16* a_in = b.global ? h->ln_plain : h->ln_win;
+    KL(launch_layernorm_bf16(h->X, T, D, b.ln1g, b.ln1b, 1e-6f, b.global ? h->ln_plain : h->ln_win, !b.global, s));
+    const long rows = b.global ? T : TW;
+    {
+      GemmEpi e;
+      e.bias = b.qkv_b;
+      e.out = h->qkv;
+      e.ld_out = 3 * D;
+      if (int r = run_gemm(h, false, GM_BIAS_BF16, a_in, D, b.qkv_w, D, rows, 3 * D, D, e, s)) return r;
+    }
+    KL(launch_attention(h->qkv, b.global ? B : B * kWinPerSide * kWinPerSide, b.global ? kGrid : kWin, heads, hd, b.relh,
+                        b.relw, h->attn_o, s));
+    {
+      // proj + window_unpartition + residual: x = shortcut + attn(x)             (image_encoder.py:187-190)
+      GemmEpi e;
+      e.bias = b.proj_b;
+      e.addend = h->X;
+      e.ld_add = D;
+      e.out = h->X;
+      e.ld_out = D;
+      e.rowmap = b.global ? RM_IDENT : RM_WINDOW_TO_TOKEN;
+      if (int r = run_gemm(h, false, GM_F32, h->attn_o, D, b.proj_w, D, rows, D, D, e, s)) return r;
+    }
+    // x = x + lin2(GELU(lin1(norm2(x))))                                          (image_encoder.py:191, common.py:25-26)
+    KL(launch_layernorm_bf16(h->X, T, D, b.ln2g, b.ln2b, 1e-6f, h->ln_plain, false, s));
+    {
+      GemmEpi e;
+      e.bias = b.lin1_b;
+      e.out = h->hid;
+      e.ld_out = 4 * D;
+      if (int r = run_gemm(h, false, GM_BIAS_GELU_BF16, h->ln_plain, D, b.lin1_w, D, T, 4 * D, D, e, s)) return r;
+    }
+    {
+      GemmEpi e;
+      e.bias = b.lin2_b;
+      e.addend = h->X;
+      e.ld_add = D;
+      e.out = h->X;
+      e.ld_out = D;
+      if (int r = run_gemm(h, false, GM_F32, h->hid, 4 * D, b.lin2_w, 4 * D, T, D, 4 * D, e, s)) return r;
+    }
+  }
+  if (nblocks != h->depth) return 0;   // debug: residual stream after `nblocks` blocks is left in X
+  // neck (image_encoder.py:92-108): conv1x1 -> LayerNorm2d -> conv3x3 -> LayerNorm2d, token-major
+  KL(launch_cast_f32_bf16(h->X, h->ln_plain, T * D, s));
+  __nv_bfloat16* z = h->attn_o;   // (T, 256) bf16 scratch
+  {
+    GemmEpi e;
+    e.out2 = z;
+    e.ld_out = 256;
+    e.ln_g = h->neck1g;
+    e.ln_b = h->neck1b;
+    e.ln_eps = 1e-6f;
+    if (int r = run_gemm(h, false, GM_LN, h->ln_plain, D, h->neck0_w, D, T, 256, D, e, s)) return r;
+  }
+  KL(launch_im2col_3x3(z, B, h->hid, s));
+  {
+    GemmEpi e;
+    e.out = h->emb_tok;
+    e.ld_out = 256;
+    e.ln_g = h->neck3g;
+    e.ln_b = h->neck3b;
+    e.ln_eps = 1e-6f;
+    if (int r = run_gemm(h, false, GM_LN, h->hid, 9 * 256, h->neck2_w, 9 * 256, T, 256, 9 * 256, e, s)) return r;
+  }
+  if (emb_out) KL(launch_tokens_to_nchw(h->emb_tok, B, emb_out, emb_dtype, s));
+  h->have_emb = true;
+  h->emb_batch = B;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ decode
+
+namespace {
+
+int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, int P, float* lowres, float* iou,
+                float* tax, cudaStream_t s) {
+  const DecSide& d = h->side[sidx];
+  const long rows = (long)P * kTokens;
+  // src = image_embeddings (repeat_interleave per prompt) + dense_prompt_embeddings      (mask_decoder.py:143-144)
+  KL(launch_keys_init(emb_tok, h->no_mask, h->prompt_frame, P, h->keys, s));
+  for (int l = 0; l < 2; ++l) {
+    const DecLayer& L = d.layer[l];
+    TokStageA a;
+    a.layer = l;
+    a.iou_token = d.iou_token;
+    a.mask_tokens = d.mask_tokens;
+    a.seg = seg;
+    a.sa = attn_ptrs(L.self_attn);
+    a.n1g = L.n1g;
+    a.n1b = L.n1b;
+    a.t2i_qw = L.t2i.qw;
+    a.t2i_qb = L.t2i.qb;
+    a.tok_state = h->tok_state;
+    a.tok_pe = h->tok_pe;
+    a.tok_q = h->tok_q;
+    KL(launch_dec_stage_a(a, P, s));
+    {
+      GemmEpi e;   // [k | v] of the image side for token->image attention
+      e.addend = L.kv_tab;
+      e.ld_add = 256;
+      e.add_mod = kTokens;
+      e.out = h->kv;
+      e.ld_out = 256;
+      if (int r = run_gemm(h, true, GM_F32, h->keys, 256, L.kv_w, 256, rows, 256, 256, e, s)) return r;
+    }
+    KL(launch_dec_t2i(h->tok_q, h->kv, h->tok_o, P, s));
+    TokStageB b;
+    b.t2i_ow = L.t2i.ow; b.t2i_ob = L.t2i.ob;
+    b.n2g = L.n2g; b.n2b = L.n2b; b.n3g = L.n3g; b.n3b = L.n3b;
+    b.mlp1w = L.mlp1w; b.mlp1b = L.mlp1b; b.mlp2w = L.mlp2w; b.mlp2b = L.mlp2b;
+    b.i2t_kw = L.i2t.kw; b.i2t_kb = L.i2t.kb; b.i2t_vw = L.i2t.vw; b.i2t_vb = L.i2t.vb;
+    b.tok_o = h->tok_o;
+    b.tok_pe = h->tok_pe;
+    b.tok_state = h->tok_state;
+    b.tok_kv = h->tok_kv;
+    KL(launch_dec_stage_b(b, P, s));
+    {
+      GemmEpi e;   // image->token queries
+      e.addend = L.q_tab;
+      e.ld_add = 128;
+      e.add_mod = kTokens;
+      e.out = h->qimg;
+      e.ld_out = 128;
+      if (int r = run_gemm(h, true, GM_F32, h->keys, 256, L.i2t.qw, 256, rows, 128, 256, e, s)) return r;
+    }
+    KL(launch_dec_i2t(h->qimg, h->tok_kv, h->oimg, P, s));
+    {
+      GemmEpi e;   // keys = norm4(keys + out_proj(attn))                                  (transformer.py:176-180)
+      e.bias = L.i2t.ob;
+      e.addend = h->keys;
+      e.ld_add = 256;
+      e.out = h->keys;
+      e.ld_out = 256;
+      e.ln_g = L.n4g;
+      e.ln_b = L.n4b;
+      e.ln_eps = 1e-5f;
+      if (int r = run_gemm(h, true, GM_LN, h->oimg, 128, L.i2t.ow, 128, rows, 256, 128, e, s)) return r;
+    }
+  }
+  // final token->image attention (transformer.py:100-104)
+  KL(launch_dec_stage_q(h->tok_state, h->tok_pe, d.final_attn.qw, d.final_attn.qb, h->tok_q, P, s));
+  {
+    GemmEpi e;
+    e.addend = d.final_kv_tab;
+    e.ld_add = 256;
+    e.add_mod = kTokens;
+    e.out = h->kv;
+    e.ld_out = 256;
+    if (int r = run_gemm(h, true, GM_F32, h->keys, 256, d.final_kv_w, 256, rows, 256, 256, e, s)) return r;
+  }
+  KL(launch_dec_t2i(h->tok_q, h->kv, h->tok_o, P, s));
+  TokHeads th;
+  th.ow = d.final_attn.ow; th.ob = d.final_attn.ob; th.nfg = d.nfg; th.nfb = d.nfb;
+  for (int j = 0; j < 3; ++j) {
+    th.hyp_w[j] = d.hyp_w[0][j]; th.hyp_b[j] = d.hyp_b[0][j];
+    th.iou_w[j] = d.iou_w[j]; th.iou_b[j] = d.iou_b[j];
+    th.tax_w[j] = d.tax_w[j]; th.tax_b[j] = d.tax_b[j];
+  }
+  th.tok_state = h->tok_state;
+  th.tok_o = h->tok_o;
+  th.hyper = h->hyper;
+  th.iou_out = iou;
+  th.tax_out = d.has_taxonomy ? tax : nullptr;
+  KL(launch_dec_heads(th, P, s));
+  if (lowres) {
+    // output_upscaling + hypernetwork product, mask slot 0 only (multimask_output=False, mask_decoder.py:110-115)
+    {
+      GemmEpi e;
+      e.bias = d.up0_b;
+      e.ln_g = d.up1_lng;
+      e.ln_b = d.up1_lnb;
+      e.ln_eps = 1e-6f;
+      e.out = h->up1;
+      if (int r = run_gemm(h, true, GM_UPS1, h->keys, 256, d.up0_w, 256, rows, 256, 256, e, s)) return r;
+    }
+    {
+      GemmEpi e;
+      e.bias = d.up3_b;
+      e.hyper = h->hyper;
+      e.out = lowres;
+      if (int r = run_gemm(h, true, GM_UPS2, h->up1, 64, d.up3_w, 64, (long)P * 16384, 128, 64, e, s)) return r;
+    }
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b200sam_decode(b200sam_t* h, const void* emb, int emb_dtype, int B, const float* seg_embeds,
+                              const int* host_prompt_offsets, float* lowres_left, float* lowres_right, float* iou_left,
+                              float* iou_right, float* taxonomy, void* stream) {
+  if (int r = check_ready(h)) return r;
+  if (B < 0 || B > h->max_batch) return fail(h, B200SAM_ERR_INVALID, "batch %d exceeds max_batch %d", B, h->max_batch);
+  if (!host_prompt_offsets) return fail(h, B200SAM_ERR_INVALID, "host_prompt_offsets is NULL");
+  if (host_prompt_offsets[0] != 0) return fail(h, B200SAM_ERR_INVALID, "prompt offsets must start at 0");
+  for (int i = 0; i < B; ++i)
+    if (host_prompt_offsets[i + 1] < host_prompt_offsets[i])
+      return fail(h, B200SAM_ERR_INVALID, "prompt offsets must be non-decreasing");   // LISA.py:193 assert
+  const int P = host_prompt_offsets[B];
+  if (P > h->max_prompts) return fail(h, B200SAM_ERR_INVALID, "%d prompts exceed max_prompts %d", P, h->max_prompts);
+  if (P == 0) return 0;   // no [SEG] token generated: empty outputs (chat.py:227)
+  if (!seg_embeds) return fail(h, B200SAM_ERR_INVALID, "seg_embeds is NULL");
+  DeviceGuard g(h->device);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const float* emb_tok = h->emb_tok;
+  if (emb) {
+    if (emb_dtype < 0 || emb_dtype > 2) return fail(h, B200SAM_ERR_INVALID, "unsupported emb dtype");
+    KL(launch_nchw_to_tokens(emb, emb_dtype, B, h->emb_in, s));
+    emb_tok = h->emb_in;
+  } else if (!h->have_emb || h->emb_batch < B) {
+    return fail(h, B200SAM_ERR_STATE, "decode(emb = NULL) needs a preceding encode of at least %d frames", B);
+  }
+  std::vector<int> pf(P);
+  for (int i = 0; i < B; ++i)
+    for (int p = host_prompt_offsets[i]; p < host_prompt_offsets[i + 1]; ++p) pf[p] = i;
+  // small pageable H2D copy, stream ordered: returns once the data is staged, so `pf` may go out of scope
+  CU(cudaMemcpyAsync(h->prompt_frame, pf.data(), (size_t)P * sizeof(int), cudaMemcpyHostToDevice, s));
+  if (lowres_left || iou_left || taxonomy)
+    if (int r = decode_side(h, 0, emb_tok, seg_embeds, P, lowres_left, iou_left, taxonomy, s)) return r;
+  if (lowres_right || iou_right)
+    if (int r = decode_side(h, 1, emb_tok, seg_embeds, P, lowres_right, iou_right, nullptr, s)) return r;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ postprocess / PE
+
+extern "C" int b200sam_postprocess(b200sam_t* h, const float* lowres, int n_masks, int in_h, int in_w, int out_h,
+                                   int out_w, float* logits_out, uint8_t* mask_out, float threshold, void* stream) {
+  if (!h) return B200SAM_ERR_INVALID;
+  if (n_masks < 0 || in_h < 1 || in_w < 1 || in_h > kImg || in_w > kImg || out_h < 1 || out_w < 1)
+    return fail(h, B200SAM_ERR_INVALID, "bad postprocess sizes n=%d in=(%d,%d) out=(%d,%d)", n_masks, in_h, in_w, out_h,
+                out_w);
+  if (n_masks == 0) return 0;
+  if (!lowres) return fail(h, B200SAM_ERR_INVALID, "lowres is NULL");
+  DeviceGuard g(h->device);
+  KL(launch_postprocess(lowres, n_masks, in_h, in_w, out_h, out_w, logits_out, mask_out, threshold,
+                        reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int b200sam_dense_pe(b200sam_t* h, float* out, void* stream) {
+  if (int r = check_ready(h)) return r;
+  if (!out) return fail(h, B200SAM_ERR_INVALID, "out is NULL");
+  DeviceGuard g(h->device);
+  KL(launch_tokens_to_nchw(h->pe_tok, 1, out, DT_F32, reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ operator entry points
+
+extern "C" int b200sam_op_gemm(int device, int tf32, int mode, const void* A, int lda, const void* Wt, int ldw, int M,
+                               int N, int K, const float* bias, const float* addend, int ld_add, int add_mod,
+                               const float* ln_g, const float* ln_b, float ln_eps, void* out, int ld_out, int rowmap,
+                               int debug_simt, void* stream) {
+  DeviceGuard g(device);
+  if (gemm_tc_init(device) != cudaSuccess) return B200SAM_ERR_CUDA;
+  GemmEpi e;
+  e.bias = bias;
+  e.addend = addend;
+  e.ld_add = ld_add;
+  e.add_mod = add_mod;
+  e.out = out;
+  e.ld_out = ld_out;
+  e.rowmap = rowmap;
+  e.ln_g = ln_g;
+  e.ln_b = ln_b;
+  e.ln_eps = ln_eps;
+  if (mode < GM_BIAS_BF16 || mode > GM_LN) return B200SAM_ERR_INVALID;
+  cudaError_t err = gemm_tc(tf32 != 0, mode, A, lda, Wt, ldw, M, N, K, e, reinterpret_cast<cudaStream_t>(stream),
+                            debug_simt != 0);
+  if (err == cudaErrorInvalidValue) return B200SAM_ERR_INVALID;
+  return err == cudaSuccess ? 0 : B200SAM_ERR_CUDA;
+}
+
+extern "C" int b200sam_op_layernorm(const float* x, int rows, int D, const float* g, const float* b, float eps,
+                                    void* out_bf16, int windowed, void* stream) {
+  cudaError_t err = launch_layernorm_bf16(x, rows, D, g, b, eps, reinterpret_cast<__nv_bfloat16*>(out_bf16),
+                                          windowed != 0, reinterpret_cast<cudaStream_t>(stream));
+  if (err == cudaErrorInvalidValue) return B200SAM_ERR_INVALID;
+  return err == cudaSuccess ? 0 : B200SAM_ERR_CUDA;
+}
+
+extern "C" int b200sam_op_attention(const void* qkv_bf16, int nbatch, int S, int heads, int hd, const float* rel_h,
+                                    const float* rel_w, void* out_bf16, void* stream) {
+  if ((S != kWin && S != kGrid) || (hd != 64 && hd != 80) || heads <= 0 || nbatch < 0) return B200SAM_ERR_INVALID;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int RP = S == kWin ? 32 : 128;
+  __nv_bfloat16* tabs = nullptr;
+  if (cudaMalloc(reinterpret_cast<void**>(&tabs), (size_t)2 * RP * hd * 2) != cudaSuccess) return B200SAM_ERR_CUDA;
+  cudaError_t err = launch_relpos_pack(rel_h, S, hd, tabs, s);
+  if (err == cudaSuccess) err = launch_relpos_pack(rel_w, S, hd, tabs + RP * hd, s);
+  if (err == cudaSuccess)
+    err = launch_attention(reinterpret_cast<const __nv_bfloat16*>(qkv_bf16), nbatch, S, heads, hd, tabs, tabs + RP * hd,
+                           reinterpret_cast<__nv_bfloat16*>(out_bf16), s);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+  cudaFree(tabs);
+  return err == cudaSuccess ? 0 : B200SAM_ERR_CUDA;
+}

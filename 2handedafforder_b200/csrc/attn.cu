@@ -13,7 +13,7 @@
 #include "common.cuh"
 #include "kernels.cuh"
 
-namespace b200sam {
+namespace bsam {
 
 namespace {
 
@@ -332,4 +332,4 @@ cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int he
   return cudaErrorInvalidValue;
 }
 
-}  // namespace b200sam
+}  // namespace bsam

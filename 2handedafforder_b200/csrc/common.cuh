@@ -8,7 +8,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-namespace b200sam {
+namespace bsam {
 
 // Fixed geometry of the path: 1024^2 frames, 16x16 patches, 14x14 windows
 // (reference: 2Haff/model/segment_anything/build_sam.py:67-84).
@@ -178,4 +178,4 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
-}  // namespace b200sam
+}  // namespace bsam

@@ -8,7 +8,7 @@
 
 #include "common.cuh"
 
-namespace b200sam {
+namespace bsam {
 
 namespace {
 
@@ -411,4 +411,4 @@ cudaError_t launch_dec_heads(const TokHeads& a, int P, cudaStream_t s) {
   return cudaGetLastError();
 }
 
-}  // namespace b200sam
+}  // namespace bsam

@@ -2,7 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
-namespace b200sam {
+namespace bsam {
 
 struct AttnPtrs {
   const float *qw, *qb, *kw, *kb, *vw, *vb, *ow, *ob;
@@ -56,4 +56,4 @@ cudaError_t launch_dec_stage_b(const TokStageB& a, int P, cudaStream_t s);
 cudaError_t launch_dec_i2t(const float* qimg, const float* tok_kv, float* oimg, int P, cudaStream_t s);
 cudaError_t launch_dec_heads(const TokHeads& a, int P, cudaStream_t s);
 
-}  // namespace b200sam
+}  // namespace bsam

@@ -4,7 +4,7 @@
 #include "common.cuh"
 #include "kernels.cuh"
 
-namespace b200sam {
+namespace bsam {
 
 namespace {
 
@@ -287,4 +287,4 @@ cudaError_t launch_relpos_pack(const float* rel, int S, int hd, __nv_bfloat16* o
   return cudaGetLastError();
 }
 
-}  // namespace b200sam
+}  // namespace bsam

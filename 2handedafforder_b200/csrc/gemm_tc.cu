@@ -24,7 +24,7 @@
 
 #include "common.cuh"
 
-namespace b200sam {
+namespace bsam {
 
 namespace {
 
@@ -473,4 +473,4 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
   }
 }
 
-}  // namespace b200sam
+}  // namespace bsam

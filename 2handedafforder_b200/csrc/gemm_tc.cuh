@@ -3,7 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-namespace b200sam {
+namespace bsam {
 
 // Epilogue selector.  C[m, n] = sum_k A[m, k] * W[n, k]  (both operands K-major, i.e. nn.Linear layout),
 // then per mode:
@@ -46,4 +46,4 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
 // Must be called once per process before gemm_tc (resolves cuTensorMapEncodeTiled, sets smem attributes).
 cudaError_t gemm_tc_init(int device);
 
-}  // namespace b200sam
+}  // namespace bsam

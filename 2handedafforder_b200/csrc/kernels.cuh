@@ -4,7 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-namespace b200sam {
+namespace bsam {
 
 enum DType : int { DT_F32 = 0, DT_BF16 = 1, DT_F16 = 2 };
 
@@ -39,4 +39,4 @@ struct DecoderWorkspace;
 cudaError_t launch_postprocess(const float* lowres, int n, int in_h, int in_w, int out_h, int out_w, float* logits,
                                uint8_t* mask, float thr, cudaStream_t s);
 
-}  // namespace b200sam
+}  // namespace bsam

@@ -10,7 +10,7 @@
 #include "gemm_tc.cuh"
 #include "kernels.cuh"
 
-namespace b200sam {
+namespace bsam {
 
 struct Tensor {
   float* d = nullptr;               // fp32 master copy on the device
@@ -61,7 +61,7 @@ struct DecSide {
   const float* tax_b[3];
 };
 
-}  // namespace b200sam
+}  // namespace bsam
 
 struct b200sam {
   int dim = 0, depth = 0, heads = 0, hd = 0;
@@ -70,25 +70,26 @@ struct b200sam {
   std::string err;
   int64_t launches = 0;
   bool debug_simt = false;
+  int debug_stop_block = -1;         // >= 0: encode() stops after that many blocks (bisecting only)
   bool finalized = false;
   bool have_emb = false;
   int emb_batch = 0;
 
-  std::map<std::string, b200sam::Tensor> w;
+  std::map<std::string, bsam::Tensor> w;
   std::vector<void*> owned;          // derived device buffers (freed in destroy)
 
   // encoder
   __nv_bfloat16* patch_w = nullptr;
   const float* patch_b = nullptr;
   const float* pos = nullptr;
-  std::vector<b200sam::EncBlock> blk;
+  std::vector<bsam::EncBlock> blk;
   __nv_bfloat16 *neck0_w = nullptr, *neck2_w = nullptr;
   const float *neck1g, *neck1b, *neck3g, *neck3b;
   // prompt encoder
   float* pe_tok = nullptr;           // (4096, 256) dense positional encoding, token-major
   const float* no_mask = nullptr;    // (256)
   // decoders
-  b200sam::DecSide side[2];
+  bsam::DecSide side[2];
 
   // workspace (sized for max_batch / max_prompts)
   float* X = nullptr;                // (B*4096, D) fp32 residual stream

@@ -1,0 +1,405 @@
+"""Drop-in `visual_model` for 2HandedAfforder's LISA wrapper, backed by libb200sam (sm_100a CUDA).
+
+Mirrors the reference `Sam` container as LISA drives it
+(2Haff/model/segment_anything/modeling/sam.py:18-55,155-189; call sites 2Haff/model/LISA.py:157-168,
+284-325, 487-532): submodules `image_encoder`, `prompt_encoder`, `mask_decoder_left`, `mask_decoder_right`
+and the method `postprocess_masks`, with the reference's argument names, shapes and state_dict keys.
+All arithmetic happens in the CUDA library; this file only validates arguments, owns the nn.Parameters
+(so `from_pretrained`, `.bfloat16()`, `.cuda()`, `load_state_dict` keep working) and marshals pointers.
+
+There is NO PyTorch / CPU fallback: calling any compute method without a CUDA device or without the built
+library raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+from torch import nn
+
+from . import _lib
+from ._manifest import GRID, OUT_CH, manifest
+
+IMG_SIZE = 1024   # build_sam.py:68
+
+_DTYPES = {torch.float32: _lib.F32, torch.bfloat16: _lib.BF16, torch.float16: _lib.F16}
+
+
+def _stream_ptr() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t: Optional[torch.Tensor]) -> C.c_void_p:
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+class _Tree(nn.Module):
+    """Parameter container; children/parameters are attached by dotted state_dict name."""
+
+    def attach(self, dotted: str, value: torch.Tensor, is_buffer: bool) -> None:
+        node = self
+        parts = dotted.split(".")
+        for p in parts[:-1]:
+            if p not in node._modules:
+                node.add_module(p, _Tree())
+            node = node._modules[p]
+        if is_buffer:
+            node.register_buffer(parts[-1], value)
+        else:
+            node.register_parameter(parts[-1], nn.Parameter(value))
+
+
+def _init_tensor(name: str, shape: Tuple[int, ...], g: torch.Generator) -> torch.Tensor:
+    """Random init in the spirit of the reference modules' defaults (values are normally overwritten by a
+    checkpoint).  pos_embed / rel_pos_* start at zero as in image_encoder.py:70-74,232-233."""
+    leaf = name.rsplit(".", 1)[-1]
+    if "pos_embed" in name or "rel_pos" in name:
+        return torch.zeros(shape)
+    if "gaussian_matrix" in name or "_token" in name or "embed" in name.split(".")[-2]:
+        return torch.randn(shape, generator=g)
+    if leaf == "bias":
+        return torch.zeros(shape)
+    if len(shape) == 1:   # norm weight
+        return torch.ones(shape)
+    fan_in = int(math.prod(shape[1:])) if len(shape) > 1 else shape[0]
+    bound = 1.0 / math.sqrt(max(fan_in, 1))
+    return (torch.rand(shape, generator=g) * 2 - 1) * bound
+
+
+class _Component(_Tree):
+    def _bind(self, owner: "B200Sam") -> None:
+        object.__setattr__(self, "_owner", owner)   # not a registered submodule: no module cycle
+
+
+class ImageEncoderB200(_Component):
+    """ImageEncoderViT (image_encoder.py:17-125).  `forward` accepts any batch (the reference's
+    get_visual_embs loops B=1, LISA.py:157-168)."""
+
+    img_size = IMG_SIZE   # read by the reference's postprocess_masks (sam.py:180)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return self._owner._encode(x, want_output=True)
+
+
+class PromptEncoderB200(_Component):
+    """PromptEncoder, text-prompt path (prompt_encoder.py:140-186)."""
+
+    embed_dim = OUT_CH
+    image_embedding_size = (GRID, GRID)
+    input_image_size = (IMG_SIZE, IMG_SIZE)
+
+    def get_dense_pe(self) -> torch.Tensor:
+        """(1,256,64,64) positional encoding (prompt_encoder.py:67-76), fp32, computed once on the device."""
+        return self._owner._dense_pe()
+
+    def forward(self, points=None, boxes=None, masks=None, text_embeds=None):
+        if points is not None or boxes is not None or masks is not None:
+            raise NotImplementedError(
+                "B200 SAM branch implements the text-prompt path only (points/boxes/masks are never passed by "
+                "2Haff/model/LISA.py:288-293,498-503)")
+        if text_embeds is None:
+            raise ValueError("text_embeds is required")
+        if text_embeds.dim() != 3 or text_embeds.shape[1] != 1 or text_embeds.shape[2] != OUT_CH:
+            raise ValueError(f"text_embeds must be (N,1,{OUT_CH}), got {tuple(text_embeds.shape)}")
+        n = text_embeds.shape[0]
+        # cat with an fp32 empty tensor promotes to fp32 (prompt_encoder.py:165-177, Appendix A9)
+        sparse = text_embeds.to(torch.float32)
+        w = self.no_mask_embed.weight
+        dense = w.reshape(1, -1, 1, 1).expand(n, -1, GRID, GRID)   # stride-0 view (prompt_encoder.py:182-184)
+        return sparse, dense
+
+
+class MaskDecoderB200(_Component):
+    """MaskDecoder (mask_decoder.py:16-178) of one side."""
+
+    def __init__(self, side: str):
+        super().__init__()
+        self.side = side
+
+    def forward(self, image_embeddings, image_pe=None, sparse_prompt_embeddings=None,
+                dense_prompt_embeddings=None, multimask_output: bool = False):
+        if multimask_output:
+            raise NotImplementedError("multimask_output=True is never used by LISA (LISA.py:280,489)")
+        return self._owner._decode_one_side(self.side, image_embeddings, sparse_prompt_embeddings,
+                                            dense_prompt_embeddings)
+
+
+class B200Sam(nn.Module):
+    """The `visual_model` drop-in.  See module docstring."""
+
+    mask_threshold: float = 0.0    # sam.py:19
+    image_format: str = "RGB"
+
+    def __init__(self, encoder_embed_dim: int, encoder_depth: int, encoder_num_heads: int,
+                 encoder_global_attn_indexes: Sequence[int], max_batch: int = 8, max_prompts: int = 32,
+                 seed: int = 0):
+        super().__init__()
+        self.arch = (int(encoder_embed_dim), int(encoder_depth), int(encoder_num_heads),
+                     tuple(int(i) for i in encoder_global_attn_indexes))
+        self.image_encoder = ImageEncoderB200()
+        self.prompt_encoder = PromptEncoderB200()
+        self.mask_decoder_left = MaskDecoderB200("left")
+        self.mask_decoder_right = MaskDecoderB200("right")
+        for c in (self.image_encoder, self.prompt_encoder, self.mask_decoder_left, self.mask_decoder_right):
+            c._bind(self)
+        g = torch.Generator().manual_seed(seed)
+        self._names: List[str] = []
+        for name, shape, is_buf in manifest(*self.arch):
+            top, rest = name.split(".", 1)
+            getattr(self, top).attach(rest, _init_tensor(name, shape, g), is_buf)
+            self._names.append(name)
+        # non-persistent buffers of the reference (sam.py:48-51); callers normalise on the host
+        self.register_buffer("pixel_mean", torch.tensor([123.675, 116.28, 103.53]).view(-1, 1, 1), False)
+        self.register_buffer("pixel_std", torch.tensor([58.395, 57.12, 57.375]).view(-1, 1, 1), False)
+        self._handle: Optional[C.c_void_p] = None
+        self._handle_device: Optional[int] = None
+        self._cap = (int(max_batch), int(max_prompts))
+        self._sig = None
+        self._frozen = False
+        self._pe_cache: Optional[torch.Tensor] = None
+        self.eval()
+
+    # ------------------------------------------------------------------ handle / weights
+    @property
+    def device(self) -> torch.device:
+        return self.pixel_mean.device
+
+    def _tensors(self) -> List[Tuple[str, torch.Tensor]]:
+        sd = dict(self.named_parameters())
+        sd.update(dict(self.named_buffers()))
+        return [(n, sd[n]) for n in self._names]
+
+    def _destroy(self) -> None:
+        if self._handle is not None:
+            _lib.load().b200sam_destroy(self._handle)
+            self._handle = None
+            self._sig = None
+            self._pe_cache = None
+
+    def __del__(self):
+        try:
+            self._destroy()
+        except Exception:
+            pass
+
+    def _ensure(self, device: torch.device, batch: int = 0, prompts: int = 0) -> C.c_void_p:
+        if device.type != "cuda":
+            raise RuntimeError("B200Sam needs a CUDA (sm_100a) device: there is no CPU fallback")
+        lib = _lib.load()
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        cap_b, cap_p = self._cap
+        if batch > cap_b or prompts > cap_p:   # grow the pre-allocated workspace (outside the hot path)
+            self._cap = (max(cap_b, batch), max(cap_p, prompts))
+            self._destroy()
+        if self._handle is not None and self._handle_device != idx:
+            self._destroy()
+        if self._handle is None:
+            h = C.c_void_p()
+            dim, depth, heads, gidx = self.arch
+            arr = (C.c_int * len(gidx))(*gidx)
+            rc = lib.b200sam_create_custom(C.byref(h), dim, depth, heads, arr, len(gidx), idx, self._cap[0],
+                                           self._cap[1])
+            if rc != 0:
+                msg = _lib.last_error(h)
+                lib.b200sam_destroy(h)
+                raise RuntimeError(f"b200sam_create failed (status {rc}): {msg}")
+            self._handle, self._handle_device = h, idx
+            self._sig = None
+        if not (self._frozen and self._sig is not None):
+            self._sync_weights()
+        return self._handle
+
+    def _sync_weights(self) -> None:
+        tensors = self._tensors()
+        sig = tuple((t.data_ptr(), t._version, t.dtype) for _, t in tensors)
+        if sig == self._sig:
+            return
+        lib, h = _lib.load(), self._handle
+        for name, t in tensors:
+            src = t.detach()
+            if src.dtype not in _DTYPES:
+                src = src.float()
+            src = src.contiguous()
+            shape = (C.c_int64 * src.dim())(*src.shape)
+            _lib.check(lib.b200sam_load_weight(h, name.encode(), _ptr(src), _DTYPES[src.dtype], shape, src.dim()),
+                       h, f"load_weight({name})")
+        _lib.check(lib.b200sam_finalize_weights(h), h, "finalize_weights")
+        self._sig = sig
+        self._pe_cache = None
+
+    def freeze_weights(self, frozen: bool = True) -> None:
+        """Skip the per-call parameter-change check (inference servers / benchmarks)."""
+        self._frozen = frozen
+
+    def launch_count(self) -> int:
+        return 0 if self._handle is None else int(_lib.load().b200sam_launch_count(self._handle))
+
+    # ------------------------------------------------------------------ encode
+    def _encode(self, x: torch.Tensor, want_output: bool) -> Optional[torch.Tensor]:
+        if x.dim() != 4 or tuple(x.shape[1:]) != (3, IMG_SIZE, IMG_SIZE):
+            raise ValueError(f"frames must be (B,3,{IMG_SIZE},{IMG_SIZE}), got {tuple(x.shape)}")
+        if x.dtype not in _DTYPES:
+            raise TypeError(f"unsupported frame dtype {x.dtype}")
+        h = self._ensure(x.device, batch=x.shape[0])
+        x = x.contiguous()
+        out = torch.empty((x.shape[0], OUT_CH, GRID, GRID), dtype=x.dtype, device=x.device) if want_output else None
+        with torch.cuda.device(x.device):
+            rc = _lib.load().b200sam_encode(h, _ptr(x), _DTYPES[x.dtype], x.shape[0], _ptr(out), _DTYPES[x.dtype],
+                                            _stream_ptr())
+        _lib.check(rc, h, "encode")
+        return out
+
+    @torch.no_grad()
+    def get_visual_embs(self, pixel_values: torch.Tensor) -> torch.Tensor:
+        """Batched equivalent of LISAForCausalLM.get_visual_embs (LISA.py:157-168)."""
+        return self._encode(pixel_values, want_output=True)
+
+    # ------------------------------------------------------------------ prompt encoder / decoder
+    def _dense_pe(self) -> torch.Tensor:
+        dev = self.device
+        h = self._ensure(dev)
+        if self._pe_cache is None:
+            out = torch.empty((1, OUT_CH, GRID, GRID), dtype=torch.float32, device=dev)
+            with torch.cuda.device(dev):
+                _lib.check(_lib.load().b200sam_dense_pe(h, _ptr(out), _stream_ptr()), h, "dense_pe")
+            self._pe_cache = out
+        return self._pe_cache
+
+    def _check_dense(self, dense: Optional[torch.Tensor]) -> None:
+        if dense is None:
+            return
+        w = self.prompt_encoder.no_mask_embed.weight
+        if dense.data_ptr() != w.data_ptr() or dense.stride(-1) != 0 or dense.stride(-2) != 0:
+            raise NotImplementedError(
+                "dense_prompt_embeddings must be the no-mask embedding returned by prompt_encoder(...) "
+                "(mask prompts are not on the LISA path)")
+
+    def _decode_raw(self, emb: Optional[torch.Tensor], n_frames: int, seg: torch.Tensor, offsets: Sequence[int],
+                    left: bool, right: bool, device: torch.device) -> Dict[str, torch.Tensor]:
+        P = int(offsets[-1])
+        f32 = dict(dtype=torch.float32, device=device)
+        out: Dict[str, torch.Tensor] = {}
+        if left:
+            out["lowres_left"] = torch.empty((P, 256, 256), **f32)
+            out["iou_left"] = torch.empty((P, 4), **f32)
+            out["taxonomy"] = torch.empty((P, 4), **f32)
+        if right:
+            out["lowres_right"] = torch.empty((P, 256, 256), **f32)
+            out["iou_right"] = torch.empty((P, 4), **f32)
+        if P == 0:
+            return out
+        h = self._ensure(device, batch=n_frames, prompts=P)
+        seg = seg.to(device=device, dtype=torch.float32).contiguous()
+        offs = (C.c_int * len(offsets))(*[int(o) for o in offsets])
+        emb_dt = _lib.F32
+        if emb is not None:
+            if emb.dtype not in _DTYPES:
+                raise TypeError(f"unsupported embedding dtype {emb.dtype}")
+            emb = emb.contiguous()
+            emb_dt = _DTYPES[emb.dtype]
+        with torch.cuda.device(device):
+            rc = _lib.load().b200sam_decode(
+                h, _ptr(emb), emb_dt, n_frames, _ptr(seg), offs,
+                _ptr(out.get("lowres_left")), _ptr(out.get("lowres_right")), _ptr(out.get("iou_left")),
+                _ptr(out.get("iou_right")), _ptr(out.get("taxonomy")), _stream_ptr())
+        _lib.check(rc, h, "decode")
+        return out
+
+    def _decode_one_side(self, side: str, image_embeddings: torch.Tensor, sparse: torch.Tensor,
+                         dense: Optional[torch.Tensor]):
+        if image_embeddings.dim() != 4 or tuple(image_embeddings.shape) != (1, OUT_CH, GRID, GRID):
+            raise ValueError(f"image_embeddings must be (1,{OUT_CH},{GRID},{GRID}) per call (LISA.py:306,505), got "
+                             f"{tuple(image_embeddings.shape)}")
+        if sparse is None or sparse.dim() != 3 or sparse.shape[1] != 1 or sparse.shape[2] != OUT_CH:
+            raise ValueError("sparse_prompt_embeddings must be (N,1,256): exactly one [SEG] embedding per prompt")
+        self._check_dense(dense)
+        n = sparse.shape[0]
+        res = self._decode_raw(image_embeddings, 1, sparse.reshape(n, OUT_CH), [0, n], side == "left", side == "right",
+                               image_embeddings.device)
+        masks = res[f"lowres_{side}"].reshape(n, 1, 256, 256)
+        iou = res[f"iou_{side}"][:, 0:1]                       # multimask_output=False slice (mask_decoder.py:110-115)
+        if side == "left":
+            return masks, iou, res["taxonomy"]
+        return masks, iou
+
+    # ------------------------------------------------------------------ postprocess
+    def _postprocess_raw(self, lowres: torch.Tensor, input_size, original_size, want_logits: bool,
+                         want_mask: bool, threshold: float):
+        n = lowres.shape[0]
+        h_in, w_in = int(input_size[0]), int(input_size[1])
+        H, W = int(original_size[0]), int(original_size[1])
+        dev = lowres.device
+        logits = torch.empty((n, H, W), dtype=torch.float32, device=dev) if want_logits else None
+        mask = torch.empty((n, H, W), dtype=torch.uint8, device=dev) if want_mask else None
+        if n == 0:
+            return logits, mask
+        h = self._ensure(dev)
+        with torch.cuda.device(dev):
+            rc = _lib.load().b200sam_postprocess(h, _ptr(lowres), n, h_in, w_in, H, W, _ptr(logits), _ptr(mask),
+                                                 float(threshold), _stream_ptr())
+        _lib.check(rc, h, "postprocess")
+        return logits, mask
+
+    def postprocess_masks(self, masks: torch.Tensor, input_size: Tuple[int, ...],
+                          original_size: Tuple[int, ...]) -> torch.Tensor:
+        """Sam.postprocess_masks (sam.py:155-189): returns fp32 (N,C,H,W)."""
+        if masks.dim() != 4 or tuple(masks.shape[-2:]) != (256, 256):
+            raise ValueError(f"masks must be (N,C,256,256), got {tuple(masks.shape)}")
+        n, c = masks.shape[:2]
+        low = masks.to(torch.float32).contiguous().reshape(n * c, 256, 256)
+        logits, _ = self._postprocess_raw(low, input_size, original_size, True, False, 0.0)
+        return logits.reshape(n, c, int(original_size[0]), int(original_size[1]))
+
+    # ------------------------------------------------------------------ fused fast path
+    @torch.no_grad()
+    def segment(self, frames: torch.Tensor, seg_embeds: Sequence[torch.Tensor], resize_list, original_size_list,
+                threshold: float = 0.0, return_logits: bool = False) -> Dict[str, object]:
+        """encode + both decoders + postprocess + threshold for a batch of frames, without per-image Python
+        loops over kernels (the sequence LISA.evaluate runs per image, LISA.py:487-532).
+
+        frames (B,3,1024,1024); seg_embeds: B tensors (N_i,256).  Returns a dict with
+        `masks_left` / `masks_right`: list of B uint8 tensors (N_i,H_i,W_i) = logit > threshold,
+        `logits_left` / `logits_right` (only if return_logits), `taxonomy` (P,4), `iou_left`, `iou_right` (P,4),
+        `offsets` (B+1).
+        """
+        B = frames.shape[0]
+        if len(seg_embeds) != B or len(resize_list) != B or len(original_size_list) != B:
+            raise ValueError("seg_embeds / resize_list / original_size_list must have one entry per frame")  # LISA.py:193
+        offsets = [0]
+        for e in seg_embeds:
+            if e.dim() != 2 or e.shape[1] != OUT_CH:
+                raise ValueError(f"seg_embeds entries must be (N,{OUT_CH})")
+            offsets.append(offsets[-1] + e.shape[0])
+        dev = frames.device
+        self._ensure(dev, batch=B, prompts=offsets[-1])
+        self._encode(frames, want_output=False)
+        seg = torch.cat([e.to(device=dev, dtype=torch.float32) for e in seg_embeds], 0) if B else \
+            torch.empty((0, OUT_CH), device=dev)
+        res = self._decode_raw(None, B, seg, offsets, True, True, dev)
+        out: Dict[str, object] = {"taxonomy": res["taxonomy"], "iou_left": res["iou_left"],
+                                  "iou_right": res["iou_right"], "offsets": offsets,
+                                  "lowres_left": res["lowres_left"], "lowres_right": res["lowres_right"]}
+        for side in ("left", "right"):
+            masks: List[torch.Tensor] = [None] * B
+            logits: List[torch.Tensor] = [None] * B
+            i = 0
+            while i < B:   # one launch per run of frames that share (resize, original) sizes
+                j = i + 1
+                key = (tuple(int(v) for v in resize_list[i]), tuple(int(v) for v in original_size_list[i]))
+                while j < B and (tuple(int(v) for v in resize_list[j]),
+                                 tuple(int(v) for v in original_size_list[j])) == key:
+                    j += 1
+                low = res[f"lowres_{side}"][offsets[i]:offsets[j]]
+                lg, mk = self._postprocess_raw(low, key[0], key[1], return_logits, True, threshold)
+                for f in range(i, j):
+                    a, b = offsets[f] - offsets[i], offsets[f + 1] - offsets[i]
+                    masks[f] = mk[a:b]
+                    if return_logits:
+                        logits[f] = lg[a:b]
+                i = j
+            out[f"masks_{side}"] = masks
+            if return_logits:
+                out[f"logits_{side}"] = logits
+        return out

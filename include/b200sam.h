@@ -65,7 +65,8 @@ int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype, int B, vo
  * of a batch.  emb: (B,256,64,64) NCHW in emb_dtype, or NULL to use the embedding left by the last encode.
  * seg_embeds: (P,256) f32, P = host_prompt_offsets[B]; prompts of frame i are rows [off[i], off[i+1]).
  * Outputs (all f32, any may be NULL): lowres_left/right (P,256,256) = mask slot 0 (multimask_output=False,
- * mask_decoder.py:110-115); iou_left/right (P,4) full IoU head; taxonomy (P,4) softmax (left decoder only). */
+ * mask_decoder.py:110-115); iou_left/right (P,4) full IoU head; taxonomy (P,4) softmax (left decoder only).
+ * A decoder whose outputs are all NULL is not run (the facade's mask_decoder_left / _right call one side each). */
 int b200sam_decode(b200sam_t* h, const void* emb, int emb_dtype, int B, const float* seg_embeds,
                    const int* host_prompt_offsets, float* lowres_left, float* lowres_right, float* iou_left,
                    float* iou_right, float* taxonomy, void* stream);
@@ -84,6 +85,12 @@ int64_t b200sam_launch_count(const b200sam_t* h);
 
 /* Debug switch: 1 = evaluate every GEMM with the SIMT debug kernel instead of tcgen05 (bisecting only). */
 int b200sam_set_debug_simt_gemm(b200sam_t* h, int on);
+
+/* Debug: make b200sam_encode stop after `nblocks` transformer blocks (-1 = run everything, the default) and
+ * copy the fp32 residual stream (B,64,64,D) out; used by the per-block parity tests against the reference's
+ * forward-hook taps. */
+int b200sam_debug_stop_after_block(b200sam_t* h, int nblocks);
+int b200sam_debug_read_tokens(b200sam_t* h, float* out, int B, void* stream);
 
 /* ---- operator-level entry points (used by the per-op parity tests; same kernels the path uses) ---- */
 
