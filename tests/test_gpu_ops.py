@@ -1,0 +1,164 @@
+"""Operator-level parity of the sm_100a kernels (through the C ABI) against plain fp32 PyTorch on the GPU.
+
+Tolerances: bf16-operand GEMMs with fp32 accumulation are compared with an fp32 matmul of the SAME bf16-rounded
+operands (so only accumulation order and output rounding differ): 4e-3 of the output range for bf16 outputs
+(2^-8 output rounding), 2e-4 for fp32 outputs.  TF32 GEMMs: 2e-3 of range against full fp32.
+"""
+import math
+
+import pytest
+import torch
+
+from tests import gpu_util as G
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand(shape, seed, scale=1.0, dtype=torch.float32):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(dtype).cuda()
+
+
+GEMM_SHAPES = [(128, 256, 64), (300, 960, 320), (4096, 3840, 1280), (4100, 1280, 5120), (4096, 256, 2304)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+@pytest.mark.parametrize("mode", [0, 1])
+def test_gemm_bf16_out(M, N, K, mode):
+    A = _rand((M, K), 1, 1.0, torch.bfloat16)
+    W = _rand((N, K), 2, 1.0 / math.sqrt(K), torch.bfloat16)
+    bias = _rand((N,), 3, 0.5)
+    ref = A.float() @ W.float().t() + bias
+    if mode == 1:
+        ref = torch.nn.functional.gelu(ref)
+    out = G.op_gemm(A, W, mode, bias=bias)
+    assert G.rel_err(out, ref) < 4e-3
+    simt = G.op_gemm(A[:256], W, mode, bias=bias, simt=True)
+    assert G.rel_err(simt, ref[:256]) < 4e-3
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_f32_residual_in_place(M, N, K):
+    A = _rand((M, K), 4, 1.0, torch.bfloat16)
+    W = _rand((N, K), 5, 1.0 / math.sqrt(K), torch.bfloat16)
+    bias = _rand((N,), 6, 0.5)
+    X = _rand((M, N), 7)
+    ref = X + A.float() @ W.float().t() + bias
+    out = X.clone()
+    G.op_gemm(A, W, 2, bias=bias, addend=out, out=out)      # x = x + proj(...) in place
+    assert G.rel_err(out, ref) < 2e-4
+
+
+def test_gemm_f32_broadcast_addend():
+    """patch-embed epilogue: + bias + pos_embed[row % 4096] (image_encoder.py:111-113)."""
+    M, N, K = 2 * 4096, 320, 768
+    A = _rand((M, K), 8, 1.0, torch.bfloat16)
+    W = _rand((N, K), 9, 1.0 / math.sqrt(K), torch.bfloat16)
+    bias = _rand((N,), 10, 0.5)
+    pos = _rand((4096, N), 11)
+    ref = A.float() @ W.float().t() + bias + pos.repeat(2, 1)
+    out = G.op_gemm(A, W, 2, bias=bias, addend=pos, add_mod=4096)
+    assert G.rel_err(out, ref) < 2e-4
+
+
+def test_gemm_window_unpartition_rowmap():
+    """proj epilogue scatters window-ordered rows back to token order, dropping pad rows
+    (window_unpartition, image_encoder.py:291-318)."""
+    B, D = 2, 256
+    A = _rand((B * 4900, D), 12, 1.0, torch.bfloat16)
+    W = _rand((D, D), 13, 1.0 / math.sqrt(D), torch.bfloat16)
+    X = _rand((B * 4096, D), 14)
+    full = (A.float() @ W.float().t()).reshape(B, 5, 5, 14, 14, D).permute(0, 1, 3, 2, 4, 5).reshape(B, 70, 70, D)
+    ref = X + full[:, :64, :64].reshape(B * 4096, D)
+    out = X.clone()
+    G.op_gemm(A, W, 2, addend=out, out=out, rowmap=1)
+    assert G.rel_err(out, ref) < 2e-4
+
+
+@pytest.mark.parametrize("tf32", [False, True])
+def test_gemm_layernorm_epilogue(tf32):
+    M, N, K = 4096 + 37, 256, 128 if tf32 else 1280
+    dt = torch.float32 if tf32 else torch.bfloat16
+    A = _rand((M, K), 15, 1.0, dt)
+    W = _rand((N, K), 16, 1.0 / math.sqrt(K), dt)
+    bias = _rand((N,), 17, 0.5)
+    add = _rand((M, N), 18)
+    g, b = 1 + 0.1 * _rand((N,), 19), 0.05 * _rand((N,), 20)
+    ref = torch.nn.functional.layer_norm(add + A.float() @ W.float().t() + bias, (N,), g, b, 1e-5)
+    out = G.op_gemm(A, W, 3, tf32=tf32, bias=bias, addend=add, ln_g=g, ln_b=b, eps=1e-5)
+    assert G.rel_err(out, ref) < (2e-3 if tf32 else 3e-4)
+
+
+@pytest.mark.parametrize("M,N,K", [(4096, 256, 256), (5000, 128, 256), (333, 256, 128)])
+def test_gemm_tf32(M, N, K):
+    A = _rand((M, K), 21)
+    W = _rand((N, K), 22, 1.0 / math.sqrt(K))
+    tab = _rand((4096, N), 23)
+    ref = A @ W.t() + tab[torch.arange(M).cuda() % 4096]
+    out = G.op_gemm(A, W, 2, tf32=True, addend=tab, add_mod=4096)
+    assert G.rel_err(out, ref) < 2e-3
+    exact = G.op_gemm(A[:128], W, 2, tf32=True, addend=tab, add_mod=4096, simt=True)
+    assert G.rel_err(exact, ref[:128]) < 1e-5
+
+
+def test_gemm_rejects_bad_shapes():
+    A = _rand((128, 60), 24, 1.0, torch.bfloat16)
+    W = _rand((256, 60), 25, 1.0, torch.bfloat16)
+    out = torch.empty((128, 256), dtype=torch.bfloat16, device="cuda")
+    rc = G.lib().b200sam_op_gemm(0, 0, 0, G.P(A), 60, G.P(W), 60, 128, 256, 60, None, None, 0, 0, None, None, 0.0,
+                                 G.P(out), 256, 0, 0, G.stream())
+    assert rc == -1   # K % 8 != 0 is an error, never a fallback
+
+
+@pytest.mark.parametrize("D", [256, 320, 768, 1280])
+@pytest.mark.parametrize("windowed", [0, 1])
+def test_layernorm(D, windowed):
+    B = 2
+    x = _rand((B * 4096, D), 26, 2.0) + 0.3
+    g, b = 1 + 0.1 * _rand((D,), 27), 0.05 * _rand((D,), 28)
+    rows_out = B * 4900 if windowed else B * 4096
+    out = torch.zeros((rows_out, D), dtype=torch.bfloat16, device="cuda")
+    rc = G.lib().b200sam_op_layernorm(G.P(x), B * 4096, D, G.P(g), G.P(b), 1e-6, G.P(out), windowed, G.stream())
+    assert rc == 0
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.layer_norm(x, (D,), g, b, 1e-6)
+    if windowed:   # window_partition with zero pad AFTER the norm (image_encoder.py:179-183,263-288)
+        pad = torch.zeros((B, 70, 70, D), device="cuda")
+        pad[:, :64, :64] = ref.reshape(B, 64, 64, D)
+        ref = pad.reshape(B, 5, 14, 5, 14, D).permute(0, 1, 3, 2, 4, 5).reshape(B * 4900, D)
+    assert G.rel_err(out, ref) < 4e-3
+    if windowed:
+        assert float(out.float().reshape(B, 25, 196, D)[:, 24, 195].abs().max()) == 0.0   # pad rows untouched
+
+
+def _attention_ref(qkv, nb, S, heads, hd, rel_h, rel_w):
+    """Attention.forward with add_decomposed_rel_pos (image_encoder.py:235-260,354-392) in fp32."""
+    T = S * S
+    x = qkv.float().reshape(nb, T, 3, heads, hd).permute(2, 0, 3, 1, 4)
+    q, k, v = x[0], x[1], x[2]
+    attn = (q * hd ** -0.5) @ k.transpose(-2, -1)
+    idx = (torch.arange(S)[:, None] - torch.arange(S)[None, :] + S - 1).cuda()
+    Rh = rel_h.bfloat16().float()[idx]
+    Rw = rel_w.bfloat16().float()[idx]
+    rq = q.reshape(nb, heads, S, S, hd)
+    bh = torch.einsum("bnhwc,hkc->bnhwk", rq, Rh)
+    bw = torch.einsum("bnhwc,wkc->bnhwk", rq, Rw)
+    attn = attn.reshape(nb, heads, S, S, S, S) + bh[..., :, None] + bw[..., None, :]
+    attn = torch.softmax(attn.reshape(nb, heads, T, T), -1)
+    return (attn @ v).permute(0, 2, 1, 3).reshape(nb * T, heads * hd)
+
+
+@pytest.mark.parametrize("S,nb,heads,hd", [(14, 50, 4, 64), (14, 27, 3, 80), (64, 2, 2, 64), (64, 1, 3, 80)])
+def test_attention_relpos(S, nb, heads, hd):
+    rows = nb * S * S
+    qkv = _rand((rows, 3 * heads * hd), 30, 1.5, torch.bfloat16)
+    rel_h = _rand((2 * S - 1, hd), 31, 0.3)
+    rel_w = _rand((2 * S - 1, hd), 32, 0.3)
+    out = torch.empty((rows, heads * hd), dtype=torch.bfloat16, device="cuda")
+    rc = G.lib().b200sam_op_attention(G.P(qkv), nb, S, heads, hd, G.P(rel_h), G.P(rel_w), G.P(out), G.stream())
+    assert rc == 0
+    torch.cuda.synchronize()
+    ref = _attention_ref(qkv, nb, S, heads, hd, rel_h, rel_w)
+    # P is fed to the PV product as bf16 and the output is stored as bf16
+    assert G.rel_err(out, ref) < 1e-2
+    assert float((out.float() - ref).abs().mean() / ref.abs().mean()) < 5e-3
