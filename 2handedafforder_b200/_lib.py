@@ -31,6 +31,8 @@ SYMBOLS = [
     ("b200sam_dense_pe", _I, [_P, _P, _P]),
     ("b200sam_launch_count", _L, [_P]),
     ("b200sam_set_debug_simt_gemm", _I, [_P, _I]),
+    ("b200sam_profile_enable", _I, [_P, _I]),
+    ("b200sam_profile_read", _I, [_P, C.POINTER(_F), C.POINTER(_L), _I]),
     ("b200sam_debug_stop_after_block", _I, [_P, _I]),
     ("b200sam_debug_read_tokens", _I, [_P, _P, _I, _P]),
     ("b200sam_op_gemm", _I, [_I, _I, _I, _P, _I, _P, _I, _I, _I, _I, _P, _P, _I, _I, _P, _P, _F, _P, _I, _I, _I, _P]),

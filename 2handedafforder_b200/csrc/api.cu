@@ -42,14 +42,35 @@ int fail(b200sam_t* h, int code, const char* fmt, ...) {
       return fail(h, B200SAM_ERR_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
   } while (0)
 
-// kernel launch through one of the launch_* helpers: counts it
+// kernel launch through one of the launch_* helpers: counts it and, in profiling mode, brackets it with CUDA
+// events on the launching stream tagged with the current kernel class (h->pc)
 #define KL(call)                                                                                   \
   do {                                                                                             \
+    prof_begin(h);                                                                                 \
     cudaError_t e_ = (call);                                                                       \
     if (e_ != cudaSuccess)                                                                         \
       return fail(h, B200SAM_ERR_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+    prof_end(h);                                                                                   \
     ++h->launches;                                                                                 \
   } while (0)
+
+void prof_begin(b200sam_t* h) {
+  if (!h->prof_on) return;
+  if (h->prof_used == h->prof_ev.size()) {
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    h->prof_ev.push_back({a, b});
+    h->prof_cls.push_back(0);
+  }
+  cudaEventRecord(h->prof_ev[h->prof_used].first, h->prof_stream);
+}
+void prof_end(b200sam_t* h) {
+  if (!h->prof_on) return;
+  cudaEventRecord(h->prof_ev[h->prof_used].second, h->prof_stream);
+  h->prof_cls[h->prof_used] = h->pc;
+  ++h->prof_used;
+}
 
 struct DeviceGuard {
   int prev = -1;
@@ -427,6 +448,10 @@ extern "C" void b200sam_destroy(b200sam_t* h) {
   {
     DeviceGuard g(h->device);
     for (void* p : h->owned) cudaFree(p);
+    for (auto& ev : h->prof_ev) {
+      cudaEventDestroy(ev.first);
+      cudaEventDestroy(ev.second);
+    }
     for (auto& kv : h->w) cudaFree(kv.second.d);
   }
   delete h;
@@ -439,6 +464,31 @@ extern "C" int64_t b200sam_launch_count(const b200sam_t* h) { return h ? h->laun
 extern "C" int b200sam_set_debug_simt_gemm(b200sam_t* h, int on) {
   if (!h) return B200SAM_ERR_INVALID;
   h->debug_simt = on != 0;
+  return 0;
+}
+
+extern "C" int b200sam_profile_enable(b200sam_t* h, int on) {
+  if (!h) return B200SAM_ERR_INVALID;
+  h->prof_on = on != 0;
+  h->prof_used = 0;
+  return 0;
+}
+
+extern "C" int b200sam_profile_read(b200sam_t* h, float* host_ms, int64_t* host_count, int n_classes) {
+  if (!h || !host_ms || !host_count || n_classes < B200SAM_PC_COUNT) return B200SAM_ERR_INVALID;
+  DeviceGuard g(h->device);
+  for (int i = 0; i < n_classes; ++i) {
+    host_ms[i] = 0.f;
+    host_count[i] = 0;
+  }
+  for (size_t i = 0; i < h->prof_used; ++i) {
+    CU(cudaEventSynchronize(h->prof_ev[i].second));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, h->prof_ev[i].first, h->prof_ev[i].second));
+    host_ms[h->prof_cls[i]] += ms;
+    host_count[h->prof_cls[i]] += 1;
+  }
+  h->prof_used = 0;
   return 0;
 }
 
@@ -506,6 +556,8 @@ extern "C" int b200sam_load_weight(b200sam_t* h, const char* name, const void* p
 extern "C" int b200sam_finalize_weights(b200sam_t* h) {
   if (!h) return B200SAM_ERR_INVALID;
   DeviceGuard g(h->device);
+  const bool prof_was = h->prof_on;
+  h->prof_on = false;   // one-time packing kernels are not part of any profile
   for (const auto& m : build_manifest(h))
     if (m.required && !h->w.count(m.name)) return fail(h, B200SAM_ERR_STATE, "missing weight '%s'", m.name.c_str());
   // free derived buffers of a previous finalize (workspace is kept: it is allocated first, see below)
@@ -557,6 +609,7 @@ extern "C" int b200sam_finalize_weights(b200sam_t* h) {
   for (int s = 0; s < 2; ++s)
     if (int r = finalize_side(h, s)) return r;
   CU(cudaDeviceSynchronize());
+  h->prof_on = prof_was;
   h->finalized = true;
   h->have_emb = false;
   return 0;
@@ -574,10 +627,12 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
     return fail(h, B200SAM_ERR_INVALID, "unsupported dtype");
   DeviceGuard g(h->device);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  h->prof_stream = s;
   const int D = h->dim, heads = h->heads, hd = h->hd;
   const long T = (long)B * kTokens, TW = (long)B * kWinRowsPerFrame;
 
   // PatchEmbed + pos_embed (image_encoder.py:111-113): im2col index map, GEMM, bias + pos_embed in the epilogue
+  h->pc = B200SAM_PC_ELEMENTWISE;
   KL(launch_im2col_patch(frames, frames_dtype, B, h->hid, s));
   {
     GemmEpi e;
@@ -587,6 +642,7 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
     e.add_mod = kTokens;
     e.out = h->X;
     e.ld_out = D;
+    h->pc = B200SAM_PC_GEMM_PATCH;
     if (int r = run_gemm(h, false, GM_F32, h->hid, 768, h->patch_w, 768, T, D, 768, e, s)) return r;
   }
   const int nblocks = (h->debug_stop_block >= 0 && h->debug_stop_block < h->depth) ? h->debug_stop_block : h->depth;
@@ -594,6 +650,7 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
     const EncBlock& b = h->blk[i];
     // norm1 (+ window_partition folded into the store; pad rows of ln_win are zero = F.pad after the norm)
     const __nv_bfloat16* a_in = b.global ? h->ln_plain : h->ln_win;
+    h->pc = B200SAM_PC_LAYERNORM;
     KL(launch_layernorm_bf16(h->X, T, D, b.ln1g, b.ln1b, 1e-6f, b.global ? h->ln_plain : h->ln_win, !b.global, s));
     const long rows = b.global ? T : TW;
     {
@@ -601,8 +658,10 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
       e.bias = b.qkv_b;
       e.out = h->qkv;
       e.ld_out = 3 * D;
+      h->pc = B200SAM_PC_GEMM_QKV;
       if (int r = run_gemm(h, false, GM_BIAS_BF16, a_in, D, b.qkv_w, D, rows, 3 * D, D, e, s)) return r;
     }
+    h->pc = b.global ? B200SAM_PC_ATTN_GLOBAL : B200SAM_PC_ATTN_WINDOW;
     KL(launch_attention(h->qkv, b.global ? B : B * kWinPerSide * kWinPerSide, b.global ? kGrid : kWin, heads, hd, b.relh,
                         b.relw, h->attn_o, s));
     {
@@ -614,15 +673,18 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
       e.out = h->X;
       e.ld_out = D;
       e.rowmap = b.global ? RM_IDENT : RM_WINDOW_TO_TOKEN;
+      h->pc = B200SAM_PC_GEMM_PROJ;
       if (int r = run_gemm(h, false, GM_F32, h->attn_o, D, b.proj_w, D, rows, D, D, e, s)) return r;
     }
     // x = x + lin2(GELU(lin1(norm2(x))))                                          (image_encoder.py:191, common.py:25-26)
+    h->pc = B200SAM_PC_LAYERNORM;
     KL(launch_layernorm_bf16(h->X, T, D, b.ln2g, b.ln2b, 1e-6f, h->ln_plain, false, s));
     {
       GemmEpi e;
       e.bias = b.lin1_b;
       e.out = h->hid;
       e.ld_out = 4 * D;
+      h->pc = B200SAM_PC_GEMM_LIN1;
       if (int r = run_gemm(h, false, GM_BIAS_GELU_BF16, h->ln_plain, D, b.lin1_w, D, T, 4 * D, D, e, s)) return r;
     }
     {
@@ -632,11 +694,13 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
       e.ld_add = D;
       e.out = h->X;
       e.ld_out = D;
+      h->pc = B200SAM_PC_GEMM_LIN2;
       if (int r = run_gemm(h, false, GM_F32, h->hid, 4 * D, b.lin2_w, 4 * D, T, D, 4 * D, e, s)) return r;
     }
   }
   if (nblocks != h->depth) return 0;   // debug: residual stream after `nblocks` blocks is left in X
   // neck (image_encoder.py:92-108): conv1x1 -> LayerNorm2d -> conv3x3 -> LayerNorm2d, token-major
+  h->pc = B200SAM_PC_NECK;
   KL(launch_cast_f32_bf16(h->X, h->ln_plain, T * D, s));
   __nv_bfloat16* z = h->attn_o;   // (T, 256) bf16 scratch
   {
@@ -658,6 +722,7 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
     e.ln_eps = 1e-6f;
     if (int r = run_gemm(h, false, GM_LN, h->hid, 9 * 256, h->neck2_w, 9 * 256, T, 256, 9 * 256, e, s)) return r;
   }
+  h->pc = B200SAM_PC_ELEMENTWISE;
   if (emb_out) KL(launch_tokens_to_nchw(h->emb_tok, B, emb_out, emb_dtype, s));
   h->have_emb = true;
   h->emb_batch = B;
@@ -673,6 +738,7 @@ int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, 
   const DecSide& d = h->side[sidx];
   const long rows = (long)P * kTokens;
   // src = image_embeddings (repeat_interleave per prompt) + dense_prompt_embeddings      (mask_decoder.py:143-144)
+  h->pc = B200SAM_PC_DEC_ELEMENTWISE;
   KL(launch_keys_init(emb_tok, h->no_mask, h->prompt_frame, P, h->keys, s));
   for (int l = 0; l < 2; ++l) {
     const DecLayer& L = d.layer[l];
@@ -689,6 +755,7 @@ int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, 
     a.tok_state = h->tok_state;
     a.tok_pe = h->tok_pe;
     a.tok_q = h->tok_q;
+    h->pc = B200SAM_PC_DEC_TOKEN;
     KL(launch_dec_stage_a(a, P, s));
     {
       GemmEpi e;   // [k | v] of the image side for token->image attention
@@ -697,8 +764,10 @@ int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, 
       e.add_mod = kTokens;
       e.out = h->kv;
       e.ld_out = 256;
+      h->pc = B200SAM_PC_DEC_GEMM;
       if (int r = run_gemm(h, true, GM_F32, h->keys, 256, L.kv_w, 256, rows, 256, 256, e, s)) return r;
     }
+    h->pc = B200SAM_PC_DEC_TOKEN;
     KL(launch_dec_t2i(h->tok_q, h->kv, h->tok_o, P, s));
     TokStageB b;
     b.t2i_ow = L.t2i.ow; b.t2i_ob = L.t2i.ob;
@@ -717,8 +786,10 @@ int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, 
       e.add_mod = kTokens;
       e.out = h->qimg;
       e.ld_out = 128;
+      h->pc = B200SAM_PC_DEC_GEMM;
       if (int r = run_gemm(h, true, GM_F32, h->keys, 256, L.i2t.qw, 256, rows, 128, 256, e, s)) return r;
     }
+    h->pc = B200SAM_PC_DEC_TOKEN;
     KL(launch_dec_i2t(h->qimg, h->tok_kv, h->oimg, P, s));
     {
       GemmEpi e;   // keys = norm4(keys + out_proj(attn))                                  (transformer.py:176-180)
@@ -730,10 +801,12 @@ int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, 
       e.ln_g = L.n4g;
       e.ln_b = L.n4b;
       e.ln_eps = 1e-5f;
+      h->pc = B200SAM_PC_DEC_GEMM;
       if (int r = run_gemm(h, true, GM_LN, h->oimg, 128, L.i2t.ow, 128, rows, 256, 128, e, s)) return r;
     }
   }
   // final token->image attention (transformer.py:100-104)
+  h->pc = B200SAM_PC_DEC_TOKEN;
   KL(launch_dec_stage_q(h->tok_state, h->tok_pe, d.final_attn.qw, d.final_attn.qb, h->tok_q, P, s));
   {
     GemmEpi e;
@@ -742,8 +815,10 @@ int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, 
     e.add_mod = kTokens;
     e.out = h->kv;
     e.ld_out = 256;
+    h->pc = B200SAM_PC_DEC_GEMM;
     if (int r = run_gemm(h, true, GM_F32, h->keys, 256, d.final_kv_w, 256, rows, 256, 256, e, s)) return r;
   }
+  h->pc = B200SAM_PC_DEC_TOKEN;
   KL(launch_dec_t2i(h->tok_q, h->kv, h->tok_o, P, s));
   TokHeads th;
   th.ow = d.final_attn.ow; th.ob = d.final_attn.ob; th.nfg = d.nfg; th.nfb = d.nfb;
@@ -767,6 +842,7 @@ int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, 
       e.ln_b = d.up1_lnb;
       e.ln_eps = 1e-6f;
       e.out = h->up1;
+      h->pc = B200SAM_PC_DEC_UPSCALE;
       if (int r = run_gemm(h, true, GM_UPS1, h->keys, 256, d.up0_w, 256, rows, 256, 256, e, s)) return r;
     }
     {
@@ -798,9 +874,11 @@ extern "C" int b200sam_decode(b200sam_t* h, const void* emb, int emb_dtype, int 
   if (!seg_embeds) return fail(h, B200SAM_ERR_INVALID, "seg_embeds is NULL");
   DeviceGuard g(h->device);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  h->prof_stream = s;
   const float* emb_tok = h->emb_tok;
   if (emb) {
     if (emb_dtype < 0 || emb_dtype > 2) return fail(h, B200SAM_ERR_INVALID, "unsupported emb dtype");
+    h->pc = B200SAM_PC_DEC_ELEMENTWISE;
     KL(launch_nchw_to_tokens(emb, emb_dtype, B, h->emb_in, s));
     emb_tok = h->emb_in;
   } else if (!h->have_emb || h->emb_batch < B) {
@@ -829,6 +907,8 @@ extern "C" int b200sam_postprocess(b200sam_t* h, const float* lowres, int n_mask
   if (n_masks == 0) return 0;
   if (!lowres) return fail(h, B200SAM_ERR_INVALID, "lowres is NULL");
   DeviceGuard g(h->device);
+  h->prof_stream = reinterpret_cast<cudaStream_t>(stream);
+  h->pc = B200SAM_PC_POSTPROCESS;
   KL(launch_postprocess(lowres, n_masks, in_h, in_w, out_h, out_w, logits_out, mask_out, threshold,
                         reinterpret_cast<cudaStream_t>(stream)));
   return 0;
@@ -838,6 +918,8 @@ extern "C" int b200sam_dense_pe(b200sam_t* h, float* out, void* stream) {
   if (int r = check_ready(h)) return r;
   if (!out) return fail(h, B200SAM_ERR_INVALID, "out is NULL");
   DeviceGuard g(h->device);
+  h->prof_stream = reinterpret_cast<cudaStream_t>(stream);
+  h->pc = B200SAM_PC_ELEMENTWISE;
   KL(launch_tokens_to_nchw(h->pe_tok, 1, out, DT_F32, reinterpret_cast<cudaStream_t>(stream)));
   return 0;
 }

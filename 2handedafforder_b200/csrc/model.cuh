@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <map>
+#include <utility>
 #include <string>
 #include <vector>
 
@@ -70,6 +71,13 @@ struct b200sam {
   std::string err;
   int64_t launches = 0;
   bool debug_simt = false;
+  // per-kernel-class CUDA-event profile (b200sam_profile_enable / _read)
+  bool prof_on = false;
+  int pc = 0;
+  cudaStream_t prof_stream = nullptr;
+  size_t prof_used = 0;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_ev;
+  std::vector<int> prof_cls;
   int debug_stop_block = -1;         // >= 0: encode() stops after that many blocks (bisecting only)
   bool finalized = false;
   bool have_emb = false;

@@ -86,6 +86,31 @@ int64_t b200sam_launch_count(const b200sam_t* h);
 /* Debug switch: 1 = evaluate every GEMM with the SIMT debug kernel instead of tcgen05 (bisecting only). */
 int b200sam_set_debug_simt_gemm(b200sam_t* h, int on);
 
+/* Kernel classes of the per-launch profile. */
+enum b200sam_profile_class {
+  B200SAM_PC_ELEMENTWISE = 0,     /* im2col of the patches, layout transposes */
+  B200SAM_PC_GEMM_PATCH = 1,
+  B200SAM_PC_LAYERNORM = 2,
+  B200SAM_PC_GEMM_QKV = 3,
+  B200SAM_PC_ATTN_WINDOW = 4,
+  B200SAM_PC_ATTN_GLOBAL = 5,
+  B200SAM_PC_GEMM_PROJ = 6,
+  B200SAM_PC_GEMM_LIN1 = 7,
+  B200SAM_PC_GEMM_LIN2 = 8,
+  B200SAM_PC_NECK = 9,
+  B200SAM_PC_DEC_ELEMENTWISE = 10,
+  B200SAM_PC_DEC_TOKEN = 11,
+  B200SAM_PC_DEC_GEMM = 12,
+  B200SAM_PC_DEC_UPSCALE = 13,
+  B200SAM_PC_POSTPROCESS = 14,
+  B200SAM_PC_COUNT = 15
+};
+/* Measurement aid for bench.py: while enabled, every kernel launch of this handle is bracketed by a pair of CUDA
+ * events on the launching stream.  b200sam_profile_read synchronises on them, writes the summed milliseconds and
+ * the launch count of every class into the two HOST arrays (length n_classes >= B200SAM_PC_COUNT) and resets. */
+int b200sam_profile_enable(b200sam_t* h, int on);
+int b200sam_profile_read(b200sam_t* h, float* host_ms, int64_t* host_count, int n_classes);
+
 /* Debug: make b200sam_encode stop after `nblocks` transformer blocks (-1 = run everything, the default) and
  * copy the fp32 residual stream (B,64,64,D) out; used by the per-block parity tests against the reference's
  * forward-hook taps. */
