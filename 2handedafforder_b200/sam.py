@@ -268,7 +268,7 @@ class B200Sam(nn.Module):
         return self._pe_cache
 
     def _check_dense(self, dense: Optional[torch.Tensor]) -> None:
-        if dense is None:
+        if dense is None or dense.numel() == 0:
             return
         w = self.prompt_encoder.no_mask_embed.weight
         if dense.data_ptr() != w.data_ptr() or dense.stride(-1) != 0 or dense.stride(-2) != 0:
