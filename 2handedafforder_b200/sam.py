@@ -362,7 +362,7 @@ class B200Sam(nn.Module):
         frames (B,3,1024,1024); seg_embeds: B tensors (N_i,256).  Returns a dict with
         `masks_left` / `masks_right`: list of B uint8 tensors (N_i,H_i,W_i) = logit > threshold,
         `logits_left` / `logits_right` (only if return_logits), `taxonomy` (P,4), `iou_left`, `iou_right` (P,4),
-        `offsets` (B+1).
+        `offsets` (B+1); `masks_left_packed` / `masks_right_packed` (P,H,W) when every frame shares one size.
         """
         B = frames.shape[0]
         if len(seg_embeds) != B or len(resize_list) != B or len(original_size_list) != B:
@@ -393,6 +393,8 @@ class B200Sam(nn.Module):
                     j += 1
                 low = res[f"lowres_{side}"][offsets[i]:offsets[j]]
                 lg, mk = self._postprocess_raw(low, key[0], key[1], return_logits, True, threshold)
+                if i == 0 and j == B:   # one size for the whole batch: also hand out the contiguous (P,H,W) buffer
+                    out[f"masks_{side}_packed"] = mk
                 for f in range(i, j):
                     a, b = offsets[f] - offsets[i], offsets[f + 1] - offsets[i]
                     masks[f] = mk[a:b]

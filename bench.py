@@ -1,0 +1,401 @@
+#!/usr/bin/env python
+"""bench.py - frames/s of ViT-H encode + bimanual mask decode at 1024^2 on N B200 (BASELINE.json metric).
+
+One "step" = one `visual_model.segment(...)` call over a batch of B synthetic frames x 3 [SEG] prompts:
+ImageEncoderViT (ViT-H) -> PromptEncoder text path -> mask_decoder_left + mask_decoder_right -> postprocess_masks to
+1080x1920 -> threshold (u8 masks).  N > 1: every rank runs its own frames (weak scaling, frames are independent:
+SURVEY.md 8e) and the u8 masks are gathered to rank 0 over NCCL inside the step.
+
+    python bench.py --gpus 1 --steps 10 --warmup 3              # this repo's CUDA path
+    python bench.py --impl reference --steps 1 --warmup 0       # CPU arm: the oracle port on the host cores
+
+JSON keys follow the driver contract: value (device-resident inputs, CUDA events, max over ranks), e2e (pinned
+host inputs, H2D + D2H inside the timed region), roofline (dominant kernel class, measured with per-launch CUDA
+events through b200sam_profile_*), cpu_baseline (oracle port on the host cores, bounded sample), clocks,
+gpu_launches.  Nothing here reads /root/reference.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+PKG = "2handedafforder_b200"
+IMG, GRID, OUT_CH = 1024, 64, 256
+RESIZE, ORIGINAL = (576, 1024), (1080, 1920)      # 16:9 video frame, inference.py:91-105
+VIT_H = dict(dim=1280, depth=32, heads=16, global_idx=(7, 15, 23, 31))
+
+PC_NAMES = ["elementwise", "gemm_patch", "layernorm", "gemm_qkv", "attn_window", "attn_global", "gemm_proj",
+            "gemm_lin1", "gemm_lin2", "neck", "dec_elementwise", "dec_token", "dec_gemm", "dec_upscale",
+            "postprocess"]
+
+
+def flops_per_frame(n_prompts: int) -> dict:
+    """Algorithmic FLOPs per frame by kernel class (multiply-add = 2, unpadded tokens)."""
+    D, T, depth, hd = VIT_H["dim"], GRID * GRID, VIT_H["depth"], VIT_H["dim"] // VIT_H["heads"]
+    n_glob = len(VIT_H["global_idx"])
+    n_win = depth - n_glob
+    f = {
+        "gemm_patch": 2.0 * T * 768 * D,
+        "gemm_qkv": depth * 2.0 * T * D * 3 * D,
+        "gemm_proj": depth * 2.0 * T * D * D,
+        "gemm_lin1": depth * 2.0 * T * D * 4 * D,
+        "gemm_lin2": depth * 2.0 * T * D * 4 * D,
+        "attn_window": n_win * (2.0 * 2 * T * 196 * D + 2.0 * 2 * T * 14 * D),
+        "attn_global": n_glob * (2.0 * 2 * T * T * D + 2.0 * 2 * T * 64 * D),
+        "neck": 2.0 * T * D * OUT_CH + 2.0 * T * OUT_CH * OUT_CH * 9,
+        "decoder": n_prompts * 2 * 3.606e9 + n_prompts * 0.004e9,
+    }
+    f["total"] = sum(f.values())
+    return f
+
+
+def load_peaks() -> dict:
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as fh:
+            d = json.load(fh)
+        return {"bf16_burst": d["bf16_tflops"], "bf16_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                "hbm_gbs": d["hbm_gbs"], "source": "measured (MEASURED_PEAKS.json)"}
+    return {"bf16_burst": 1590.0, "bf16_sustained": 1400.0, "hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        self.t.join(timeout=2)
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        # under load = samples whose power draw is above half the max seen
+        thr = 0.5 * max(pw)
+        load = [s for s, p in zip(sm, pw) if p >= thr] or sm
+        return {"sm_mhz": statistics.median(load), "sm_max_mhz": max(mx), "power_w_max": max(pw),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------------- synthetic data
+
+def make_frames(torch, start: int, count: int):
+    """(count,3,1024,1024) fp32 ~ N(0,1), rows >= 576 zero (16:9 frame padded to square); seed 10+index."""
+    out = torch.empty((count, 3, IMG, IMG), dtype=torch.float32)
+    for i in range(count):
+        g = torch.Generator().manual_seed(10 + start + i)
+        out[i] = torch.randn(3, IMG, IMG, generator=g)
+    out[:, :, RESIZE[0]:, :] = 0.0
+    return out
+
+
+def make_seg(torch, index: int, n: int):
+    g = torch.Generator().manual_seed(100003 + index)
+    return torch.randn(n, OUT_CH, generator=g)
+
+
+def build_model(torch, max_batch: int, max_prompts: int):
+    """Random-init ViT-H visual_model (the facade's own seeded init; pos_embed / rel_pos_* get N(0, 0.02) noise so the
+    rel-pos path does real arithmetic - they are zeros at init in the reference, image_encoder.py:70-74,232-233)."""
+    pkg = importlib.import_module(PKG)
+    sam = pkg.build_sam_vit_h(max_batch=max_batch, max_prompts=max_prompts)
+    g = torch.Generator().manual_seed(1)
+    with torch.no_grad():
+        for name, p in sam.named_parameters():
+            if "pos_embed" in name or "rel_pos" in name:
+                p.copy_(0.02 * torch.randn(p.shape, generator=g))
+    return sam
+
+
+# ----------------------------------------------------------------------------------------------- CPU arm
+
+def cpu_reference_frames_per_s(torch, sd, n_prompts: int, steps: int, warmup: int):
+    """The oracle port (oracle/sam_oracle.py, fp32, all host threads) on ONE ViT-H frame x n_prompts per step:
+    encode + both decoders + postprocess + threshold.  Returns (frames/s, seconds per step list, threads)."""
+    from oracle import sam_oracle as O
+    from oracle import synth
+    arch = synth.ARCHS["vit_h"]
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    times = []
+    with torch.no_grad():
+        for it in range(warmup + steps):
+            frames = make_frames(torch, it, 1)
+            segs = [make_seg(torch, it, n_prompts)]
+            t0 = time.perf_counter()
+            res = O.segment(sd, arch, frames, segs, [RESIZE], [ORIGINAL], O.FP32)[0]
+            for side in ("left", "right"):
+                _ = (res[f"masks_{side}"] > 0).to(torch.uint8)
+            dt = time.perf_counter() - t0
+            if it >= warmup:
+                times.append(dt)
+    return len(times) / sum(times), times, threads
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's CPU path (oracle port; the reference is Python and cannot travel to the GPU
+    box) timed on the host cores.  Rank 0 only; other ranks exit 0."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return 0
+    import torch
+    sam = build_model(torch, 1, args.prompts)
+    sd = {k: v.detach().float() for k, v in sam.state_dict().items()}
+    steps = max(1, args.steps)
+    fps, times, threads = cpu_reference_frames_per_s(torch, sd, args.prompts, steps, args.warmup)
+    sample = f"1 ViT-H frame x {args.prompts} prompts per step (encode + 2 decoders + postprocess 1080x1920), fp32"
+    line = {
+        "impl": "reference", "metric": "frames/s ViT-H encode + bimanual mask decode @1024^2", "value": fps,
+        "unit": "frames/s", "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, frames_per_step=1),
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(args, frames_per_step: int) -> dict:
+    return {"workload": "configs[1]: SAM ViT-H bf16, batch of synthetic 1024^2 frames x 3 [SEG] prompts "
+                        "(left+right decoders, taxonomy), postprocess to 1080x1920 + threshold",
+            "frames_per_step_per_gpu": frames_per_step, "prompts_per_frame": args.prompts,
+            "resize": list(RESIZE), "original_size": list(ORIGINAL), "parallelism": f"frames sharded x{args.gpus}",
+            "l2": "per-step working set (1.27 GB bf16 weights + >4 GB activations) >> 126 MB L2; no explicit flush"}
+
+
+# ----------------------------------------------------------------------------------------------- GPU arm
+
+def read_profile(lib, handle):
+    ms = (C.c_float * len(PC_NAMES))()
+    cnt = (C.c_int64 * len(PC_NAMES))()
+    rc = lib.b200sam_profile_read(handle, ms, cnt, len(PC_NAMES))
+    if rc != 0:
+        raise RuntimeError(f"b200sam_profile_read status {rc}")
+    return {n: (float(ms[i]), int(cnt[i])) for i, n in enumerate(PC_NAMES)}
+
+
+def run_gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device (sm_100a): libb200sam has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n_gpus = world
+
+    B, NP = args.batch, args.prompts
+    P = B * NP
+    _lib = importlib.import_module(PKG + "._lib")
+    lib = _lib.load()
+    sam = build_model(torch, B, P).to(dev)
+    sam.freeze_weights(True)
+
+    # this rank's shard of the synthetic clip: frames [rank*B, rank*B + B)
+    host_frames = make_frames(torch, rank * B, B).to(torch.bfloat16).pin_memory()
+    host_seg = torch.cat([make_seg(torch, rank * B + i, NP) for i in range(B)], 0).pin_memory()
+    frames = host_frames.to(dev)
+    segs = [host_seg[i * NP:(i + 1) * NP].to(dev) for i in range(B)]
+    resize, original = [RESIZE] * B, [ORIGINAL] * B
+    H, W = ORIGINAL
+    gather_buf = None
+    if world > 1 and rank == 0:
+        gather_buf = [torch.empty((2, P, H, W), dtype=torch.uint8, device=dev) for _ in range(world)]
+    send_buf = torch.empty((2, P, H, W), dtype=torch.uint8, device=dev) if world > 1 else None
+
+    def step(fr, sg):
+        out = sam.segment(fr, sg, resize, original, threshold=0.0, return_logits=False)
+        if world > 1:   # masks come back to rank 0 over NCCL
+            send_buf[0].copy_(out["masks_left_packed"])
+            send_buf[1].copy_(out["masks_right_packed"])
+            dist.gather(send_buf, gather_buf, dst=0)
+        return out
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 0)):
+        step(frames, segs)
+    barrier()
+    handle = sam._handle
+
+    # ---- timed region 1: inputs resident in HBM, CUDA events, max over ranks
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    l0 = sam.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        out = step(frames, segs)
+    ev1.record()
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    launches = sam.launch_count() - l0
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    fps = world * B * args.steps / (ms_total * 1e-3)
+
+    # ---- timed region 2: end to end from pinned host buffers (H2D frames + prompts, D2H masks + heads)
+    host_masks = torch.empty((2, P, H, W), dtype=torch.uint8).pin_memory()
+    host_heads = torch.empty((3, P, 4), dtype=torch.float32).pin_memory()
+    h2d = host_frames.numel() * host_frames.element_size() + host_seg.numel() * 4
+    d2h = host_masks.numel() + host_heads.numel() * 4
+
+    def e2e_step():
+        fr = host_frames.to(dev, non_blocking=True)
+        sg_all = host_seg.to(dev, non_blocking=True)
+        sg = [sg_all[i * NP:(i + 1) * NP] for i in range(B)]
+        o = step(fr, sg)
+        host_masks[0].copy_(o["masks_left_packed"], non_blocking=True)
+        host_masks[1].copy_(o["masks_right_packed"], non_blocking=True)
+        host_heads[0].copy_(o["taxonomy"], non_blocking=True)
+        host_heads[1].copy_(o["iou_left"], non_blocking=True)
+        host_heads[2].copy_(o["iou_right"], non_blocking=True)
+        torch.cuda.current_stream().synchronize()   # the caller consumes the masks on the host
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_fps = world * B * args.steps / float(t.item())
+
+    # ---- per-launch CUDA events (b200sam_profile_*) over the same steps -> roofline of the dominant kernel
+    kernels, roofline = {}, None
+    if rank == 0:
+        lib.b200sam_profile_enable(handle, 1)
+        psteps = min(args.steps, 3)
+        for _ in range(psteps):
+            sam.segment(frames, segs, resize, original, threshold=0.0)
+        torch.cuda.synchronize()
+        prof = read_profile(lib, handle)
+        lib.b200sam_profile_enable(handle, 0)
+        fl = flops_per_frame(NP)
+        peaks = load_peaks()
+        tot_ms = sum(v[0] for v in prof.values()) / psteps
+        for name, (ms, cnt) in prof.items():
+            if cnt == 0:
+                continue
+            k = {"ms_per_step": ms / psteps, "launches_per_step": cnt // psteps, "share": (ms / psteps) / tot_ms}
+            if name in fl:
+                k["tflops"] = fl[name] * B / (ms / psteps * 1e-3) / 1e12
+            kernels[name] = k
+        dom = max((n for n in kernels if n in fl), key=lambda n: kernels[n]["ms_per_step"])
+        kd = kernels[dom]
+        roofline = {"bound": "tensor", "kernel": dom, "achieved": kd["tflops"], "peak": peaks["bf16_sustained"],
+                    "unit": "TFLOP/s", "frac": kd["tflops"] / peaks["bf16_sustained"], "traffic": None,
+                    "peak_source": peaks["source"] + ", sustained figure (kernel timed inside a long step)",
+                    "flops_per_launch": fl[dom] * B / kd["launches_per_step"],
+                    "avg_launch_ms": kd["ms_per_step"] / kd["launches_per_step"],
+                    "whole_step_tflops": fl["total"] * B / (ms_total / args.steps * 1e-3) / 1e12,
+                    "whole_step_frac": fl["total"] * B / (ms_total / args.steps * 1e-3) / 1e12 / peaks["bf16_sustained"]}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        sd = {k: v.detach().float().cpu() for k, v in sam.state_dict().items()}
+        cfps, times, threads = cpu_reference_frames_per_s(torch, sd, NP, 1, 0)
+        cpu = {"value": cfps, "unit": "frames/s", "cores": threads, "kind": "port",
+               "sample": f"1 ViT-H frame x {NP} prompts, fp32 oracle port, {times[0]:.1f} s"}
+
+    if rank == 0:
+        line = {
+            "metric": "frames/s ViT-H encode + bimanual mask decode @1024^2", "value": fps, "unit": "frames/s",
+            "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": workload_config(args, B),
+            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "kernels": kernels,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=8, help="frames per step per GPU (configs[1]: 8)")
+    ap.add_argument("--prompts", type=int, default=3, help="[SEG] prompts per frame")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    args.warmup = max(args.warmup, 3)
+    return run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
