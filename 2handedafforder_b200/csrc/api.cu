@@ -582,8 +582,8 @@ extern "C" int b200sam_finalize_weights(b200sam_t* h) {
     if (int r = make_bf16(h, W(h, p + "mlp.lin2.weight"), 4 * D * D, &b.lin2_w)) return r;
     const int S = b.global ? kGrid : kWin;
     const int RP = b.global ? 128 : 32;
-    CU(dalloc(h, &b.relh, (size_t)RP * h->hd));
-    CU(dalloc(h, &b.relw, (size_t)RP * h->hd));
+    CU(dalloc(h, &b.relh, (size_t)2 * RP * h->hd));   // [relh ; relw] contiguous: one tensor map covers both
+    b.relw = b.relh + (size_t)RP * h->hd;
     KL(launch_relpos_pack(W(h, p + "attn.rel_pos_h"), S, h->hd, b.relh, 0));
     KL(launch_relpos_pack(W(h, p + "attn.rel_pos_w"), S, h->hd, b.relw, 0));
   }
@@ -962,6 +962,8 @@ extern "C" int b200sam_op_attention(const void* qkv_bf16, int nbatch, int S, int
                                     const float* rel_w, void* out_bf16, void* stream) {
   if ((S != kWin && S != kGrid) || (hd != 64 && hd != 80) || heads <= 0 || nbatch < 0) return B200SAM_ERR_INVALID;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || gemm_tc_init(dev) != cudaSuccess) return B200SAM_ERR_CUDA;
   const int RP = S == kWin ? 32 : 128;
   __nv_bfloat16* tabs = nullptr;
   if (cudaMalloc(reinterpret_cast<void**>(&tabs), (size_t)2 * RP * hd * 2) != cudaSuccess) return B200SAM_ERR_CUDA;
@@ -972,5 +974,6 @@ extern "C" int b200sam_op_attention(const void* qkv_bf16, int nbatch, int S, int
                            reinterpret_cast<__nv_bfloat16*>(out_bf16), s);
   if (err == cudaSuccess) err = cudaStreamSynchronize(s);
   cudaFree(tabs);
+  if (err != cudaSuccess) fprintf(stderr, "b200sam_op_attention: %s\n", cudaGetErrorString(err));
   return err == cudaSuccess ? 0 : B200SAM_ERR_CUDA;
 }

@@ -325,9 +325,12 @@ cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int he
                              const __nv_bfloat16* relh, const __nv_bfloat16* relw, __nv_bfloat16* out,
                              cudaStream_t s) {
   if (nbatch <= 0) return cudaSuccess;
-  if (S == 14 && hd == 80) return launch_one<14, 80, 7>(qkv, nbatch, heads, relh, relw, out, s);
+  if (S == 14 && (hd == 80 || hd == 64)) {
+    // tcgen05 path (attn_tc.cu); the two padded tables must be contiguous: [relh (32 rows); relw (32 rows)]
+    if (relw != relh + 32 * hd) return cudaErrorInvalidValue;
+    return launch_attention_window_tc(qkv, nbatch, heads, hd, relh, out, s);
+  }
   if (S == 64 && hd == 80) return launch_one<64, 80, 8>(qkv, nbatch, heads, relh, relw, out, s);
-  if (S == 14 && hd == 64) return launch_one<14, 64, 7>(qkv, nbatch, heads, relh, relw, out, s);
   if (S == 64 && hd == 64) return launch_one<64, 64, 8>(qkv, nbatch, heads, relh, relw, out, s);
   return cudaErrorInvalidValue;
 }

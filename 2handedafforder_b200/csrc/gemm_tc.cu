@@ -447,6 +447,26 @@ cudaError_t gemm_tc_init(int device) {
   return cudaSuccess;
 }
 
+cudaError_t make_tmap_2d(void* out, const void* ptr, int esz, long rows, long cols, long ld, int box_cols, int box_rows,
+                         int swizzle_bytes) {
+  if (!g_encode) return cudaErrorInitializationError;
+  if (box_cols * esz != swizzle_bytes || box_rows > 256) return cudaErrorInvalidValue;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * esz};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (strides[0] & 15)) return cudaErrorInvalidValue;
+  const CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
+  CUresult r = g_encode(reinterpret_cast<CUtensorMap*>(out),
+                        esz == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                        const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
+int gemm_num_sms() { return g_num_sms; }
+
 cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, int ldw, int M, int N, int K,
                     const GemmEpi& e, cudaStream_t s, bool dbg) {
   if (!g_encode && !dbg) return cudaErrorInitializationError;

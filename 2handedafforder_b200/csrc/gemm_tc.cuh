@@ -43,6 +43,12 @@ struct GemmEpi {
 cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, int ldw, int M, int N, int K,
                     const GemmEpi& epi, cudaStream_t stream, bool debug_simt = false);
 
+// 2-D tiled tensor map over a row-major (rows, cols) matrix with leading dimension ld (elements).  elem_bytes 2 or 4,
+// swizzle_bytes in {32, 64, 128} with box_cols * elem_bytes == swizzle_bytes.  Needs gemm_tc_init.
+cudaError_t make_tmap_2d(void* tensor_map_out /*CUtensorMap*/, const void* ptr, int elem_bytes, long rows, long cols,
+                         long ld, int box_cols, int box_rows, int swizzle_bytes);
+int gemm_num_sms();
+
 // Must be called once per process before gemm_tc (resolves cuTensorMapEncodeTiled, sets smem attributes).
 cudaError_t gemm_tc_init(int device);
 

@@ -30,6 +30,9 @@ cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int he
                              const __nv_bfloat16* relh, const __nv_bfloat16* relw, __nv_bfloat16* out,
                              cudaStream_t s);
 cudaError_t attention_init();
+// ---- attn_tc.cu (tcgen05): windowed attention; rel = (64, hd) bf16 [rel_pos_h padded to 32 rows; rel_pos_w padded]
+cudaError_t launch_attention_window_tc(const __nv_bfloat16* qkv, int nwin, int heads, int hd, const __nv_bfloat16* rel,
+                                       __nv_bfloat16* out, cudaStream_t s);
 
 // ---- decoder.cu
 struct DecSideWeights;   // device pointers of one mask decoder (api.cu owns it)
