@@ -346,6 +346,11 @@ int alloc_workspace(b200sam_t* h) {
   CU(dalloc(h, &h->ln_plain, B * kTokens * D));
   CU(dalloc(h, &h->qkv, B * kWinRowsPerFrame * 3 * D));
   CU(dalloc(h, &h->attn_o, B * kWinRowsPerFrame * D));
+  {
+    __half* g = nullptr;
+    CU(dalloc(h, &g, B * kTokens * (size_t)h->heads * 256));
+    h->gbuf = g;
+  }
   const size_t hid_cols = 4 * D > 9 * 256 ? 4 * D : 9 * 256;
   CU(dalloc(h, &h->hid, B * kTokens * hid_cols));
   CU(dalloc(h, &h->emb_tok, B * kTokens * 256));
@@ -586,6 +591,10 @@ extern "C" int b200sam_finalize_weights(b200sam_t* h) {
     b.relw = b.relh + (size_t)RP * h->hd;
     KL(launch_relpos_pack(W(h, p + "attn.rel_pos_h"), S, h->hd, b.relh, 0));
     KL(launch_relpos_pack(W(h, p + "attn.rel_pos_w"), S, h->hd, b.relw, 0));
+    if (b.global) {
+      CU(dalloc(h, &b.relg, (size_t)256 * 128));
+      KL(launch_relpos_pack_g(W(h, p + "attn.rel_pos_h"), W(h, p + "attn.rel_pos_w"), h->hd, b.relg, 0));
+    }
   }
   if (int r = make_bf16(h, W(h, e + "neck.0.weight"), 256 * D, &h->neck0_w)) return r;
   {
@@ -663,7 +672,8 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
     }
     h->pc = b.global ? B200SAM_PC_ATTN_GLOBAL : B200SAM_PC_ATTN_WINDOW;
     KL(launch_attention(h->qkv, b.global ? B : B * kWinPerSide * kWinPerSide, b.global ? kGrid : kWin, heads, hd, b.relh,
-                        b.relw, h->attn_o, s));
+                        b.relw, b.relg, h->gbuf, h->attn_o, s));
+    if (b.global) ++h->launches;   // the batched bias-projection GEMM in front of the global kernel
     {
       // proj + window_unpartition + residual: x = shortcut + attn(x)             (image_encoder.py:187-190)
       GemmEpi e;
@@ -967,13 +977,22 @@ extern "C" int b200sam_op_attention(const void* qkv_bf16, int nbatch, int S, int
   const int RP = S == kWin ? 32 : 128;
   __nv_bfloat16* tabs = nullptr;
   if (cudaMalloc(reinterpret_cast<void**>(&tabs), (size_t)2 * RP * hd * 2) != cudaSuccess) return B200SAM_ERR_CUDA;
+  __nv_bfloat16* relg = nullptr;
+  void* gbuf = nullptr;
   cudaError_t err = launch_relpos_pack(rel_h, S, hd, tabs, s);
   if (err == cudaSuccess) err = launch_relpos_pack(rel_w, S, hd, tabs + RP * hd, s);
+  if (err == cudaSuccess && S == kGrid) {
+    err = cudaMalloc(reinterpret_cast<void**>(&relg), 256 * 128 * 2);
+    if (err == cudaSuccess) err = cudaMalloc(&gbuf, (size_t)nbatch * kTokens * heads * 256 * 2 + 256);
+    if (err == cudaSuccess) err = launch_relpos_pack_g(rel_h, rel_w, hd, relg, s);
+  }
   if (err == cudaSuccess)
     err = launch_attention(reinterpret_cast<const __nv_bfloat16*>(qkv_bf16), nbatch, S, heads, hd, tabs, tabs + RP * hd,
-                           reinterpret_cast<__nv_bfloat16*>(out_bf16), s);
+                           relg, gbuf, reinterpret_cast<__nv_bfloat16*>(out_bf16), s);
   if (err == cudaSuccess) err = cudaStreamSynchronize(s);
   cudaFree(tabs);
+  cudaFree(relg);
+  cudaFree(gbuf);
   if (err != cudaSuccess) fprintf(stderr, "b200sam_op_attention: %s\n", cudaGetErrorString(err));
   return err == cudaSuccess ? 0 : B200SAM_ERR_CUDA;
 }

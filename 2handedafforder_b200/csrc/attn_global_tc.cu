@@ -1,0 +1,406 @@
+// Global (64x64 tokens) attention with decomposed relative-position bias on tcgen05 tensor cores
+// (reference: Attention.forward image_encoder.py:235-260, add_decomposed_rel_pos :354-392).
+//
+//   A[q,k] = (q . k) * hd^-1/2 + q . Rh[qy - ky + 63] + q . Rw[qx - kx + 63]      (bias uses the UNSCALED q)
+//   O = softmax_k(A) V
+//
+// Flash-style, the 4096 x 4096 score matrix never exists in HBM (the reference materialises it, 1 GB fp32 per frame,
+// and touches it ~5x).  A persistent CTA owns 256 query rows (two M = 128 tiles that ping-pong on the tensor core)
+// of one (frame, head) and streams 128-key tiles:
+//   warp 0      TMA producer: Q tiles once per work item; K and V tiles through two 4-stage rings
+//               (head dim 80 = one SWIZZLE_128B box of 64 columns + one SWIZZLE_32B box of 16)
+//   warp 1      tcgen05.mma issuer: S_t = Q_t K_j^T into TMEM, then O_t += P_t V_j with P read from TMEM and V as an
+//               MN-major B operand; S_t(j+1) is issued right behind it so the tensor core works while the other
+//               tile's softmax runs
+//   warps 4-7 / 8-11   softmax of tile 0 / tile 1, one thread per query row: a 128-key tile is two image rows, so
+//               the h-bias is two scalars per tile and the w-bias 64 registers; lazy rescaling (O and the row sum are
+//               only rescaled when the running maximum grows by more than 2^8); P (bf16) goes back into the S columns
+// The bias projections G = Q [Rh; Rw]^T come from a batched tcgen05 GEMM (gemm_tc GM_F16) as fp16.
+#include <cudaTypedefs.h>
+
+#include "common.cuh"
+#include "gemm_tc.cuh"
+#include "kernels.cuh"
+
+namespace bsam {
+
+namespace {
+
+constexpr int kGT = kTokens;          // 4096
+constexpr int kBKeys = 128;           // keys per tile = two image rows
+constexpr int kNIter = kGT / kBKeys;  // 32
+constexpr int kQBlocks = kGT / 256;   // 16 work items per (frame, head)
+constexpr int kStagesG = 4;
+constexpr int kThreadsG = 384;
+constexpr int kOColG = 256;           // O_t at kOColG + t * 128
+
+template <int HD>
+struct GlbCfg {
+  static constexpr int kRem = HD - 64;
+  static constexpr int kMain = 128 * 128;                 // one 128-row tile, 64 columns: 16 KB
+  static constexpr int kRemB = kRem ? 128 * 32 : 0;       // 16 columns: 4 KB
+  static constexpr int kTile = kMain + kRemB;
+  static constexpr int oQm = 0;                           // 2 tiles
+  static constexpr int oKm = 2 * kMain;                   // kStagesG tiles
+  static constexpr int oVm = oKm + kStagesG * kMain;
+  static constexpr int oQr = oVm + kStagesG * kMain;
+  static constexpr int oKr = oQr + 2 * kRemB;
+  static constexpr int oVr = oKr + kStagesG * kRemB;
+  static constexpr int oBar = oVr + kStagesG * kRemB;
+  static constexpr int kSmem = oBar + 512 + 1024;
+};
+
+__device__ __forceinline__ float ex2_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int HD>
+__global__ void __launch_bounds__(kThreadsG, 1)
+attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tm32,
+                      const __half* __restrict__ G, __nv_bfloat16* __restrict__ out, int nbatch, int heads,
+                      float scale) {
+  using C = GlbCfg<HD>;
+  constexpr bool kHasRem = C::kRem > 0;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::oBar);
+  uint64_t* q_full = bars + 0;
+  uint64_t* q_empty = bars + 1;
+  uint64_t* k_full = bars + 2;                    // [kStagesG]
+  uint64_t* k_empty = k_full + kStagesG;
+  uint64_t* v_full = k_empty + kStagesG;
+  uint64_t* v_empty = v_full + kStagesG;
+  uint64_t* s_full = v_empty + kStagesG;          // [2]
+  uint64_t* p_full = s_full + 2;                  // [2]
+  uint64_t* o_full = p_full + 2;                  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nitems = nbatch * heads * kQBlocks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm128);
+    if (kHasRem) tma_prefetch_desc(&tm32);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(q_full, 1);
+    mbar_init(q_empty, 1);
+    for (int i = 0; i < kStagesG; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&v_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_full[i], 4);
+      mbar_init(&o_full[i], 1);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int it = 0, kc = 0;
+      for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
+        const int bh = item / kQBlocks, qb = item - bh * kQBlocks;
+        const int b = bh / heads, head = bh - b * heads;
+        const int row0 = b * kGT;
+        const int cq = head * HD, ck = heads * HD + head * HD, cv = 2 * heads * HD + head * HD;
+        mbar_wait(q_empty, (it & 1) ^ 1);
+        mbar_expect_tx(q_full, 2 * C::kTile);
+        for (int t = 0; t < 2; ++t) {
+          tma_load_2d(smem + C::oQm + t * C::kMain, &tm128, q_full, cq, row0 + qb * 256 + t * 128);
+          if (kHasRem) tma_load_2d(smem + C::oQr + t * C::kRemB, &tm32, q_full, cq + 64, row0 + qb * 256 + t * 128);
+        }
+        for (int j = 0; j < kNIter; ++j, ++kc) {
+          const int s = kc % kStagesG;
+          const uint32_t ph = (kc / kStagesG) & 1;
+          mbar_wait(&k_empty[s], ph ^ 1);
+          mbar_expect_tx(&k_full[s], C::kTile);
+          tma_load_2d(smem + C::oKm + s * C::kMain, &tm128, &k_full[s], ck, row0 + j * kBKeys);
+          if (kHasRem) tma_load_2d(smem + C::oKr + s * C::kRemB, &tm32, &k_full[s], ck + 64, row0 + j * kBKeys);
+          mbar_wait(&v_empty[s], ph ^ 1);
+          mbar_expect_tx(&v_full[s], C::kTile);
+          tma_load_2d(smem + C::oVm + s * C::kMain, &tm128, &v_full[s], cv, row0 + j * kBKeys);
+          if (kHasRem) tma_load_2d(smem + C::oVr + s * C::kRemB, &tm32, &v_full[s], cv + 64, row0 + j * kBKeys);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idS = umma_idesc_bf16(128, kBKeys, false, false);
+      constexpr uint32_t idO64 = umma_idesc_bf16(128, 64, false, true);
+      constexpr uint32_t idO16 = umma_idesc_bf16(128, 16, false, true);
+      const uint32_t sQm = smem_u32(smem + C::oQm), sQr = smem_u32(smem + C::oQr);
+      const uint32_t sKm = smem_u32(smem + C::oKm), sKr = smem_u32(smem + C::oKr);
+      const uint32_t sVm = smem_u32(smem + C::oVm), sVr = smem_u32(smem + C::oVr);
+      auto issue_S = [&](int t, int ks) {
+        const uint32_t aM = sQm + t * C::kMain, aR = sQr + t * C::kRemB;
+        const uint32_t bM = sKm + ks * C::kMain, bR = sKr + ks * C::kRemB;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma_ss<false>(tmem + t * 128, umma_desc(aM + k * 32, 1024, 0, 2), umma_desc(bM + k * 32, 1024, 0, 2), idS,
+                         k != 0);
+        if (kHasRem) umma_ss<false>(tmem + t * 128, umma_desc(aR, 256, 0, 6), umma_desc(bR, 256, 0, 6), idS, 1);
+      };
+      int it = 0, kc = 0;          // kc: index of the K/V tile of iteration 0 of this item in the rings
+      uint32_t np[2] = {0, 0};     // P tiles consumed per M tile (parity of p_full)
+      for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it, kc += kNIter) {
+        mbar_wait(q_full, it & 1);
+        {
+          const int s = kc % kStagesG;
+          mbar_wait(&k_full[s], (kc / kStagesG) & 1);
+          tc_fence_after();
+          issue_S(0, s);
+          umma_commit(&s_full[0]);
+          issue_S(1, s);
+          umma_commit(&s_full[1]);
+          umma_commit(&k_empty[s]);
+        }
+#pragma unroll 1
+        for (int j = 0; j < kNIter; ++j) {
+          const int sv = (kc + j) % kStagesG;
+          const int sk = (kc + j + 1) % kStagesG;
+          const bool more = j + 1 < kNIter;
+          if (more) mbar_wait(&k_full[sk], ((kc + j + 1) / kStagesG) & 1);
+          mbar_wait(&v_full[sv], ((kc + j) / kStagesG) & 1);
+#pragma unroll 1
+          for (int t = 0; t < 2; ++t) {
+            mbar_wait(&p_full[t], np[t] & 1);
+            ++np[t];
+            tc_fence_after();
+            const uint32_t dO = tmem + kOColG + t * 128, aP = tmem + t * 128;
+            const uint32_t bM = sVm + sv * C::kMain, bR = sVr + sv * C::kRemB;
+#pragma unroll
+            for (int ks = 0; ks < kBKeys / 16; ++ks) {
+              umma_ts_bf16(dO, aP + ks * 8, umma_desc(bM + ks * 2048, 1024, 1024, 2), idO64, (j | ks) != 0);
+              if (kHasRem)
+                umma_ts_bf16(dO + 64, aP + ks * 8, umma_desc(bR + ks * 512, 256, 256, 6), idO16, (j | ks) != 0);
+            }
+            if (t == 1) umma_commit(&v_empty[sv]);
+            if (more) {
+              issue_S(t, sk);
+              umma_commit(&s_full[t]);
+              if (t == 1) {
+                umma_commit(&k_empty[sk]);
+                if (j + 2 == kNIter) umma_commit(q_empty);   // last score MMAs of this item: Q tiles are dead
+              }
+            } else {
+              umma_commit(&o_full[t]);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    const int t = (warp - 4) >> 2, q = warp & 3;
+    const int rl = q * 32 + lane;                       // row inside the M tile
+    const uint32_t tl = tmem + (uint32_t(q * 32) << 16);
+    const uint32_t tS = tl + t * 128, tO = tl + kOColG + t * 128;
+    constexpr float kLog2e = 1.4426950408889634f;
+    const float cs = scale * kLog2e;
+    const long ldg = (long)heads * 256, ldo = (long)heads * HD;
+    uint32_t ns = 0;                                     // score tiles consumed (parity of s_full[t])
+    int it = 0;
+    for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
+      const int bhh = item / kQBlocks, qb = item - bhh * kQBlocks;
+      const int b = bhh / heads, head = bhh - b * heads;
+      const int qrow = qb * 256 + t * 128 + rl;          // token index inside the frame
+      const int qy = qrow >> 6, qx = qrow & 63;
+      const __half* g = G + ((long)b * kGT + qrow) * ldg + head * 256;
+      // w-bias: bw[kx] = G[128 + qx - kx + 63], pre-multiplied by log2 e
+      float bw[64];
+      float bwmax = -INFINITY;
+      {
+        const __half* gw = g + 128 + qx;
+#pragma unroll
+        for (int kx = 0; kx < 64; ++kx) {
+          bw[kx] = __half2float(__ldg(gw + 63 - kx)) * kLog2e;
+          bwmax = fmaxf(bwmax, bw[kx]);
+        }
+      }
+      const __half* gh = g + qy + 63;                    // h-bias of key row ky: gh[-ky]
+      float bh0 = __half2float(__ldg(gh)) * kLog2e, bh1 = __half2float(__ldg(gh - 1)) * kLog2e;
+      float m_used = -INFINITY, l = 0.f;
+#pragma unroll 1
+      for (int j = 0; j < kNIter; ++j) {
+        // prefetch the next tile's two h-bias values
+        float nb0 = 0.f, nb1 = 0.f;
+        if (j + 1 < kNIter) {
+          nb0 = __half2float(__ldg(gh - 2 * (j + 1)));
+          nb1 = __half2float(__ldg(gh - 2 * (j + 1) - 1));
+        }
+        mbar_wait(&s_full[t], ns & 1);
+        ++ns;
+        tc_fence_after();
+        // ---- pass 1: maximum of the raw scores -> upper bound of the biased tile maximum
+        float mx = -INFINITY;
+        {
+          uint32_t v[32];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            tmem_ld_32x32(tS + c * 32, v);
+            tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+          }
+        }
+        const float Mt = mx * cs + bwmax + fmaxf(bh0, bh1);
+        const bool grow = Mt > m_used + 8.f;
+        if (__any_sync(0xffffffffu, grow)) {
+          const float m_new = grow ? Mt : m_used;
+          const float f = ex2_fast(m_used - m_new);     // 0 on the first tile (m_used = -inf), 1 for unchanged rows
+          l *= f;
+          m_used = m_new;
+          if (j > 0) {
+            uint32_t v[32];
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+              tmem_ld_32x32(tO + c * 32, v);
+              tmem_wait_ld();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * f);
+              // 32 columns back as two x16 stores
+              uint32_t a[16], bq[16];
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                a[i] = v[i];
+                bq[i] = v[16 + i];
+              }
+              tmem_st_32x32_16(tO + c * 32, a);
+              tmem_st_32x32_16(tO + c * 32 + 16, bq);
+            }
+            if (kHasRem) {
+              uint32_t w[16];
+              tmem_ld_32x32_16(tO + 64, w);
+              tmem_wait_ld();
+#pragma unroll
+              for (int i = 0; i < 16; ++i) w[i] = __float_as_uint(__uint_as_float(w[i]) * f);
+              tmem_st_32x32_16(tO + 64, w);
+            }
+          }
+        }
+        const float c0 = bh0 - m_used, c1 = bh1 - m_used;
+        // ---- pass 2: p = 2^(s*cs + bw + bh - m), row sum, P (bf16 pairs) into the first 64 columns of S_t
+        float sum = 0.f;
+        {
+          uint32_t v[32];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            tmem_ld_32x32(tS + c * 32, v);
+            tmem_wait_ld();
+            const float cc = c < 2 ? c0 : c1;
+            uint32_t u[16];
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              const float p0 = ex2_fast(fmaf(__uint_as_float(v[i]), cs, bw[(c & 1) * 32 + i]) + cc);
+              const float p1 = ex2_fast(fmaf(__uint_as_float(v[i + 1]), cs, bw[(c & 1) * 32 + i + 1]) + cc);
+              sum += p0 + p1;
+              u[i >> 1] = pack_bf16(p0, p1);
+            }
+            tmem_st_32x32_16(tS + c * 16, u);
+          }
+        }
+        l += sum;
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_full[t]);
+        bh0 = nb0 * kLog2e;
+        bh1 = nb1 * kLog2e;
+      }
+      // ---- epilogue: O / l -> bf16
+      mbar_wait(&o_full[t], it & 1);
+      tc_fence_after();
+      const float inv = 1.f / l;
+      __nv_bfloat16* go = out + ((long)b * kGT + qrow) * ldo + head * HD;
+      {
+        uint32_t v[32];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          tmem_ld_32x32(tO + c * 32, v);
+          tmem_wait_ld();
+          uint4* o4 = reinterpret_cast<uint4*>(go + c * 32);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            uint4 x;
+            x.x = pack_bf16(__uint_as_float(v[8 * i + 0]) * inv, __uint_as_float(v[8 * i + 1]) * inv);
+            x.y = pack_bf16(__uint_as_float(v[8 * i + 2]) * inv, __uint_as_float(v[8 * i + 3]) * inv);
+            x.z = pack_bf16(__uint_as_float(v[8 * i + 4]) * inv, __uint_as_float(v[8 * i + 5]) * inv);
+            x.w = pack_bf16(__uint_as_float(v[8 * i + 6]) * inv, __uint_as_float(v[8 * i + 7]) * inv);
+            o4[i] = x;
+          }
+        }
+        if (kHasRem) {
+          uint32_t w[16];
+          tmem_ld_32x32_16(tO + 64, w);
+          tmem_wait_ld();
+          uint4* o4 = reinterpret_cast<uint4*>(go + 64);
+#pragma unroll
+          for (int i = 0; i < 2; ++i) {
+            uint4 x;
+            x.x = pack_bf16(__uint_as_float(w[8 * i + 0]) * inv, __uint_as_float(w[8 * i + 1]) * inv);
+            x.y = pack_bf16(__uint_as_float(w[8 * i + 2]) * inv, __uint_as_float(w[8 * i + 3]) * inv);
+            x.z = pack_bf16(__uint_as_float(w[8 * i + 4]) * inv, __uint_as_float(w[8 * i + 5]) * inv);
+            x.w = pack_bf16(__uint_as_float(w[8 * i + 6]) * inv, __uint_as_float(w[8 * i + 7]) * inv);
+            o4[i] = x;
+          }
+        }
+      }
+      tc_fence_before();   // orders these TMEM reads before the next item's p_full arrive -> PV(0) overwrite
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
+template <int HD>
+cudaError_t launch_global(const __nv_bfloat16* qkv, int nbatch, int heads, const __half* G, __nv_bfloat16* out,
+                          cudaStream_t s) {
+  using C = GlbCfg<HD>;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(attn_global_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
+    if (e != cudaSuccess) return e;
+    attr = true;
+  }
+  const long rows = (long)nbatch * kGT, cols = 3L * heads * HD;
+  CUtensorMap tm128, tm32;
+  cudaError_t e = make_tmap_2d(&tm128, qkv, 2, rows, cols, cols, 64, 128, 128);
+  if (e != cudaSuccess) return e;
+  if (C::kRem) {
+    e = make_tmap_2d(&tm32, qkv, 2, rows, cols, cols, 16, 128, 32);
+    if (e != cudaSuccess) return e;
+  } else {
+    tm32 = tm128;
+  }
+  const int nitems = nbatch * heads * kQBlocks;
+  const int grid = nitems < gemm_num_sms() ? nitems : gemm_num_sms();
+  attn_global_tc_kernel<HD><<<grid, kThreadsG, C::kSmem, s>>>(tm128, tm32, G, out, nbatch, heads,
+                                                            1.0f / sqrtf((float)HD));
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+// qkv: (nbatch*4096, 3*heads*hd) bf16; G: (nbatch*4096, heads*256) fp16 = per head [q.Rh[0..126], 0, q.Rw[0..126], 0].
+cudaError_t launch_attention_global_tc(const __nv_bfloat16* qkv, int nbatch, int heads, int hd, const __half* G,
+                                       __nv_bfloat16* out, cudaStream_t s) {
+  if (nbatch <= 0) return cudaSuccess;
+  if (hd == 80) return launch_global<80>(qkv, nbatch, heads, G, out, s);
+  if (hd == 64) return launch_global<64>(qkv, nbatch, heads, G, out, s);
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace bsam

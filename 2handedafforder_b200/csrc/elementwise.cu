@@ -197,6 +197,20 @@ __global__ void relpos_pack_kernel(const float* __restrict__ rel, int nrows, int
   out[i] = __float2bfloat16(r < nrows ? rel[i] : 0.f);
 }
 
+// (256, 128) bf16: rows 0..126 = rel_pos_h, 128..254 = rel_pos_w, everything else (incl. columns >= hd) zero
+__global__ void relpos_pack_g_kernel(const float* __restrict__ rel_h, const float* __restrict__ rel_w, int hd,
+                                     __nv_bfloat16* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 256 * 128) return;
+  int r = i >> 7, c = i & 127;
+  float v = 0.f;
+  if (c < hd) {
+    if (r < 127) v = rel_h[r * hd + c];
+    else if (r >= 128 && r < 255) v = rel_w[(r - 128) * hd + c];
+  }
+  out[i] = __float2bfloat16(v);
+}
+
 }  // namespace
 
 cudaError_t launch_layernorm_bf16(const float* x, long rows, int D, const float* g, const float* b, float eps,
@@ -284,6 +298,11 @@ cudaError_t launch_keys_init(const float* emb_tok, const float* no_mask, const i
 cudaError_t launch_relpos_pack(const float* rel, int S, int hd, __nv_bfloat16* out, cudaStream_t s) {
   const int RP = (S == 14) ? 32 : 128;
   relpos_pack_kernel<<<(RP * hd + 255) / 256, 256, 0, s>>>(rel, 2 * S - 1, hd, RP, out);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_relpos_pack_g(const float* rel_h, const float* rel_w, int hd, __nv_bfloat16* out, cudaStream_t s) {
+  relpos_pack_g_kernel<<<(256 * 128 + 255) / 256, 256, 0, s>>>(rel_h, rel_w, hd, out);
   return cudaGetLastError();
 }
 

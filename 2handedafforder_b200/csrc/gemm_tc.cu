@@ -121,7 +121,8 @@ __device__ __forceinline__ void store_bf16x32(__nv_bfloat16* o, const float (&v)
 // One output row (row of the 128-row tile owned by this thread), columns [n0, n0 + BN).
 // `src.load` is warp-collective for the TMEM source: every lane must call it the same number of times.
 template <int MODE, int BN, class Src>
-__device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, long row, int M, int N, int n0) {
+__device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, long row, int M, int N, int n0,
+                                             long out_off = 0) {
   const bool row_in = row < M;
   const int ncols = min(BN, N - n0);
   const int nchunks = ncols / 32;
@@ -138,6 +139,25 @@ __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, l
           for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
         }
         store_bf16x32(o + c * 32, v);
+      }
+    }
+  } else if constexpr (MODE == GM_F16) {
+    __half* o = reinterpret_cast<__half*>(e.out) + row * (long)e.ld_out + n0 + out_off;
+    for (int c = 0; c < nchunks; ++c) {
+      src.load(c, v);
+      if (row_in) {
+        uint4* o4 = reinterpret_cast<uint4*>(o + c * 32);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 t;
+          __half2 h0 = __floats2half2_rn(v[8 * j + 0], v[8 * j + 1]), h1 = __floats2half2_rn(v[8 * j + 2], v[8 * j + 3]);
+          __half2 h2 = __floats2half2_rn(v[8 * j + 4], v[8 * j + 5]), h3 = __floats2half2_rn(v[8 * j + 6], v[8 * j + 7]);
+          t.x = *reinterpret_cast<uint32_t*>(&h0);
+          t.y = *reinterpret_cast<uint32_t*>(&h1);
+          t.z = *reinterpret_cast<uint32_t*>(&h2);
+          t.w = *reinterpret_cast<uint32_t*>(&h3);
+          o4[j] = t;
+        }
       }
     }
   } else if constexpr (MODE == GM_F32) {
@@ -278,7 +298,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int lane = threadIdx.x & 31;
   const int m_tiles = (M + kBM - 1) / kBM;
   const int n_tiles = (N + BN - 1) / BN;
-  const int num_tiles = m_tiles * n_tiles;
+  const int tiles_per_batch = m_tiles * n_tiles;
+  const int num_tiles = tiles_per_batch * e.batch;
   const int kblocks = (K + kBK - 1) / kBK;
 
   if (warp == 0 && lane == 0) {
@@ -307,13 +328,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+        const int bidx = tile / tiles_per_batch, trem = tile - bidx * tiles_per_batch;
+        const int m_blk = trem / n_tiles, n_blk = trem % n_tiles;
+        const int a_col0 = bidx * e.a_batch_off;
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sA = smem + stage * Cfg::kStageBytes;
           uint8_t* sB = sA + kBM * 128;
           mbar_expect_tx(&full[stage], Cfg::kStageBytes);
-          tma_load_2d(sA, &tmA, &full[stage], kb * kBK, m_blk * kBM);
+          tma_load_2d(sA, &tmA, &full[stage], a_col0 + kb * kBK, m_blk * kBM);
           tma_load_2d(sB, &tmB, &full[stage], kb * kBK, n_blk * BN);
           if (++stage == kStages) {
             stage = 0;
@@ -356,14 +379,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int ew = warp & 3;              // TMEM lane quadrant this warp may access
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+      const int bidx = tile / tiles_per_batch, trem = tile - bidx * tiles_per_batch;
+      const int m_blk = trem / n_tiles, n_blk = trem % n_tiles;
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
       mbar_wait(&tmem_full[as], aph);
       tc_fence_after();
       TmemSrc src{tmem_base + (uint32_t(ew * 32) << 16) + uint32_t(as * BN)};
       const long row = (long)m_blk * kBM + ew * 32 + lane;
-      epilogue_row<MODE, BN>(e, src, row, M, N, n_blk * BN);
+      epilogue_row<MODE, BN>(e, src, row, M, N, n_blk * BN, (long)bidx * e.out_batch_off);
       tc_fence_before();
       mbar_arrive(&tmem_empty[as]);
     }
@@ -420,11 +444,11 @@ cudaError_t launch(const void* A, int lda, const void* W, int ldw, int M, int N,
     attr_set = true;
   }
   CUtensorMap tmA, tmB;
-  cudaError_t err = make_tmap(&tmA, A, kTf32, M, K, lda, kBM);
+  cudaError_t err = make_tmap(&tmA, A, kTf32, M, e.batch > 1 ? lda : K, lda, kBM);
   if (err != cudaSuccess) return err;
   err = make_tmap(&tmB, W, kTf32, N, K, ldw, BN);
   if (err != cudaSuccess) return err;
-  const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN);
+  const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * e.batch;
   const int grid = tiles < g_num_sms ? tiles : g_num_sms;
   gemm_tc_kernel<kTf32, MODE, BN><<<grid, kThreads, TileCfg<BN>::kSmemBytes, stream>>>(tmA, tmB, M, N, K, e);
   return cudaGetLastError();
@@ -471,6 +495,7 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
                     const GemmEpi& e, cudaStream_t s, bool dbg) {
   if (!g_encode && !dbg) return cudaErrorInitializationError;
   if (N % 32 != 0 || K % 8 != 0) return cudaErrorInvalidValue;
+  if (e.batch != 1 && (mode != GM_F16 || tf32 || dbg || e.batch < 1)) return cudaErrorInvalidValue;
   if ((mode == GM_LN || mode == GM_UPS1) && N != 256) return cudaErrorInvalidValue;
   if (mode == GM_UPS2 && N != 128) return cudaErrorInvalidValue;
   if (!tf32) {
@@ -479,6 +504,7 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
       case GM_BIAS_GELU_BF16: return launch<false, GM_BIAS_GELU_BF16, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
       case GM_F32: return launch<false, GM_F32, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
       case GM_LN: return launch<false, GM_LN, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
+      case GM_F16: return launch<false, GM_F16, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
       default: return cudaErrorInvalidValue;
     }
   }

@@ -14,6 +14,7 @@ enum GemmMode : int {
   GM_LN = 3,              // N == 256: y = LayerNorm_n(acc (+bias) (+addend[m])) * g + b -> out_f32 and/or out2_bf16
   GM_UPS1 = 4,            // N == 256 = 4 x 64: per 64-group LN (eps) -> GELU -> pixel-shuffle store (ConvT k2 s2)
   GM_UPS2 = 5,            // N == 128 = 4 x 32: GELU -> dot with hyper[p, 0:32] -> pixel-shuffle store of the mask logit
+  GM_F16 = 6,             // out_f16[m, n] = acc (batched over column slices of A: rel-pos projections of every head)
 };
 
 enum RowMap : int {
@@ -34,6 +35,12 @@ struct GemmEpi {
   const float* ln_b = nullptr;
   float ln_eps = 0.f;
   const float* hyper = nullptr;   // GM_UPS2: (P, 32) mask-0 hypernetwork vector per prompt
+  // GM_F16 only: `batch` independent products sharing W; batch b reads A columns [b*a_batch_off, b*a_batch_off + K)
+  // (the A tensor map then spans the full lda-wide rows, so W must be zero in any K padding) and writes output
+  // columns [b*out_batch_off, b*out_batch_off + N).
+  int batch = 1;
+  int a_batch_off = 0;
+  int out_batch_off = 0;
 };
 
 // A: (M, K) row-major with leading dimension lda (elements); W: (N, K) row-major, ldw.

@@ -22,15 +22,20 @@ cudaError_t launch_keys_init(const float* emb_tok, const float* no_mask, const i
                              cudaStream_t s);
 // rel-pos table (2S-1, hd) f32 -> bf16 padded to RP rows (32 for S=14, 128 for S=64), extra rows zero
 cudaError_t launch_relpos_pack(const float* rel, int S, int hd, __nv_bfloat16* out, cudaStream_t s);
+cudaError_t launch_relpos_pack_g(const float* rel_h, const float* rel_w, int hd, __nv_bfloat16* out, cudaStream_t s);
 
 // ---- attn.cu
 // qkv: (nbatch*S*S, 3*heads*hd) bf16 packed [q | k | v] per row, heads-major inside each; out (rows, heads*hd).
 // relh/relw: bf16 tables from launch_relpos_pack.
+// S == 64 additionally needs relg = (256, 128) bf16 [rel_pos_h (127 rows) ; 0 ; rel_pos_w (127 rows) ; 0], columns
+// >= hd zero (launch_relpos_pack_g), and gbuf = (nbatch*4096, heads*256) fp16 scratch for the bias projections.
 cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int heads, int hd,
-                             const __nv_bfloat16* relh, const __nv_bfloat16* relw, __nv_bfloat16* out,
-                             cudaStream_t s);
+                             const __nv_bfloat16* relh, const __nv_bfloat16* relw, const __nv_bfloat16* relg,
+                             void* gbuf, __nv_bfloat16* out, cudaStream_t s);
 cudaError_t attention_init();
 // ---- attn_tc.cu (tcgen05): windowed attention; rel = (64, hd) bf16 [rel_pos_h padded to 32 rows; rel_pos_w padded]
+cudaError_t launch_attention_global_tc(const __nv_bfloat16* qkv, int nbatch, int heads, int hd, const __half* G,
+                                       __nv_bfloat16* out, cudaStream_t s);
 cudaError_t launch_attention_window_tc(const __nv_bfloat16* qkv, int nwin, int heads, int hd, const __nv_bfloat16* rel,
                                        __nv_bfloat16* out, cudaStream_t s);
 

@@ -25,6 +25,7 @@ struct EncBlock {
   const float *qkv_b, *proj_b, *lin1_b, *lin2_b;
   __nv_bfloat16 *qkv_w, *proj_w, *lin1_w, *lin2_w;
   __nv_bfloat16 *relh, *relw;       // padded bf16 rel-pos tables
+  __nv_bfloat16* relg = nullptr;    // global blocks: (256, 128) stacked + zero padded tables (B operand of the G GEMM)
 };
 
 // transformer.Attention weights (transformer.py:185-218), fp32 device pointers into the masters
@@ -105,6 +106,7 @@ struct b200sam {
   __nv_bfloat16* ln_plain = nullptr; // (B*4096, D)
   __nv_bfloat16* qkv = nullptr;      // (B*4900, 3D)
   __nv_bfloat16* attn_o = nullptr;   // (B*4900, D)
+  void* gbuf = nullptr;              // (B*4096, heads*256) fp16 rel-pos projections of the global blocks
   __nv_bfloat16* hid = nullptr;      // (B*4096, 4D) MLP hidden; also im2col scratch
   float* emb_tok = nullptr;          // (B*4096, 256) fp32 image embedding, token-major
   // decoder workspace
