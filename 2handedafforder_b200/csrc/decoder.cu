@@ -6,7 +6,11 @@
 // memory; weights stream from L2 with 16-byte loads, one warp per output feature and warp-shuffle reductions.
 #include "decoder.cuh"
 
+#include <cooperative_groups.h>
+
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace bsam {
 
@@ -70,11 +74,85 @@ __device__ void block_add_ln(float* xs, const float* res, const float* __restric
   }
 }
 
+// ------------------------------------------------------------------------------------------------ cluster helpers
+// The token side is 6 rows per prompt: far too little work for one CTA per prompt to hide the latency of streaming
+// ~6 MB of fp32 weights.  Each prompt is therefore handled by a thread-block cluster of 8 CTAs: every CTA keeps the
+// full token state in its own shared memory, computes 1/8 of the output features of each Linear and all-gathers
+// its slice into the shared memory of all 8 CTAs through distributed shared memory; cheap steps (6x6 attention,
+// LayerNorm) are recomputed redundantly instead of synchronised.
+constexpr int kCl = 8;
+
+// Features [rank*OUT/8, (rank+1)*OUT/8) of y = act(x W^T + b) for R rows; x in local smem; the slice is written to
+// `ys` (same smem offset) in every CTA of the cluster.  Caller must cluster.sync() before anyone reads ys.
+template <int R>
+__device__ void cl_linear(cg::cluster_group& cl, const float* __restrict__ xs, int IN, const float* __restrict__ W,
+                          const float* __restrict__ b, int OUT, float* ys, int ldy, bool relu) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int per = OUT / kCl, o_lo = (int)cl.block_rank() * per;
+  float* dst = cl.map_shared_rank(ys, lane & (kCl - 1));
+  for (int o = o_lo + warp; o < o_lo + per; o += nw) {
+    const float4* wr = reinterpret_cast<const float4*>(W + (long)o * IN);
+    float acc[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r] = 0.f;
+    for (int i = lane; i < IN / 4; i += 32) {
+      const float4 wv = __ldg(wr + i);
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const float4 xv = *reinterpret_cast<const float4*>(xs + r * IN + 4 * i);
+        acc[r] += wv.x * xv.x + wv.y * xv.y + wv.z * xv.z + wv.w * xv.w;
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r] = warp_sum(acc[r]);
+    if (lane < kCl) {
+      const float bb = b ? __ldg(b + o) : 0.f;
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const float v = acc[r] + bb;
+        dst[r * ldy + o] = relu ? fmaxf(v, 0.f) : v;
+      }
+    }
+  }
+}
+
+// Same split, result straight to global memory (row stride ldy).
+template <int R>
+__device__ void cl_linear_global(cg::cluster_group& cl, const float* __restrict__ xs, int IN,
+                                 const float* __restrict__ W, const float* __restrict__ b, int OUT,
+                                 float* __restrict__ yg, int ldy) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int per = (OUT + kCl - 1) / kCl, o_lo = (int)cl.block_rank() * per;
+  const int o_hi = min(OUT, o_lo + per);
+  for (int o = o_lo + warp; o < o_hi; o += nw) {
+    const float4* wr = reinterpret_cast<const float4*>(W + (long)o * IN);
+    float acc[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r] = 0.f;
+    for (int i = lane; i < IN / 4; i += 32) {
+      const float4 wv = __ldg(wr + i);
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const float4 xv = *reinterpret_cast<const float4*>(xs + r * IN + 4 * i);
+        acc[r] += wv.x * xv.x + wv.y * xv.y + wv.z * xv.z + wv.w * xv.w;
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) acc[r] = warp_sum(acc[r]);
+    if (lane == 0) {
+      const float bb = b ? __ldg(b + o) : 0.f;
+#pragma unroll
+      for (int r = 0; r < R; ++r) yg[r * ldy + o] = acc[r] + bb;
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ stage A
 // Builds the tokens (layer 0), token self-attention + norm1, and the token->image query projection.
 // transformer.py:153-167 (layer 0 REPLACES the queries and uses no PE; later layers add), mask_decoder.py:131-138.
-__global__ void __launch_bounds__(kThreadsTok)
+__global__ void __cluster_dims__(kCl, 1, 1) __launch_bounds__(kThreadsTok)
 dec_stage_a_kernel(TokStageA a) {
+  cg::cluster_group cl = cg::this_cluster();
   extern __shared__ __align__(16) float sm[];
   float* sQ = sm;                  // (6,256) queries
   float* sT = sQ + kTok * kC;      // (6,256) token PE (initial tokens)
@@ -83,7 +161,9 @@ dec_stage_a_kernel(TokStageA a) {
   float* sk = sq + kTok * kC;
   float* sv = sk + kTok * kC;
   float* sA = sv + kTok * kC;      // (6,256) attention output
-  const int p = blockIdx.x, tid = threadIdx.x;
+  float* sY = sA + kTok * kC;      // (6,256) out_proj result
+  const int p = blockIdx.x / kCl, tid = threadIdx.x;
+  const bool lead = cl.block_rank() == 0;
   float* gQ = a.tok_state + (long)p * kTok * kC;
   float* gT = a.tok_pe + (long)p * kTok * kC;
 
@@ -94,7 +174,7 @@ dec_stage_a_kernel(TokStageA a) {
       sT[i] = v;
       sQ[i] = v;
       sX[i] = v;
-      gT[i] = v;
+      if (lead) gT[i] = v;
     }
   } else {
     for (int i = tid; i < kTok * kC; i += kThreadsTok) {
@@ -103,12 +183,12 @@ dec_stage_a_kernel(TokStageA a) {
       sX[i] = sQ[i] + sT[i];
     }
   }
-  __syncthreads();
-  block_linear<kTok>(sX, kC, a.sa.qw, a.sa.qb, kC, sq, kC, false);
-  block_linear<kTok>(sX, kC, a.sa.kw, a.sa.kb, kC, sk, kC, false);
-  block_linear<kTok>(sQ, kC, a.sa.vw, a.sa.vb, kC, sv, kC, false);   // v = queries (no PE), transformer.py:160
-  __syncthreads();
-  // 8 heads x 32, 6x6 scores: one thread per (head, query)
+  cl.sync();                       // every CTA of the cluster is running; local tiles are complete
+  cl_linear<kTok>(cl, sX, kC, a.sa.qw, a.sa.qb, kC, sq, kC, false);
+  cl_linear<kTok>(cl, sX, kC, a.sa.kw, a.sa.kb, kC, sk, kC, false);
+  cl_linear<kTok>(cl, sQ, kC, a.sa.vw, a.sa.vb, kC, sv, kC, false);   // v = queries (no PE), transformer.py:160
+  cl.sync();
+  // 8 heads x 32, 6x6 scores: one thread per (head, query); recomputed by every CTA
   if (tid < 8 * kTok) {
     const int h = tid / kTok, qi = tid % kTok;
     float s[kTok], mx = -INFINITY;
@@ -130,16 +210,16 @@ dec_stage_a_kernel(TokStageA a) {
     }
   }
   __syncthreads();
-  block_linear<kTok>(sA, kC, a.sa.ow, a.sa.ob, kC, sX, kC, false);    // attn_out -> sX
-  __syncthreads();
-  block_add_ln(sX, a.layer == 0 ? nullptr : sQ, a.n1g, a.n1b, kTok);   // queries = norm1(attn_out (+ queries))
+  cl_linear<kTok>(cl, sA, kC, a.sa.ow, a.sa.ob, kC, sY, kC, false);
+  cl.sync();
+  block_add_ln(sY, a.layer == 0 ? nullptr : sQ, a.n1g, a.n1b, kTok);   // queries = norm1(attn_out (+ queries))
   __syncthreads();
   for (int i = tid; i < kTok * kC; i += kThreadsTok) {
-    gQ[i] = sX[i];
-    sQ[i] = sX[i] + sT[i];                                             // q = queries + query_pe
+    if (lead) gQ[i] = sY[i];
+    sX[i] = sY[i] + sT[i];                                             // q = queries + query_pe
   }
   __syncthreads();
-  block_linear<kTok>(sQ, kC, a.t2i_qw, a.t2i_qb, 128, a.tok_q + (long)p * kTok * 128, 128, false);
+  cl_linear_global<kTok>(cl, sX, kC, a.t2i_qw, a.t2i_qb, 128, a.tok_q + (long)p * kTok * 128, 128);
 }
 
 // Only the q projection (final_attn_token_to_image, transformer.py:100-102).
@@ -229,41 +309,44 @@ dec_t2i_attn_kernel(const float* __restrict__ tok_q, const float* __restrict__ k
 
 // ------------------------------------------------------------------------------------------------ stage B
 // out_proj of the token->image attention + norm2, MLP (ReLU) + norm3, and the token k/v projections for the
-// image->token attention (transformer.py:163-181).
-__global__ void __launch_bounds__(kThreadsTok)
+// image->token attention (transformer.py:163-181).  Cluster of 8 CTAs per prompt (see cl_linear).
+__global__ void __cluster_dims__(kCl, 1, 1) __launch_bounds__(kThreadsTok)
 dec_stage_b_kernel(TokStageB a) {
+  cg::cluster_group cl = cg::this_cluster();
   extern __shared__ __align__(16) float sm[];
-  float* sQ = sm;                    // (6,256)
-  float* sT = sQ + kTok * kC;        // (6,256)
+  float* sQ = sm;                    // (6,256) queries, later queries + pe
+  float* sT = sQ + kTok * kC;        // (6,256) token pe
   float* sO = sT + kTok * kC;        // (6,128) attention output
-  float* sX = sO + kTok * 128;       // (6,256) scratch
-  float* sH = sX + kTok * kC;        // (6,2048) MLP hidden
-  const int p = blockIdx.x, tid = threadIdx.x;
+  float* sX = sO + kTok * 128;       // (6,256) out_proj -> norm2 output
+  float* sY = sX + kTok * kC;        // (6,256) mlp output -> norm3 output
+  float* sH = sY + kTok * kC;        // (6,2048) MLP hidden
+  const int p = blockIdx.x / kCl, tid = threadIdx.x;
+  const bool lead = cl.block_rank() == 0;
   float* gQ = a.tok_state + (long)p * kTok * kC;
   for (int i = tid; i < kTok * kC; i += kThreadsTok) {
     sQ[i] = gQ[i];
     sT[i] = a.tok_pe[(long)p * kTok * kC + i];
   }
   for (int i = tid; i < kTok * 128; i += kThreadsTok) sO[i] = a.tok_o[(long)p * kTok * 128 + i];
-  __syncthreads();
-  block_linear<kTok>(sO, 128, a.t2i_ow, a.t2i_ob, kC, sX, kC, false);
-  __syncthreads();
+  cl.sync();
+  cl_linear<kTok>(cl, sO, 128, a.t2i_ow, a.t2i_ob, kC, sX, kC, false);
+  cl.sync();
   block_add_ln(sX, sQ, a.n2g, a.n2b, kTok);          // queries = norm2(queries + attn_out)
   __syncthreads();
-  block_linear<kTok>(sX, kC, a.mlp1w, a.mlp1b, 2048, sH, 2048, true);
-  __syncthreads();
-  block_linear<kTok>(sH, 2048, a.mlp2w, a.mlp2b, kC, sQ, kC, false);
-  __syncthreads();
-  block_add_ln(sQ, sX, a.n3g, a.n3b, kTok);          // queries = norm3(queries + mlp_out)
+  cl_linear<kTok>(cl, sX, kC, a.mlp1w, a.mlp1b, 2048, sH, 2048, true);
+  cl.sync();
+  cl_linear<kTok>(cl, sH, 2048, a.mlp2w, a.mlp2b, kC, sY, kC, false);
+  cl.sync();
+  block_add_ln(sY, sX, a.n3g, a.n3b, kTok);          // queries = norm3(queries + mlp_out)
   __syncthreads();
   for (int i = tid; i < kTok * kC; i += kThreadsTok) {
-    gQ[i] = sQ[i];
-    sX[i] = sQ[i] + sT[i];                           // k input = queries + query_pe
+    if (lead) gQ[i] = sY[i];
+    sQ[i] = sY[i] + sT[i];                           // k input = queries + query_pe
   }
   __syncthreads();
   float* gkv = a.tok_kv + (long)p * kTok * 256;
-  block_linear<kTok>(sX, kC, a.i2t_kw, a.i2t_kb, 128, gkv, 256, false);
-  block_linear<kTok>(sQ, kC, a.i2t_vw, a.i2t_vb, 128, gkv + 128, 256, false);
+  cl_linear_global<kTok>(cl, sQ, kC, a.i2t_kw, a.i2t_kb, 128, gkv, 256);
+  cl_linear_global<kTok>(cl, sY, kC, a.i2t_vw, a.i2t_vb, 128, gkv + 128, 256);
 }
 
 // ------------------------------------------------------------------------------------------------ image -> token attention
@@ -316,48 +399,45 @@ dec_i2t_attn_kernel(const float* __restrict__ qimg, const float* __restrict__ to
 
 // ------------------------------------------------------------------------------------------------ heads
 // Final attention out_proj + norm_final_attn, hypernetwork MLP of mask token 0, IoU head, taxonomy head
-// (transformer.py:100-104, mask_decoder.py:150-178).
-__global__ void __launch_bounds__(kThreadsTok)
+// (transformer.py:100-104, mask_decoder.py:150-178).  Cluster of 8 CTAs per prompt; the three MLPs advance layer by
+// layer together so there is one cluster barrier per layer.
+__global__ void __cluster_dims__(kCl, 1, 1) __launch_bounds__(kThreadsTok)
 dec_heads_kernel(TokHeads a) {
+  cg::cluster_group cl = cg::this_cluster();
   extern __shared__ __align__(16) float sm[];
   float* sQ = sm;                  // (6,256)
   float* sO = sQ + kTok * kC;      // (6,128)
   float* sX = sO + kTok * 128;     // (6,256)
-  float* sA = sX + kTok * kC;      // 1024
-  float* sB = sA + 1024;           // 1024
-  const int p = blockIdx.x, tid = threadIdx.x;
+  float* sA = sX + kTok * kC;      // 256 hyper | 256 iou | 1024 taxonomy
+  float* sB = sA + 1536;           // same split
+  float* sC = sB + 1536;           // 4 taxonomy logits
+  const int p = blockIdx.x / kCl, tid = threadIdx.x;
+  const bool tax = a.tax_w[0] != nullptr && a.tax_out != nullptr;
   for (int i = tid; i < kTok * kC; i += kThreadsTok) sQ[i] = a.tok_state[(long)p * kTok * kC + i];
   for (int i = tid; i < kTok * 128; i += kThreadsTok) sO[i] = a.tok_o[(long)p * kTok * 128 + i];
-  __syncthreads();
-  block_linear<kTok>(sO, 128, a.ow, a.ob, kC, sX, kC, false);
-  __syncthreads();
+  cl.sync();
+  cl_linear<kTok>(cl, sO, 128, a.ow, a.ob, kC, sX, kC, false);
+  cl.sync();
   block_add_ln(sX, sQ, a.nfg, a.nfb, kTok);          // hs = norm_final_attn(queries + attn_out)
   __syncthreads();
-  // hypernetwork MLP 0 on mask token 0 (row 1): 256 -> 256 -> 256 -> 32, ReLU
-  block_linear<1>(sX + 1 * kC, kC, a.hyp_w[0], a.hyp_b[0], 256, sA, 256, true);
-  __syncthreads();
-  block_linear<1>(sA, kC, a.hyp_w[1], a.hyp_b[1], 256, sB, 256, true);
-  __syncthreads();
-  block_linear<1>(sB, kC, a.hyp_w[2], a.hyp_b[2], 32, a.hyper + (long)p * 32, 32, false);
-  __syncthreads();
-  // IoU head on the iou token (row 0): 256 -> 256 -> 256 -> 4
-  block_linear<1>(sX, kC, a.iou_w[0], a.iou_b[0], 256, sA, 256, true);
-  __syncthreads();
-  block_linear<1>(sA, kC, a.iou_w[1], a.iou_b[1], 256, sB, 256, true);
-  __syncthreads();
-  if (a.iou_out) block_linear<1>(sB, kC, a.iou_w[2], a.iou_b[2], 4, a.iou_out + (long)p * 4, 4, false);
-  __syncthreads();
-  if (a.tax_w[0] != nullptr && a.tax_out != nullptr) {
-    // taxonomy: mask_tokens_out.flatten(1) (rows 1..4 are contiguous = 1024) -> 1024 -> 1024 -> 4 -> softmax
-    block_linear<1>(sX + 1 * kC, 1024, a.tax_w[0], a.tax_b[0], 1024, sA, 1024, true);
-    __syncthreads();
-    block_linear<1>(sA, 1024, a.tax_w[1], a.tax_b[1], 1024, sB, 1024, true);
-    __syncthreads();
-    block_linear<1>(sB, 1024, a.tax_w[2], a.tax_b[2], 4, sA, 4, false);
+  // layer 1: hypernetwork MLP 0 on mask token 0 (row 1), IoU head on the iou token (row 0), taxonomy on
+  // mask_tokens_out.flatten(1) (rows 1..4 are contiguous = 1024)
+  cl_linear<1>(cl, sX + 1 * kC, kC, a.hyp_w[0], a.hyp_b[0], 256, sA, 256, true);
+  cl_linear<1>(cl, sX, kC, a.iou_w[0], a.iou_b[0], 256, sA + 256, 256, true);
+  if (tax) cl_linear<1>(cl, sX + 1 * kC, 1024, a.tax_w[0], a.tax_b[0], 1024, sA + 512, 1024, true);
+  cl.sync();
+  cl_linear<1>(cl, sA, kC, a.hyp_w[1], a.hyp_b[1], 256, sB, 256, true);
+  cl_linear<1>(cl, sA + 256, kC, a.iou_w[1], a.iou_b[1], 256, sB + 256, 256, true);
+  if (tax) cl_linear<1>(cl, sA + 512, 1024, a.tax_w[1], a.tax_b[1], 1024, sB + 512, 1024, true);
+  cl.sync();
+  cl_linear_global<1>(cl, sB, kC, a.hyp_w[2], a.hyp_b[2], 32, a.hyper + (long)p * 32, 32);
+  if (a.iou_out) cl_linear_global<1>(cl, sB + 256, kC, a.iou_w[2], a.iou_b[2], 4, a.iou_out + (long)p * 4, 4);
+  if (tax && cl.block_rank() == kCl - 1) {
+    block_linear<1>(sB + 512, 1024, a.tax_w[2], a.tax_b[2], 4, sC, 4, false);
     __syncthreads();
     if (tid == 0) {
-      float mx = fmaxf(fmaxf(sA[0], sA[1]), fmaxf(sA[2], sA[3]));
-      float e0 = expf(sA[0] - mx), e1 = expf(sA[1] - mx), e2 = expf(sA[2] - mx), e3 = expf(sA[3] - mx);
+      float mx = fmaxf(fmaxf(sC[0], sC[1]), fmaxf(sC[2], sC[3]));
+      float e0 = expf(sC[0] - mx), e1 = expf(sC[1] - mx), e2 = expf(sC[2] - mx), e3 = expf(sC[3] - mx);
       float inv = 1.f / (e0 + e1 + e2 + e3);
       float* o = a.tax_out + (long)p * 4;
       o[0] = e0 * inv; o[1] = e1 * inv; o[2] = e2 * inv; o[3] = e3 * inv;
@@ -365,9 +445,9 @@ dec_heads_kernel(TokHeads a) {
   }
 }
 
-constexpr int kSmemA = 7 * kTok * kC * 4;
-constexpr int kSmemB = (3 * kTok * kC + kTok * 128 + kTok * 2048) * 4;
-constexpr int kSmemH = (2 * kTok * kC + kTok * 128 + 2048) * 4;
+constexpr int kSmemA = 8 * kTok * kC * 4;
+constexpr int kSmemB = (4 * kTok * kC + kTok * 128 + kTok * 2048) * 4;
+constexpr int kSmemH = (2 * kTok * kC + kTok * 128 + 2 * 1536 + 16) * 4;
 
 }  // namespace
 
@@ -381,7 +461,7 @@ cudaError_t decoder_init() {
 
 cudaError_t launch_dec_stage_a(const TokStageA& a, int P, cudaStream_t s) {
   if (P <= 0) return cudaSuccess;
-  dec_stage_a_kernel<<<P, kThreadsTok, kSmemA, s>>>(a);
+  dec_stage_a_kernel<<<P * kCl, kThreadsTok, kSmemA, s>>>(a);
   return cudaGetLastError();
 }
 cudaError_t launch_dec_stage_q(const float* tok_state, const float* tok_pe, const float* qw, const float* qb,
@@ -397,7 +477,7 @@ cudaError_t launch_dec_t2i(const float* tok_q, const float* kv, float* tok_o, in
 }
 cudaError_t launch_dec_stage_b(const TokStageB& a, int P, cudaStream_t s) {
   if (P <= 0) return cudaSuccess;
-  dec_stage_b_kernel<<<P, kThreadsTok, kSmemB, s>>>(a);
+  dec_stage_b_kernel<<<P * kCl, kThreadsTok, kSmemB, s>>>(a);
   return cudaGetLastError();
 }
 cudaError_t launch_dec_i2t(const float* qimg, const float* tok_kv, float* oimg, int P, cudaStream_t s) {
@@ -407,7 +487,7 @@ cudaError_t launch_dec_i2t(const float* qimg, const float* tok_kv, float* oimg, 
 }
 cudaError_t launch_dec_heads(const TokHeads& a, int P, cudaStream_t s) {
   if (P <= 0) return cudaSuccess;
-  dec_heads_kernel<<<P, kThreadsTok, kSmemH, s>>>(a);
+  dec_heads_kernel<<<P * kCl, kThreadsTok, kSmemH, s>>>(a);
   return cudaGetLastError();
 }
 

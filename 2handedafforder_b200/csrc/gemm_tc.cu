@@ -29,7 +29,7 @@ namespace bsam {
 namespace {
 
 constexpr int kBM = 128;
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;   // warps 0-3: TMA / MMA / TMEM alloc / spare; warps 4-11: epilogue
 
 template <int BN>
 struct TileCfg {
@@ -120,30 +120,40 @@ __device__ __forceinline__ void store_bf16x32(__nv_bfloat16* o, const float (&v)
 
 // One output row (row of the 128-row tile owned by this thread), columns [n0, n0 + BN).
 // `src.load` is warp-collective for the TMEM source: every lane must call it the same number of times.
-template <int MODE, int BN, class Src>
+struct NoWait {
+  __device__ __forceinline__ void operator()() const {}
+};
+
+// `half`/`nhalves`: the 32-column chunks of the tile are split between `nhalves` warps that share a TMEM lane
+// quadrant (modes with a row-wise reduction over the tile keep nhalves == 1).  `wait_acc()` blocks until the
+// accumulator is complete; it is called after the first global prefetch so that load overlaps the main loop.
+template <int MODE, int BN, class Src, class Wait>
 __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, long row, int M, int N, int n0,
-                                             long out_off = 0) {
+                                             long out_off, int half, int nhalves, const Wait& wait_acc) {
   const bool row_in = row < M;
   const int ncols = min(BN, N - n0);
   const int nchunks = ncols / 32;
+  const int c_lo = (nchunks * half) / nhalves, c_hi = (nchunks * (half + 1)) / nhalves;
   float v[32];
 
   if constexpr (MODE == GM_BIAS_BF16 || MODE == GM_BIAS_GELU_BF16) {
     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + row * (long)e.ld_out + n0;
-    for (int c = 0; c < nchunks; ++c) {
+    wait_acc();
+    for (int c = c_lo; c < c_hi; ++c) {
       src.load(c, v);
       if (row_in) {
         add_vec32(v, e.bias + n0 + c * 32);
         if constexpr (MODE == GM_BIAS_GELU_BF16) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+          for (int j = 0; j < 32; ++j) v[j] = gelu_erf_fast(v[j]);
         }
         store_bf16x32(o + c * 32, v);
       }
     }
   } else if constexpr (MODE == GM_F16) {
     __half* o = reinterpret_cast<__half*>(e.out) + row * (long)e.ld_out + n0 + out_off;
-    for (int c = 0; c < nchunks; ++c) {
+    wait_acc();
+    for (int c = c_lo; c < c_hi; ++c) {
       src.load(c, v);
       if (row_in) {
         uint4* o4 = reinterpret_cast<uint4*>(o + c * 32);
@@ -178,11 +188,37 @@ __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, l
       long arow = e.add_mod > 0 ? (orow % e.add_mod) : orow;
       a = e.addend + arow * (long)e.ld_add + n0;
     }
-    for (int c = 0; c < nchunks; ++c) {
+    // the addend (residual stream) chunk is fetched one step ahead: its HBM/L2 latency overlaps the accumulator
+    // wait and the previous chunk's TMEM load.  The addend may alias the output; chunks are disjoint columns.
+    const bool pf = ok && a != nullptr;
+    float4 nxt[8];
+    if (pf && c_lo < c_hi) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) nxt[j] = reinterpret_cast<const float4*>(a + c_lo * 32)[j];
+    }
+    wait_acc();
+    for (int c = c_lo; c < c_hi; ++c) {
+      float4 cur[8];
+      if (pf) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) cur[j] = nxt[j];
+        if (c + 1 < c_hi) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) nxt[j] = reinterpret_cast<const float4*>(a + (c + 1) * 32)[j];
+        }
+      }
       src.load(c, v);
       if (ok) {
         if (e.bias) add_vec32(v, e.bias + n0 + c * 32);
-        if (a) add_vec32_plain(v, a + c * 32);
+        if (pf) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            v[4 * j + 0] += cur[j].x;
+            v[4 * j + 1] += cur[j].y;
+            v[4 * j + 2] += cur[j].z;
+            v[4 * j + 3] += cur[j].w;
+          }
+        }
         store_f32x32(o + c * 32, v);
       }
     }
@@ -190,6 +226,7 @@ __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, l
     // N == BN == 256; shifted single-pass statistics, then a second pass over TMEM to normalise.
     const float* a = e.addend ? e.addend + row * (long)e.ld_add : nullptr;
     float shift = 0.f, s1 = 0.f, s2 = 0.f;
+    wait_acc();
     for (int c = 0; c < 8; ++c) {
       src.load(c, v);
       if (row_in) {
@@ -227,6 +264,7 @@ __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, l
     int t = (int)(row - p * kTokens);
     int y = t / kGrid, x = t % kGrid;
     float w[32];
+    wait_acc();
     for (int g = 0; g < 4; ++g) {
       src.load(2 * g, v);
       src.load(2 * g + 1, w);
@@ -261,6 +299,7 @@ __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, l
     int t = (int)(row - p * 128 * 128);
     int y = t / 128, x = t % 128;
     const float* h = e.hyper + p * 32;
+    wait_acc();
     for (int g = 0; g < 4; ++g) {
       src.load(g, v);
       if (row_in) {
@@ -313,7 +352,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], 128);
+      mbar_init(&tmem_empty[s], 256);
     }
     mbar_fence_init();
   }
@@ -377,17 +416,26 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else if (warp >= 4) {
     const int ew = warp & 3;              // TMEM lane quadrant this warp may access
+    const int eh = (warp - 4) >> 2;       // which half of the tile's column chunks
+    constexpr bool kSplit = MODE == GM_BIAS_BF16 || MODE == GM_BIAS_GELU_BF16 || MODE == GM_F32 || MODE == GM_F16;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int bidx = tile / tiles_per_batch, trem = tile - bidx * tiles_per_batch;
       const int m_blk = trem / n_tiles, n_blk = trem % n_tiles;
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
-      mbar_wait(&tmem_full[as], aph);
-      tc_fence_after();
+      auto wait_acc = [&]() {
+        mbar_wait(&tmem_full[as], aph);
+        tc_fence_after();
+      };
       TmemSrc src{tmem_base + (uint32_t(ew * 32) << 16) + uint32_t(as * BN)};
       const long row = (long)m_blk * kBM + ew * 32 + lane;
-      epilogue_row<MODE, BN>(e, src, row, M, N, n_blk * BN, (long)bidx * e.out_batch_off);
+      if (kSplit)
+        epilogue_row<MODE, BN>(e, src, row, M, N, n_blk * BN, (long)bidx * e.out_batch_off, eh, 2, wait_acc);
+      else if (eh == 0)
+        epilogue_row<MODE, BN>(e, src, row, M, N, n_blk * BN, (long)bidx * e.out_batch_off, 0, 1, wait_acc);
+      else
+        wait_acc();
       tc_fence_before();
       mbar_arrive(&tmem_empty[as]);
     }
@@ -407,7 +455,7 @@ __global__ void gemm_simt_debug_kernel(const void* A, int lda, const void* W, in
   const long row = (long)blockIdx.x * kBM + threadIdx.x;
   const int n0 = blockIdx.y * BN;
   SimtSrc<kTf32> src{A, W, lda, ldw, K, N, n0, row, row < M};
-  epilogue_row<MODE, BN>(e, src, row, M, N, n0);
+  epilogue_row<MODE, BN>(e, src, row, M, N, n0, 0, 0, 1, NoWait());
 }
 
 PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
