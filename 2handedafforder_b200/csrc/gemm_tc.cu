@@ -21,6 +21,7 @@
 
 #include <cudaTypedefs.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -447,6 +448,134 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 2) tmem_dealloc(tmem_base, 2 * BN);
 }
 
+// ------------------------------------------------------------------------------------------------ CTA-pair kernel
+// Same contract for the four big encoder GEMMs (bf16 operands), computed by CTA pairs (cluster of 2, cta_group::2):
+// one 256 x 256 output tile per pair, each CTA stages its own 128 rows of A and 128 of the 256 rows of W (so every
+// operand byte is read from L2 once per pair instead of once per CTA, and the 32 KB stages allow a 6-deep ring), the
+// leader issues tcgen05.mma with M = 256 and each CTA drains its own 128 accumulator lanes.
+constexpr int kStages2 = 6;
+constexpr int kStageBytes2 = kBM * 128 + 128 * 128;   // A half + W half
+constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + 1024 + 256;
+
+template <int MODE>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
+                GemmEpi e) {
+  constexpr int BN = 256;
+  constexpr uint32_t kIdesc = umma_idesc_bf16(256, BN, false, false);
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages2 * kStageBytes2);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + kStages2;
+  uint64_t* tmem_full = bars + 2 * kStages2;
+  uint64_t* tmem_empty = bars + 2 * kStages2 + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages2 + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  const int m_tiles = (M + 255) / 256;
+  const int n_tiles = (N + BN - 1) / BN;
+  const int num_tiles = m_tiles * n_tiles;
+  const int kblocks = (K + 63) / 64;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages2; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 512);     // the epilogue threads of both CTAs arrive on the leader's barrier
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc_2cta(tmem_slot, 2 * BN);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = pair; tile < num_tiles; tile += npairs) {
+        const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sA = smem + stage * kStageBytes2;
+          uint8_t* sB = sA + kBM * 128;
+          if (rank == 0) mbar_expect_tx(&full[stage], 2 * kStageBytes2);
+          tma_load_2d_2cta(sA, &tmA, &full[stage], kb * 64, m_blk * 256 + (int)rank * 128);
+          tma_load_2d_2cta(sB, &tmB, &full[stage], kb * 64, n_blk * BN + (int)rank * 128);
+          if (++stage == kStages2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && rank == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int tile = pair; tile < num_tiles; tile += npairs, ++it) {
+        const int as = it & 1;
+        const uint32_t aph = (it >> 1) & 1;
+        mbar_wait(&tmem_empty[as], aph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a0 = smem_u32(smem + stage * kStageBytes2);
+          const uint32_t b0 = a0 + kBM * 128;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_ss_2cta(d_tmem, umma_desc_sw128(a0 + k * 32), umma_desc_sw128(b0 + k * 32), kIdesc,
+                         (kb | k) != 0 ? 1u : 0u);
+          umma_commit_2cta(&empty[stage], 3);      // frees the slot in both CTAs
+          if (++stage == kStages2) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit_2cta(&tmem_full[as], 3);
+      }
+    }
+  } else if (warp >= 4) {
+    const int ew = warp & 3;
+    const int eh = (warp - 4) >> 2;
+    int it = 0;
+    for (int tile = pair; tile < num_tiles; tile += npairs, ++it) {
+      const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+      const int as = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      auto wait_acc = [&]() {
+        mbar_wait(&tmem_full[as], aph);
+        tc_fence_after();
+      };
+      TmemSrc src{tmem_base + (uint32_t(ew * 32) << 16) + uint32_t(as * BN)};
+      const long row = (long)m_blk * 256 + rank * 128 + ew * 32 + lane;
+      epilogue_row<MODE, BN>(e, src, row, M, N, n_blk * BN, 0, eh, 2, wait_acc);
+      tc_fence_before();
+      mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[as]), 0));
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  if (warp == 2) tmem_dealloc_2cta(tmem_base, 2 * BN);
+}
+
 // Debug-only SIMT evaluation of the same contract (one thread per output row); selected explicitly by the
 // caller to bisect tcgen05/TMA problems.  Never used unless requested.
 template <bool kTf32, int MODE, int BN>
@@ -460,6 +589,7 @@ __global__ void gemm_simt_debug_kernel(const void* A, int lda, const void* W, in
 
 PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
 int g_num_sms = 148;
+bool g_pair_kernel = true;   // B200SAM_GEMM_PAIR=0 selects the single-CTA kernel (A/B measurements)
 
 cudaError_t make_tmap(CUtensorMap* tm, const void* ptr, bool f32, long rows, long cols, long ld, int box_rows) {
   const int esz = f32 ? 4 : 2;
@@ -502,6 +632,27 @@ cudaError_t launch(const void* A, int lda, const void* W, int ldw, int M, int N,
   return cudaGetLastError();
 }
 
+template <int MODE>
+cudaError_t launch2(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const GemmEpi& e,
+                    cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t err = cudaFuncSetAttribute(gemm_tc2_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2);
+    if (err != cudaSuccess) return err;
+    attr_set = true;
+  }
+  CUtensorMap tmA, tmB;
+  cudaError_t err = make_tmap(&tmA, A, false, M, K, lda, 128);
+  if (err != cudaSuccess) return err;
+  err = make_tmap(&tmB, W, false, N, K, ldw, 128);
+  if (err != cudaSuccess) return err;
+  const int tiles = ((M + 255) / 256) * ((N + 255) / 256);
+  int pairs = g_num_sms / 2;
+  if (tiles < pairs) pairs = tiles;
+  gemm_tc2_kernel<MODE><<<2 * pairs, kThreads, kSmemBytes2, stream>>>(tmA, tmB, M, N, K, e);
+  return cudaGetLastError();
+}
+
 }  // namespace
 
 cudaError_t gemm_tc_init(int device) {
@@ -516,6 +667,7 @@ cudaError_t gemm_tc_init(int device) {
   err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   if (err != cudaSuccess) return err;
   g_num_sms = sms;
+  if (const char* v = getenv("B200SAM_GEMM_PAIR")) g_pair_kernel = atoi(v) != 0;
   return cudaSuccess;
 }
 
@@ -546,6 +698,14 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
   if (e.batch != 1 && (mode != GM_F16 || tf32 || dbg || e.batch < 1)) return cudaErrorInvalidValue;
   if ((mode == GM_LN || mode == GM_UPS1) && N != 256) return cudaErrorInvalidValue;
   if (mode == GM_UPS2 && N != 128) return cudaErrorInvalidValue;
+  if (!tf32 && !dbg && e.batch == 1 && M >= 1024 && N % 256 == 0 && g_pair_kernel) {
+    switch (mode) {
+      case GM_BIAS_BF16: return launch2<GM_BIAS_BF16>(A, lda, W, ldw, M, N, K, e, s);
+      case GM_BIAS_GELU_BF16: return launch2<GM_BIAS_GELU_BF16>(A, lda, W, ldw, M, N, K, e, s);
+      case GM_F32: return launch2<GM_F32>(A, lda, W, ldw, M, N, K, e, s);
+      default: break;
+    }
+  }
   if (!tf32) {
     switch (mode) {
       case GM_BIAS_BF16: return launch<false, GM_BIAS_BF16, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
