@@ -36,7 +36,7 @@ template <int BN>
 struct TileCfg {
   static constexpr int kStageBytes = kBM * 128 + BN * 128;
   static constexpr int kStages = (BN == 256) ? 4 : 6;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + 32768 /*epilogue tiles*/;
 };
 
 struct TmemSrc {
@@ -315,6 +315,111 @@ __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, l
   }
 }
 
+// Warp-collective epilogue of the splittable modes (bias->bf16, bias+GELU->bf16, fp16, bias+addend->fp32) with
+// coalesced global traffic.  tcgen05.ld hands every lane one accumulator ROW (32 columns); storing that directly makes
+// each 16-byte store instruction touch 32 different 128-byte lines.  Instead each 32x32 chunk is transposed through a
+// private 4 KB shared-memory tile (XOR-swizzled float4 slots, conflict free both ways) so that 8 consecutive lanes
+// cover 128 contiguous bytes of one row and a load/store instruction touches 4 lines instead of 32.
+constexpr int kEpiStageBytes = 8 * 32 * 32 * 4;   // one 32x32 fp32 tile per epilogue warp
+
+template <int MODE, int BN, class Wait>
+__device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& src, long row0, int lane, int M, int N,
+                                              int n0, long out_off, int half, int nhalves, const Wait& wait_acc,
+                                              float4* stage) {
+  const int ncols = min(BN, N - n0);
+  const int nchunks = ncols / 32;
+  const int c_lo = (nchunks * half) / nhalves, c_hi = (nchunks * (half + 1)) / nhalves;
+  // output row of the accumulator row this lane owns (-1: nothing to store)
+  int orow_own;
+  {
+    const long row = row0 + lane;
+    bool ok = row < M;
+    long orow = row;
+    if (MODE == GM_F32 && e.rowmap == RM_WINDOW_TO_TOKEN) {
+      long b = row / kWinRowsPerFrame;
+      int rem = (int)(row - b * kWinRowsPerFrame);
+      int win = rem / kWinTokens, t = rem - win * kWinTokens;
+      int y = (win / kWinPerSide) * kWin + t / kWin;
+      int x = (win % kWinPerSide) * kWin + t % kWin;
+      ok = ok && (y < kGrid) && (x < kGrid);
+      orow = b * kTokens + y * kGrid + x;
+    }
+    orow_own = ok ? (int)orow : -1;
+  }
+  const int sub = lane >> 3, cg = lane & 7;     // transposed role: rows i*4 + sub (i < 8), columns cg*4 .. cg*4+3
+  int orow[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) orow[i] = __shfl_sync(0xffffffffu, orow_own, i * 4 + sub);
+
+  const bool has_add = MODE == GM_F32 && e.addend != nullptr;
+  float4 nxt[8];
+  auto fetch = [&](int c) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (orow[i] >= 0) {
+        const long arow = e.add_mod > 0 ? (orow[i] % e.add_mod) : orow[i];
+        nxt[i] = *reinterpret_cast<const float4*>(e.addend + arow * (long)e.ld_add + n0 + c * 32 + cg * 4);
+      }
+    }
+  };
+  if (has_add && c_lo < c_hi) fetch(c_lo);
+  wait_acc();
+  float v[32];
+  for (int c = c_lo; c < c_hi; ++c) {
+    float4 cur[8];
+    if (has_add) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) cur[i] = nxt[i];
+      if (c + 1 < c_hi) fetch(c + 1);
+    }
+    src.load(c, v);
+#pragma unroll
+    for (int g = 0; g < 8; ++g)
+      stage[lane * 8 + (g ^ (lane & 7))] = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+    __syncwarp();
+    float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (MODE != GM_F16 && e.bias) b4 = __ldg(reinterpret_cast<const float4*>(e.bias + n0 + c * 32 + cg * 4));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = i * 4 + sub;
+      float4 x = stage[r * 8 + (cg ^ (r & 7))];
+      x.x += b4.x;
+      x.y += b4.y;
+      x.z += b4.z;
+      x.w += b4.w;
+      if (orow[i] < 0) continue;
+      const long col = n0 + c * 32 + cg * 4;
+      if constexpr (MODE == GM_F32) {
+        if (has_add) {
+          x.x += cur[i].x;
+          x.y += cur[i].y;
+          x.z += cur[i].z;
+          x.w += cur[i].w;
+        }
+        *reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + orow[i] * (long)e.ld_out + col) = x;
+      } else if constexpr (MODE == GM_F16) {
+        __half2 h0 = __floats2half2_rn(x.x, x.y), h1 = __floats2half2_rn(x.z, x.w);
+        uint2 t;
+        t.x = *reinterpret_cast<uint32_t*>(&h0);
+        t.y = *reinterpret_cast<uint32_t*>(&h1);
+        *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(e.out) + orow[i] * (long)e.ld_out + col + out_off) = t;
+      } else {
+        if constexpr (MODE == GM_BIAS_GELU_BF16) {
+          x.x = gelu_erf_fast(x.x);
+          x.y = gelu_erf_fast(x.y);
+          x.z = gelu_erf_fast(x.z);
+          x.w = gelu_erf_fast(x.w);
+        }
+        uint2 t;
+        t.x = pack_bf16(x.x, x.y);
+        t.y = pack_bf16(x.z, x.w);
+        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(e.out) + orow[i] * (long)e.ld_out + col) = t;
+      }
+    }
+    __syncwarp();
+  }
+}
+
 template <bool kTf32, int MODE, int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
@@ -431,8 +536,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       };
       TmemSrc src{tmem_base + (uint32_t(ew * 32) << 16) + uint32_t(as * BN)};
       const long row = (long)m_blk * kBM + ew * 32 + lane;
-      if (kSplit)
-        epilogue_row<MODE, BN>(e, src, row, M, N, n_blk * BN, (long)bidx * e.out_batch_off, eh, 2, wait_acc);
+      if constexpr (kSplit)
+        epilogue_warp<MODE, BN>(e, src, (long)m_blk * kBM + ew * 32, lane, M, N, n_blk * BN,
+                                (long)bidx * e.out_batch_off, eh, 2, wait_acc,
+                                reinterpret_cast<float4*>(smem + kStages * Cfg::kStageBytes + 256) + (warp - 4) * 256);
       else if (eh == 0)
         epilogue_row<MODE, BN>(e, src, row, M, N, n_blk * BN, (long)bidx * e.out_batch_off, 0, 1, wait_acc);
       else
@@ -455,7 +562,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // leader issues tcgen05.mma with M = 256 and each CTA drains its own 128 accumulator lanes.
 constexpr int kStages2 = 6;
 constexpr int kStageBytes2 = kBM * 128 + 128 * 128;   // A half + W half
-constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + 1024 + 256;
+constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + 1024 + 256 + 32768 /*epilogue transposition tiles*/;
 
 template <int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
@@ -564,7 +671,9 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       };
       TmemSrc src{tmem_base + (uint32_t(ew * 32) << 16) + uint32_t(as * BN)};
       const long row = (long)m_blk * 256 + rank * 128 + ew * 32 + lane;
-      epilogue_row<MODE, BN>(e, src, row, M, N, n_blk * BN, 0, eh, 2, wait_acc);
+      (void)row;
+      epilogue_warp<MODE, BN>(e, src, (long)m_blk * 256 + rank * 128 + ew * 32, lane, M, N, n_blk * BN, 0, eh, 2,
+                              wait_acc, reinterpret_cast<float4*>(smem + kStages2 * kStageBytes2 + 256) + (warp - 4) * 256);
       tc_fence_before();
       mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[as]), 0));
     }
