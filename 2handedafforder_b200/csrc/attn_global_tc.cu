@@ -105,8 +105,11 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  // register re-allocation between the warpgroups: the softmax threads keep a 128-key score row + 64 bias values
+  // (setmaxnreg at the top of every role branch)
 
   if (warp == 0) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
     if (lane == 0) {
       int it = 0, kc = 0;
       for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
@@ -135,6 +138,7 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
       }
     }
   } else if (warp == 1) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
     if (lane == 0) {
       constexpr uint32_t idS = umma_idesc_bf16(128, kBKeys, false, false);
       constexpr uint32_t idO64 = umma_idesc_bf16(128, 64, false, true);
@@ -200,7 +204,10 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
         }
       }
     }
-  } else if (warp >= 4) {
+  } else if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     const int t = (warp - 4) >> 2, q = warp & 3;
     const int rl = q * 32 + lane;                       // row inside the M tile
     const uint32_t tl = tmem + (uint32_t(q * 32) << 16);
@@ -241,18 +248,21 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
         mbar_wait(&s_full[t], ns & 1);
         ++ns;
         tc_fence_after();
-        // ---- pass 1: maximum of the raw scores -> upper bound of the biased tile maximum
-        float mx = -INFINITY;
-        {
-          uint32_t v[32];
+        // ---- the whole 128-key score row of this thread in registers (one TMEM round trip per tile)
+        uint32_t v[128];
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            tmem_ld_32x32(tS + c * 32, v);
-            tmem_wait_ld();
+        for (int c = 0; c < 4; ++c) tmem_ld_32x32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32 * c]));
+        tmem_wait_ld();
+        // maximum of the raw scores -> upper bound of the biased tile maximum
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
-          }
+        for (int i = 0; i < 128; i += 4) {
+          mx0 = fmaxf(mx0, __uint_as_float(v[i]));
+          mx1 = fmaxf(mx1, __uint_as_float(v[i + 1]));
+          mx2 = fmaxf(mx2, __uint_as_float(v[i + 2]));
+          mx3 = fmaxf(mx3, __uint_as_float(v[i + 3]));
         }
+        const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
         const float Mt = mx * cs + bwmax + fmaxf(bh0, bh1);
         const bool grow = Mt > m_used + 8.f;
         if (__any_sync(0xffffffffu, grow)) {
@@ -261,19 +271,16 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
           l *= f;
           m_used = m_new;
           if (j > 0) {
-            uint32_t v[32];
+            uint32_t o[32];
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
-              tmem_ld_32x32(tO + c * 32, v);
+              tmem_ld_32x32(tO + c * 32, o);
               tmem_wait_ld();
-#pragma unroll
-              for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * f);
-              // 32 columns back as two x16 stores
               uint32_t a[16], bq[16];
 #pragma unroll
               for (int i = 0; i < 16; ++i) {
-                a[i] = v[i];
-                bq[i] = v[16 + i];
+                a[i] = __float_as_uint(__uint_as_float(o[i]) * f);
+                bq[i] = __float_as_uint(__uint_as_float(o[16 + i]) * f);
               }
               tmem_st_32x32_16(tO + c * 32, a);
               tmem_st_32x32_16(tO + c * 32 + 16, bq);
@@ -289,26 +296,29 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
           }
         }
         const float c0 = bh0 - m_used, c1 = bh1 - m_used;
-        // ---- pass 2: p = 2^(s*cs + bw + bh - m), row sum, P (bf16 pairs) into the first 64 columns of S_t
-        float sum = 0.f;
-        {
-          uint32_t v[32];
+        // ---- p = 2^(s*cs + bw + bh - m), row sum (4 partial chains), P (bf16 pairs) into the first 64 columns of S_t
+        float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            tmem_ld_32x32(tS + c * 32, v);
-            tmem_wait_ld();
-            const float cc = c < 2 ? c0 : c1;
-            uint32_t u[16];
+        for (int c = 0; c < 4; ++c) {
+          const float cc = c < 2 ? c0 : c1;
+          uint32_t u[16];
 #pragma unroll
-            for (int i = 0; i < 32; i += 2) {
-              const float p0 = ex2_fast(fmaf(__uint_as_float(v[i]), cs, bw[(c & 1) * 32 + i]) + cc);
-              const float p1 = ex2_fast(fmaf(__uint_as_float(v[i + 1]), cs, bw[(c & 1) * 32 + i + 1]) + cc);
-              sum += p0 + p1;
-              u[i >> 1] = pack_bf16(p0, p1);
-            }
-            tmem_st_32x32_16(tS + c * 16, u);
+          for (int i = 0; i < 32; i += 4) {
+            const int k = (c & 1) * 32 + i;
+            const float p0 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i]), cs, bw[k]) + cc);
+            const float p1 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 1]), cs, bw[k + 1]) + cc);
+            const float p2 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 2]), cs, bw[k + 2]) + cc);
+            const float p3 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 3]), cs, bw[k + 3]) + cc);
+            sum0 += p0;
+            sum1 += p1;
+            sum2 += p2;
+            sum3 += p3;
+            u[i >> 1] = pack_bf16(p0, p1);
+            u[(i >> 1) + 1] = pack_bf16(p2, p3);
           }
+          tmem_st_32x32_16(tS + c * 16, u);
         }
+        const float sum = (sum0 + sum1) + (sum2 + sum3);
         l += sum;
         tmem_wait_st();
         tc_fence_before();
