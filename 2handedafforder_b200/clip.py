@@ -60,8 +60,8 @@ class _Slot:
 
     def __init__(self, mb: int, max_prompts: int, hw: Tuple[int, int], device: torch.device):
         cap = mb * max_prompts
-        self.masks = torch.zeros((2, cap, hw[0], hw[1]), dtype=torch.uint8, device=device)
-        self.heads = torch.zeros((3, cap, 4), dtype=torch.float32, device=device)
+        self.masks = torch.empty((2, cap, hw[0], hw[1]), dtype=torch.uint8, device=device)
+        self.heads = torch.empty((3, cap, 4), dtype=torch.float32, device=device)
         self.counts = torch.zeros((mb,), dtype=torch.int32, device=device)
         self.works: list = []
 

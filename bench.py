@@ -254,26 +254,34 @@ def run_gpu_arm(args):
     segs = [host_seg[i * NP:(i + 1) * NP].to(dev) for i in range(B)]
     resize, original = [RESIZE] * B, [ORIGINAL] * B
     H, W = ORIGINAL
-    gather_buf = None
-    if world > 1 and rank == 0:
-        gather_buf = [torch.empty((2, P, H, W), dtype=torch.uint8, device=dev) for _ in range(world)]
-    send_buf = torch.empty((2, P, H, W), dtype=torch.uint8, device=dev) if world > 1 else None
+    clip = importlib.import_module(PKG + ".clip")
 
     def step(fr, sg):
-        out = sam.segment(fr, sg, resize, original, threshold=0.0, return_logits=False)
-        if world > 1:   # masks come back to rank 0 over NCCL
-            send_buf[0].copy_(out["masks_left_packed"])
-            send_buf[1].copy_(out["masks_right_packed"])
-            dist.gather(send_buf, gather_buf, dst=0)
-        return out
+        return sam.segment(fr, sg, resize, original, threshold=0.0, return_logits=False)
+
+    def run_steps(k, load, sink=None):
+        """k steps.  N = 1: k segment() calls.  N > 1: the product clip path - a clip of world*B*k frames sharded
+        over the ranks, one micro-batch of B frames per rank per step, u8 masks + heads gathered to rank 0 over
+        NCCL asynchronously behind the next micro-batch."""
+        if world == 1:
+            out = None
+            for _ in range(k):
+                out = step(*load(0, B))
+                if sink is not None:
+                    sink(out)
+            return out
+        return clip.segment_clip(sam.segment, load, world * B * k, RESIZE, ORIGINAL, micro_batch=B,
+                                 max_prompts_per_frame=NP, threshold=0.0, device=dev, sink=sink, keep=False)
+
+    def resident(lo, hi):
+        return frames, segs
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 0)):
-        step(frames, segs)
+    run_steps(max(args.warmup, 0), resident)
     barrier()
     handle = sam._handle
 
@@ -285,8 +293,7 @@ def run_gpu_arm(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
-    for _ in range(args.steps):
-        out = step(frames, segs)
+    run_steps(args.steps, resident)
     ev1.record()
     barrier()
     ms_total = ev0.elapsed_time(ev1)
@@ -304,23 +311,32 @@ def run_gpu_arm(args):
     h2d = host_frames.numel() * host_frames.element_size() + host_seg.numel() * 4
     d2h = host_masks.numel() + host_heads.numel() * 4
 
-    def e2e_step():
+    def from_host(lo, hi):
         fr = host_frames.to(dev, non_blocking=True)
         sg_all = host_seg.to(dev, non_blocking=True)
-        sg = [sg_all[i * NP:(i + 1) * NP] for i in range(B)]
-        o = step(fr, sg)
+        return fr, [sg_all[i * NP:(i + 1) * NP] for i in range(B)]
+
+    def to_host_1(o):               # N = 1: the caller consumes the masks on the host after every step
         host_masks[0].copy_(o["masks_left_packed"], non_blocking=True)
         host_masks[1].copy_(o["masks_right_packed"], non_blocking=True)
         host_heads[0].copy_(o["taxonomy"], non_blocking=True)
         host_heads[1].copy_(o["iou_left"], non_blocking=True)
         host_heads[2].copy_(o["iou_right"], non_blocking=True)
-        torch.cuda.current_stream().synchronize()   # the caller consumes the masks on the host
+        torch.cuda.current_stream().synchronize()
 
-    e2e_step()
+    def to_host_n(f, ml, mr, tx, il, ir):   # N > 1, rank 0: every gathered frame goes to pinned host memory
+        a = (f % B) * NP
+        host_masks[0, a:a + NP].copy_(ml, non_blocking=True)
+        host_masks[1, a:a + NP].copy_(mr, non_blocking=True)
+        host_heads[0, a:a + NP].copy_(tx, non_blocking=True)
+        host_heads[1, a:a + NP].copy_(il, non_blocking=True)
+        host_heads[2, a:a + NP].copy_(ir, non_blocking=True)
+
+    e2e_sink = to_host_1 if world == 1 else to_host_n
+    run_steps(1, from_host, e2e_sink)
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
+    run_steps(args.steps, from_host, e2e_sink)
     barrier()
     e2e_s = time.perf_counter() - t0
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
