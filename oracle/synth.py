@@ -194,3 +194,15 @@ def flops_per_frame(arch: Arch, n_prompts: int = 3) -> float:
     f += 2.0 * T * D * OUT_CH + 2.0 * T * OUT_CH * OUT_CH * 9    # neck
     f += n_prompts * 2 * 3.606e9 + n_prompts * 0.004e9          # decoders
     return f
+
+
+import numpy as np  # noqa: E402
+
+
+def synth_image(H, W, seed):
+    """(H,W,3) uint8 RGB test frame for the preprocessing row.  Smooth structure + noise so both the antialias window and the rounding paths are exercised."""
+    rng = np.random.default_rng(seed)
+    yy, xx = np.mgrid[0:H, 0:W]
+    base = 127 + 100 * np.sin(xx / 17.0 + seed) * np.cos(yy / 11.0)
+    img = base[..., None] + rng.normal(0, 40, (H, W, 3))
+    return np.clip(img, 0, 255).astype(np.uint8)
