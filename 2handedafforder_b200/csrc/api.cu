@@ -403,6 +403,7 @@ int create_common(b200sam_t** out, int dim, int depth, int heads, const int* gid
   if (prop.major != 10)
     return fail(h, B200SAM_ERR_UNSUPPORTED, "device %d is sm_%d%d; libb200sam is built for sm_100a only", device,
                 prop.major, prop.minor);
+  h->n_sm = prop.multiProcessorCount;
   DeviceGuard g(device);
   CU(gemm_tc_init(device));
   CU(attention_init());
@@ -931,6 +932,131 @@ extern "C" int b200sam_dense_pe(b200sam_t* h, float* out, void* stream) {
   h->prof_stream = reinterpret_cast<cudaStream_t>(stream);
   h->pc = B200SAM_PC_ELEMENTWISE;
   KL(launch_tokens_to_nchw(h->pe_tok, 1, out, DT_F32, reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ callers either side
+
+namespace {
+
+int upload_ints(b200sam_t* h, const std::vector<int>& v, int** out) {
+  CU(dalloc(h, out, v.size() ? v.size() : 1));
+  if (!v.empty()) CU(cudaMemcpy(*out, v.data(), v.size() * sizeof(int), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+// transforms.py:103-113
+void preprocess_shape(int oldh, int oldw, int* newh, int* neww) {
+  const double scale = kImg * 1.0 / (oldh > oldw ? oldh : oldw);
+  *newh = (int)(oldh * scale + 0.5);
+  *neww = (int)(oldw * scale + 0.5);
+}
+
+// Pillow coefficient tables of one raw frame size, built and uploaded the first time that size is seen.
+int resample_tables(b200sam_t* h, int H, int W, const ResampleTables** out) {
+  auto it = h->resample.find({H, W});
+  if (it == h->resample.end()) {
+    ResampleTables t;
+    t.H = H;
+    t.W = W;
+    preprocess_shape(H, W, &t.new_h, &t.new_w);
+    if (t.new_h < 1 || t.new_w < 1 || t.new_h > kImg || t.new_w > kImg)
+      return fail(h, B200SAM_ERR_INVALID, "frame %dx%d resizes to %dx%d", H, W, t.new_h, t.new_w);
+    ResampleAxis ax, ay;
+    build_resample_axis(W, t.new_w, &ax);
+    build_resample_axis(H, t.new_h, &ay);
+    t.kx = ax.ksize;
+    t.ky = ay.ksize;
+    t.ident_x = ax.identity;
+    t.ident_y = ay.identity;
+    t.tile_rows = preprocess_tile_rows(ay, t.new_h);
+    if ((size_t)t.tile_rows * 128 * 3 > 200 * 1024)
+      return fail(h, B200SAM_ERR_INVALID, "frame height %d needs a %d-row tile: downscale factor not supported", H,
+                  t.tile_rows);
+    if (int r = upload_ints(h, ax.lo, &t.d_xlo)) return r;
+    if (int r = upload_ints(h, ax.cnt, &t.d_xcnt)) return r;
+    if (int r = upload_ints(h, ax.kk, &t.d_xkk)) return r;
+    if (int r = upload_ints(h, ay.lo, &t.d_ylo)) return r;
+    if (int r = upload_ints(h, ay.cnt, &t.d_ycnt)) return r;
+    if (int r = upload_ints(h, ay.kk, &t.d_ykk)) return r;
+    it = h->resample.emplace(std::make_pair(H, W), t).first;
+  }
+  *out = &it->second;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b200sam_preprocess(b200sam_t* h, const uint8_t* frames_rgb, int B, int H, int W, void* out,
+                                  int out_dtype, int* host_resize_hw, void* stream) {
+  if (!h) return B200SAM_ERR_INVALID;
+  if (B < 0 || H < 1 || W < 1 || H > 16384 || W > 16384)
+    return fail(h, B200SAM_ERR_INVALID, "bad preprocess sizes B=%d H=%d W=%d", B, H, W);
+  if (out_dtype != B200SAM_F32 && out_dtype != B200SAM_BF16 && out_dtype != B200SAM_F16)
+    return fail(h, B200SAM_ERR_INVALID, "bad output dtype %d", out_dtype);
+  DeviceGuard g(h->device);
+  const ResampleTables* t = nullptr;
+  if (int r = resample_tables(h, H, W, &t)) return r;
+  if (host_resize_hw) host_resize_hw[0] = t->new_h, host_resize_hw[1] = t->new_w;
+  if (B == 0) return 0;
+  if (!frames_rgb || !out) return fail(h, B200SAM_ERR_INVALID, "frames / out is NULL");
+  if (reinterpret_cast<uintptr_t>(out) & 15) return fail(h, B200SAM_ERR_INVALID, "out must be 16-byte aligned");
+  h->prof_stream = reinterpret_cast<cudaStream_t>(stream);
+  h->pc = B200SAM_PC_PREPROCESS;
+  KL(launch_preprocess(frames_rgb, B, H, W, *t, out, out_dtype, reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int b200sam_seg_project(b200sam_t* h, const void* hidden, int hidden_dtype, int b, int L, int hdim,
+                                   const int64_t* output_ids, int T, int64_t seg_token_idx, const void* w1,
+                                   const void* b1, const void* w2, const void* b2, int w_dtype, float* emb_out,
+                                   int max_rows, int* counts_out, void* stream) {
+  if (!h) return B200SAM_ERR_INVALID;
+  if (b < 1 || b > 1024 || T < 1 || hdim < 8 || hdim % 8 != 0 || max_rows < 1)
+    return fail(h, B200SAM_ERR_INVALID, "bad seg_project sizes b=%d T=%d hdim=%d max_rows=%d", b, T, hdim, max_rows);
+  if (L < 255 + T - 1)   // LISA.py:461-466: the hidden states carry 255 more positions than output_ids[:, 1:]
+    return fail(h, B200SAM_ERR_INVALID, "hidden length %d < 255 + T - 1 = %d", L, 255 + T - 1);
+  if ((size_t)hdim * 8 * sizeof(float) > 227 * 1024)
+    return fail(h, B200SAM_ERR_INVALID, "hidden size %d does not fit the 8-row shared-memory stage", hdim);
+  if (hidden_dtype < 0 || hidden_dtype > 2 || (w_dtype != B200SAM_F32 && w_dtype != B200SAM_BF16))
+    return fail(h, B200SAM_ERR_INVALID, "bad dtypes hidden=%d weights=%d", hidden_dtype, w_dtype);
+  if (!hidden || !output_ids || !w1 || !b1 || !w2 || !b2 || !emb_out || !counts_out)
+    return fail(h, B200SAM_ERR_INVALID, "NULL argument");
+  DeviceGuard g(h->device);
+  if (!h->seg_counts) CU(dalloc(h, &h->seg_counts, 1025));
+  if (max_rows > h->seg_cap_rows || hdim > h->seg_cap_h) {   // first use / larger request: grow (not on the hot path)
+    const int rows = max_rows > h->seg_cap_rows ? max_rows : h->seg_cap_rows;
+    const int hd = hdim > h->seg_cap_h ? hdim : h->seg_cap_h;
+    CU(dalloc(h, &h->seg_rows, rows));
+    CU(dalloc(h, &h->seg_hidden, (size_t)rows * hd));
+    h->seg_cap_rows = rows;
+    h->seg_cap_h = hd;
+  }
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  h->prof_stream = s;
+  h->pc = B200SAM_PC_SEG_PROJECT;
+  KL(launch_seg_scan(output_ids, b, T, L, seg_token_idx, h->seg_rows, max_rows, h->seg_counts, s));
+  KL(launch_rows_fc(hidden, hidden_dtype, hdim, h->seg_rows, h->seg_counts + b, max_rows, w1, b1, w_dtype, hdim, hdim,
+                    true, h->seg_hidden, h->n_sm, s));
+  KL(launch_rows_fc(h->seg_hidden, DT_F32, hdim, nullptr, h->seg_counts + b, max_rows, w2, b2, w_dtype, hdim, kOutCh,
+                    false, emb_out, h->n_sm, s));
+  CU(cudaMemcpyAsync(counts_out, h->seg_counts, sizeof(int) * (b + 1), cudaMemcpyDeviceToDevice, s));
+  return 0;
+}
+
+extern "C" int b200sam_mask_metrics(b200sam_t* h, const uint8_t* masks_left, const uint8_t* masks_right,
+                                    const float* taxonomy, const uint8_t* gt, const int* gt_index, int P, int H,
+                                    int W, int64_t* counts_out, uint8_t* pred_out, void* stream) {
+  if (!h) return B200SAM_ERR_INVALID;
+  if (P < 0 || P > 65535 || H < 1 || W < 1)
+    return fail(h, B200SAM_ERR_INVALID, "bad mask_metrics sizes P=%d H=%d W=%d", P, H, W);
+  if (P == 0) return 0;
+  if (!masks_left || !masks_right || !taxonomy || !gt || !counts_out) return fail(h, B200SAM_ERR_INVALID, "NULL argument");
+  DeviceGuard g(h->device);
+  h->prof_stream = reinterpret_cast<cudaStream_t>(stream);
+  h->pc = B200SAM_PC_METRICS;
+  KL(launch_mask_metrics(masks_left, masks_right, taxonomy, gt, gt_index, P, H, W, counts_out, pred_out, h->n_sm,
+                         reinterpret_cast<cudaStream_t>(stream)));
   return 0;
 }
 

@@ -1,0 +1,482 @@
+// The callers either side of the SAM branch, as HBM-bound integer / byte kernels:
+//
+//   preprocess_kernel   raw uint8 RGB frame -> ResizeLongestSide.apply_image (transforms.py:27-34, = Pillow's 8-bit
+//                       two-pass antialiased bilinear resample) -> (x - mean) / std -> zero pad to 1024^2 -> model
+//                       dtype (inference.py:91-105,251-256).  Bit-exact against the reference: the resample is
+//                       integer fixed point with the coefficient tables built on the host in double precision exactly
+//                       as Pillow builds them; the normalisation is one IEEE fp32 subtract and one IEEE fp32 divide.
+//   seg_scan_kernel /   `[SEG]` rows of the LLM output (LISA.py:457-476) and text_hidden_fcs = Linear-ReLU-Linear
+//   rows_fc_kernel      (LISA.py:95-101) evaluated ONLY on those rows (the reference projects every row, then gathers).
+//   mask_metrics_kernel threshold-mask evaluation of train_ds.py:662-709,761-796: taxonomy-gated left / right / OR mask
+//                       and the intersection / union / area pixel counts behind IoU and IoCM, so validate() never
+//                       copies full-resolution masks to the host.
+#include <math.h>
+
+#include <vector>
+
+#include "aux.cuh"
+#include "common.cuh"
+
+namespace bsam {
+
+// ------------------------------------------------------------------------------------------------ resample tables
+
+// Pillow precompute_coeffs + normalize_coeffs_8bpc for the bilinear (triangle, support 1) filter over the whole
+// axis.  Double precision, same operation order, so the 22-bit fixed-point weights are identical.
+void build_resample_axis(int in_size, int out_size, ResampleAxis* ax) {
+  const double scale = (double)in_size / out_size;
+  const double filterscale = scale < 1.0 ? 1.0 : scale;
+  const double support = 1.0 * filterscale;
+  const int ksize = (int)ceil(support) * 2 + 1;
+  ax->in_size = in_size;
+  ax->out_size = out_size;
+  ax->ksize = ksize;
+  ax->identity = in_size == out_size;
+  ax->lo.assign(out_size, 0);
+  ax->cnt.assign(out_size, 0);
+  ax->kk.assign((size_t)out_size * ksize, 0);
+  std::vector<double> w(ksize);
+  const double ss = 1.0 / filterscale;
+  for (int xx = 0; xx < out_size; ++xx) {
+    const double center = (xx + 0.5) * scale;
+    int lo = (int)(center - support + 0.5);
+    if (lo < 0) lo = 0;
+    int hi = (int)(center + support + 0.5);
+    if (hi > in_size) hi = in_size;
+    const int n = hi - lo;
+    double ww = 0.0;
+    for (int x = 0; x < n; ++x) {
+      double t = (x + lo - center + 0.5) * ss;
+      if (t < 0.0) t = -t;
+      w[x] = t < 1.0 ? 1.0 - t : 0.0;
+      ww += w[x];
+    }
+    for (int x = 0; x < n; ++x)
+      if (ww != 0.0) w[x] /= ww;
+    for (int x = 0; x < n; ++x) {
+      const double v = w[x] * (double)(1 << kResamplePrecisionBits);
+      ax->kk[(size_t)xx * ksize + x] = w[x] < 0 ? (int)(-0.5 + v) : (int)(0.5 + v);
+    }
+    ax->lo[xx] = lo;
+    ax->cnt[xx] = n;
+  }
+}
+
+namespace {
+
+constexpr int kTileW = 128, kTileH = 8, kPreThreads = 256;
+
+__device__ __forceinline__ uint8_t clip8(int acc) {
+  const int v = acc >> kResamplePrecisionBits;      // arithmetic shift, as Pillow's clip8 lookup index
+  return (uint8_t)min(max(v, 0), 255);
+}
+
+template <typename T>
+__device__ __forceinline__ void store4(T* p, float a, float b, float c, float d);
+template <>
+__device__ __forceinline__ void store4<float>(float* p, float a, float b, float c, float d) {
+  *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+}
+template <>
+__device__ __forceinline__ void store4<__nv_bfloat16>(__nv_bfloat16* p, float a, float b, float c, float d) {
+  uint2 v;
+  v.x = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(a)) | ((uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(b)) << 16);
+  v.y = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(c)) | ((uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(d)) << 16);
+  *reinterpret_cast<uint2*>(p) = v;
+}
+template <>
+__device__ __forceinline__ void store4<__half>(__half* p, float a, float b, float c, float d) {
+  uint2 v;
+  v.x = (uint32_t)__half_as_ushort(__float2half_rn(a)) | ((uint32_t)__half_as_ushort(__float2half_rn(b)) << 16);
+  v.y = (uint32_t)__half_as_ushort(__float2half_rn(c)) | ((uint32_t)__half_as_ushort(__float2half_rn(d)) << 16);
+  *reinterpret_cast<uint2*>(p) = v;
+}
+
+struct PreArgs {
+  const uint8_t* in;     // (B, H, W, 3)
+  int H, W, new_h, new_w;
+  const int *xlo, *xcnt, *xkk;   // horizontal tables (new_w entries), ksize kx
+  const int *ylo, *ycnt, *ykk;   // vertical tables (new_h entries), ksize ky
+  int kx, ky, ident_x, ident_y;
+  float mean[3], stdv[3];
+};
+
+// grid (1024/128, 1024/8, B), 256 threads.  One block = one 128 x 8 tile of the padded 1024^2 output, 3 channels.
+// Stage 1: horizontal pass of the input rows this tile's vertical windows touch -> uint8 tile in shared memory
+// (Pillow rounds to uint8 between the passes).  Stage 2: vertical pass, normalise, 4 pixels per thread, one 8/16-byte
+// store each; tiles in the pad region store zeros.
+template <typename T>
+__global__ void __launch_bounds__(kPreThreads) preprocess_kernel(PreArgs a, T* __restrict__ out) {
+  extern __shared__ uint8_t tile[];                 // (rows, kTileW, 3)
+  const int x0 = blockIdx.x * kTileW, y0 = blockIdx.y * kTileH;
+  const long b = blockIdx.z;
+  const int tw = min(kTileW, a.new_w - x0), th = min(kTileH, a.new_h - y0);   // live part of the tile (may be <= 0)
+  int r0 = 0, nrows = 0;
+  if (tw > 0 && th > 0) {
+    if (a.ident_y) {
+      r0 = y0;
+      nrows = th;
+    } else {
+      r0 = a.ylo[y0];
+      nrows = a.ylo[y0 + th - 1] + a.ycnt[y0 + th - 1] - r0;
+    }
+    const uint8_t* src = a.in + b * (long)a.H * a.W * 3;
+    const int items = nrows * tw * 3;
+    for (int i = threadIdx.x; i < items; i += kPreThreads) {
+      const int c = i % 3, x = (i / 3) % tw, r = i / (3 * tw);
+      const uint8_t* row = src + ((long)(r0 + r) * a.W) * 3 + c;
+      uint8_t v;
+      if (a.ident_x) {
+        v = row[(x0 + x) * 3];
+      } else {
+        const int lo = a.xlo[x0 + x], n = a.xcnt[x0 + x];
+        const int* k = a.xkk + (long)(x0 + x) * a.kx;
+        int acc = 1 << (kResamplePrecisionBits - 1);
+        for (int j = 0; j < n; ++j) acc += (int)row[(lo + j) * 3] * k[j];
+        v = clip8(acc);
+      }
+      tile[(r * kTileW + x) * 3 + c] = v;
+    }
+  }
+  __syncthreads();
+  // stage 2: items = 3 channels x 8 rows x 32 groups of 4 pixels
+  for (int i = threadIdx.x; i < 3 * kTileH * (kTileW / 4); i += kPreThreads) {
+    const int g = i % (kTileW / 4), y = (i / (kTileW / 4)) % kTileH, c = i / (kTileH * (kTileW / 4));
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if (y < th) {
+      const int Y = y0 + y;
+      int lo = Y - r0, n = 1;
+      const int* k = nullptr;
+      if (!a.ident_y) {
+        lo = a.ylo[Y] - r0;
+        n = a.ycnt[Y];
+        k = a.ykk + (long)Y * a.ky;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int x = g * 4 + j;
+        if (x < tw) {
+          int u;
+          if (a.ident_y) {
+            u = tile[(lo * kTileW + x) * 3 + c];
+          } else {
+            int acc = 1 << (kResamplePrecisionBits - 1);
+            for (int t = 0; t < n; ++t) acc += (int)tile[((lo + t) * kTileW + x) * 3 + c] * k[t];
+            u = clip8(acc);
+          }
+          v[j] = __fdiv_rn(__fsub_rn((float)u, a.mean[c]), a.stdv[c]);   // inference.py:99
+        }
+      }
+    }
+    T* o = out + ((b * 3 + c) * (long)kImg + (y0 + y)) * kImg + x0 + g * 4;
+    store4<T>(o, v[0], v[1], v[2], v[3]);
+  }
+}
+
+}  // namespace
+
+int preprocess_tile_rows(const ResampleAxis& ay, int new_h) {
+  int worst = 0;
+  for (int y0 = 0; y0 < new_h; y0 += kTileH) {
+    const int y1 = (y0 + kTileH < new_h ? y0 + kTileH : new_h) - 1;
+    const int rows = ay.identity ? (y1 - y0 + 1) : (ay.lo[y1] + ay.cnt[y1] - ay.lo[y0]);
+    if (rows > worst) worst = rows;
+  }
+  return worst;
+}
+
+cudaError_t launch_preprocess(const uint8_t* frames, int B, int H, int W, const ResampleTables& t, void* out,
+                              int out_dtype, cudaStream_t s) {
+  if (B <= 0) return cudaSuccess;
+  PreArgs a;
+  a.in = frames;
+  a.H = H;
+  a.W = W;
+  a.new_h = t.new_h;
+  a.new_w = t.new_w;
+  a.xlo = t.d_xlo;
+  a.xcnt = t.d_xcnt;
+  a.xkk = t.d_xkk;
+  a.ylo = t.d_ylo;
+  a.ycnt = t.d_ycnt;
+  a.ykk = t.d_ykk;
+  a.kx = t.kx;
+  a.ky = t.ky;
+  a.ident_x = t.ident_x;
+  a.ident_y = t.ident_y;
+  const float mean[3] = {123.675f, 116.28f, 103.53f}, stdv[3] = {58.395f, 57.12f, 57.375f};   // inference.py:93-94
+  for (int c = 0; c < 3; ++c) a.mean[c] = mean[c], a.stdv[c] = stdv[c];
+  const size_t smem = (size_t)t.tile_rows * kTileW * 3;
+  dim3 grid(kImg / kTileW, kImg / kTileH, B);
+  cudaError_t e = cudaSuccess;
+  if (out_dtype == DT_F32) {
+    if (smem > 48 * 1024) e = cudaFuncSetAttribute(preprocess_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    preprocess_kernel<float><<<grid, kPreThreads, smem, s>>>(a, reinterpret_cast<float*>(out));
+  } else if (out_dtype == DT_BF16) {
+    if (smem > 48 * 1024) e = cudaFuncSetAttribute(preprocess_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    preprocess_kernel<__nv_bfloat16><<<grid, kPreThreads, smem, s>>>(a, reinterpret_cast<__nv_bfloat16*>(out));
+  } else if (out_dtype == DT_F16) {
+    if (smem > 48 * 1024) e = cudaFuncSetAttribute(preprocess_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    preprocess_kernel<__half><<<grid, kPreThreads, smem, s>>>(a, reinterpret_cast<__half*>(out));
+  } else {
+    return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ [SEG] rows
+
+namespace {
+
+// One block.  LISA.py:457-476: mask = output_ids[:, 1:] == seg_idx, shifted right by 255 columns (the single image
+// token stands for 256 CLIP patches); rows are collected in row-major order.  counts: (b + 1) ints = prompts per
+// image, then the total; rows: flat row index (bi * L + 255 + t - 1) of every [SEG] token, at most max_rows
+// (a larger total is reported through counts[b] and the caller raises).
+__global__ void __launch_bounds__(1024) seg_scan_kernel(const int64_t* __restrict__ ids, int b, int T, int L,
+                                                         int64_t seg_idx, int* __restrict__ rows, int max_rows,
+                                                         int* __restrict__ counts) {
+  __shared__ int s_cnt[1024];
+  __shared__ int s_off[1025];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+  for (int bi = warp; bi < b; bi += nwarp) {      // pass 1: count per image
+    int c = 0;
+    for (int t0 = 1; t0 < T; t0 += 32) {
+      const int t = t0 + lane;
+      c += __popc(__ballot_sync(0xffffffffu, t < T && ids[(long)bi * T + t] == seg_idx));
+    }
+    if (lane == 0) s_cnt[bi] = c;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int acc = 0;
+    for (int bi = 0; bi < b; ++bi) {
+      s_off[bi] = acc;
+      acc += s_cnt[bi];
+      counts[bi] = s_cnt[bi];
+    }
+    s_off[b] = acc;
+    counts[b] = acc;
+  }
+  __syncthreads();
+  for (int bi = warp; bi < b; bi += nwarp) {      // pass 2: ordered compaction
+    int base = s_off[bi];
+    for (int t0 = 1; t0 < T; t0 += 32) {
+      const int t = t0 + lane;
+      const bool hit = t < T && ids[(long)bi * T + t] == seg_idx;
+      const unsigned m = __ballot_sync(0xffffffffu, hit);
+      const int pos = base + __popc(m & ((1u << lane) - 1u));
+      if (hit && pos < max_rows) rows[pos] = bi * L + 255 + (t - 1);
+      base += __popc(m);
+    }
+  }
+}
+
+constexpr int kFcRows = 8, kFcWarps = 8;
+
+__device__ __forceinline__ void load8(const float* p, float (&w)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  w[0] = a.x, w[1] = a.y, w[2] = a.z, w[3] = a.w, w[4] = b.x, w[5] = b.y, w[6] = b.z, w[7] = b.w;
+}
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&w)[8]) {
+  const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    w[2 * i] = __uint_as_float(u[i] << 16);
+    w[2 * i + 1] = __uint_as_float(u[i] & 0xffff0000u);
+  }
+}
+__device__ __forceinline__ float ld_scalar(const float* p, long i) { return __ldg(p + i); }
+__device__ __forceinline__ float ld_scalar(const __nv_bfloat16* p, long i) { return __bfloat162float(p[i]); }
+
+// y[p, j] = act(bias[j] + sum_k x[row(p), k] * Wt[j, k]) for the (device-side) n = *n_ptr gathered rows.
+// grid (ctas, ceil(max_rows / 8)); block = 8 warps; the 8 input rows of the chunk are staged once in shared memory as
+// fp32 (8 * K * 4 bytes), each warp then streams whole weight rows with 16-byte loads (the kernel is bound by the
+// one read of W: K * N * sizeof(W) bytes) and reduces 8 dot products by warp shuffle.
+template <typename WT>
+__global__ void __launch_bounds__(kFcWarps * 32)
+rows_fc_kernel(const void* __restrict__ x, int x_dtype, long x_ld, const int* __restrict__ rows,
+               const int* __restrict__ n_ptr, int max_rows, const WT* __restrict__ Wt, const WT* __restrict__ bias,
+               int K, int N, int relu, float* __restrict__ y) {
+  extern __shared__ float xs[];                    // (8, K)
+  const int n = min(*n_ptr, max_rows);
+  const int p0 = blockIdx.y * kFcRows;
+  if (p0 >= n) return;
+  const int np = min(kFcRows, n - p0);
+  for (int i = threadIdx.x; i < kFcRows * K; i += blockDim.x) {
+    const int r = i / K, k = i - r * K;
+    float v = 0.f;
+    if (r < np) {
+      const long row = rows ? rows[p0 + r] : (p0 + r);
+      const long off = row * x_ld + k;
+      if (x_dtype == DT_F32) v = reinterpret_cast<const float*>(x)[off];
+      else if (x_dtype == DT_BF16) v = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(x)[off]);
+      else v = __half2float(reinterpret_cast<const __half*>(x)[off]);
+    }
+    xs[i] = v;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int j = blockIdx.x * kFcWarps + warp; j < N; j += gridDim.x * kFcWarps) {
+    float acc[kFcRows];
+#pragma unroll
+    for (int r = 0; r < kFcRows; ++r) acc[r] = 0.f;
+    const WT* wrow = Wt + (long)j * K;
+    for (int k = lane * 8; k < K; k += 256) {
+      float w[8];
+      load8(wrow + k, w);
+#pragma unroll
+      for (int r = 0; r < kFcRows; ++r) {
+        const float4 a = *reinterpret_cast<const float4*>(xs + r * K + k);
+        const float4 c = *reinterpret_cast<const float4*>(xs + r * K + k + 4);
+        acc[r] += w[0] * a.x + w[1] * a.y + w[2] * a.z + w[3] * a.w + w[4] * c.x + w[5] * c.y + w[6] * c.z + w[7] * c.w;
+      }
+    }
+    const float bj = ld_scalar(bias, j);
+#pragma unroll
+    for (int r = 0; r < kFcRows; ++r) {
+      float v = warp_sum(acc[r]);
+      if (lane == 0 && r < np) {
+        v += bj;
+        if (relu) v = fmaxf(v, 0.f);
+        y[(long)(p0 + r) * N + j] = v;
+      }
+    }
+  }
+}
+
+}  // namespace
+
+cudaError_t launch_seg_scan(const int64_t* ids, int b, int T, int L, int64_t seg_idx, int* rows, int max_rows,
+                            int* counts, cudaStream_t s) {
+  if (b <= 0 || b > 1024) return cudaErrorInvalidValue;
+  seg_scan_kernel<<<1, 1024, 0, s>>>(ids, b, T, L, seg_idx, rows, max_rows, counts);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_rows_fc(const void* x, int x_dtype, long x_ld, const int* rows, const int* n_ptr, int max_rows,
+                           const void* Wt, const void* bias, int w_dtype, int K, int N, bool relu, float* y,
+                           int n_sm, cudaStream_t s) {
+  if (K % 8 != 0 || max_rows <= 0) return cudaErrorInvalidValue;
+  const size_t smem = (size_t)kFcRows * K * sizeof(float);
+  if (smem > 227 * 1024) return cudaErrorInvalidValue;
+  const int ctas = (N + kFcWarps - 1) / kFcWarps < n_sm ? (N + kFcWarps - 1) / kFcWarps : n_sm;
+  dim3 grid(ctas, (max_rows + kFcRows - 1) / kFcRows);
+  cudaError_t e;
+  if (w_dtype == DT_F32) {
+    e = cudaFuncSetAttribute(rows_fc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    rows_fc_kernel<float><<<grid, kFcWarps * 32, smem, s>>>(x, x_dtype, x_ld, rows, n_ptr, max_rows,
+                                                            reinterpret_cast<const float*>(Wt),
+                                                            reinterpret_cast<const float*>(bias), K, N, relu, y);
+  } else if (w_dtype == DT_BF16) {
+    e = cudaFuncSetAttribute(rows_fc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    rows_fc_kernel<__nv_bfloat16><<<grid, kFcWarps * 32, smem, s>>>(
+        x, x_dtype, x_ld, rows, n_ptr, max_rows, reinterpret_cast<const __nv_bfloat16*>(Wt),
+        reinterpret_cast<const __nv_bfloat16*>(bias), K, N, relu, y);
+  } else {
+    return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ evaluation metrics
+
+namespace {
+
+// bit j*8 of the result = byte j of v is non-zero
+__device__ __forceinline__ uint32_t nz_bytes(uint32_t v) { return __vcmpne4(v, 0u) & 0x01010101u; }
+
+// grid (ctas_per_prompt, P).  Per prompt p: k = argmax(taxonomy[p]) (first maximum, like torch.argmax);
+// pred = left (k == 0) | right (k == 1) | left OR right (otherwise)   [train_ds.py:690-706];
+// counts[p] = {|pred & gt|, |pred | gt|, |pred|}                       [train_ds.py:761-796];
+// pred_out (optional) = the gated mask as {0, 255} bytes.  16 bytes of each mask per thread per iteration.
+__global__ void __launch_bounds__(256)
+mask_metrics_kernel(const uint8_t* __restrict__ left, const uint8_t* __restrict__ right,
+                    const float* __restrict__ taxonomy, const uint8_t* __restrict__ gt,
+                    const int* __restrict__ gt_index, long HW, unsigned long long* __restrict__ counts,
+                    uint8_t* __restrict__ pred_out, int vec_ok) {
+  const long p = blockIdx.y;
+  int k = 0;
+  {
+    float best = taxonomy[p * 4];
+#pragma unroll
+    for (int i = 1; i < 4; ++i)
+      if (taxonomy[p * 4 + i] > best) best = taxonomy[p * 4 + i], k = i;
+  }
+  const uint32_t use_l = k != 1 ? 0xffffffffu : 0u, use_r = k != 0 ? 0xffffffffu : 0u;
+  const uint8_t* L = left + p * HW;
+  const uint8_t* R = right + p * HW;
+  const uint8_t* G = gt + (long)(gt_index ? gt_index[p] : p) * HW;
+  uint8_t* O = pred_out ? pred_out + p * HW : nullptr;
+  unsigned inter = 0, uni = 0, area = 0;
+  const long tid = (long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long)gridDim.x * blockDim.x;
+  if (vec_ok) {
+    const long nvec = HW / 16;
+    for (long i = tid; i < nvec; i += nth) {
+      const uint4 l = __ldg(reinterpret_cast<const uint4*>(L) + i), r = __ldg(reinterpret_cast<const uint4*>(R) + i);
+      const uint4 g = __ldg(reinterpret_cast<const uint4*>(G) + i);
+      const uint32_t lw[4] = {l.x, l.y, l.z, l.w}, rw[4] = {r.x, r.y, r.z, r.w}, gw[4] = {g.x, g.y, g.z, g.w};
+      uint32_t ow[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t pm = (nz_bytes(lw[j]) & use_l) | (nz_bytes(rw[j]) & use_r), gm = nz_bytes(gw[j]);
+        inter += __popc(pm & gm);
+        uni += __popc(pm | gm);
+        area += __popc(pm);
+        ow[j] = pm * 255u;
+      }
+      if (O) reinterpret_cast<uint4*>(O)[i] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+    }
+    for (long i = nvec * 16 + tid; i < HW; i += nth) {      // tail
+      const bool pm = (L[i] != 0 && use_l) || (R[i] != 0 && use_r), gm = G[i] != 0;
+      inter += pm && gm, uni += pm || gm, area += pm;
+      if (O) O[i] = pm ? 255 : 0;
+    }
+  } else {
+    for (long i = tid; i < HW; i += nth) {
+      const bool pm = (L[i] != 0 && use_l) || (R[i] != 0 && use_r), gm = G[i] != 0;
+      inter += pm && gm, uni += pm || gm, area += pm;
+      if (O) O[i] = pm ? 255 : 0;
+    }
+  }
+  // block reduction: warp shuffles, then one atomic per warp and counter
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    inter += __shfl_xor_sync(0xffffffffu, inter, o);
+    uni += __shfl_xor_sync(0xffffffffu, uni, o);
+    area += __shfl_xor_sync(0xffffffffu, area, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (inter) atomicAdd(counts + p * 3 + 0, (unsigned long long)inter);
+    if (uni) atomicAdd(counts + p * 3 + 1, (unsigned long long)uni);
+    if (area) atomicAdd(counts + p * 3 + 2, (unsigned long long)area);
+  }
+}
+
+}  // namespace
+
+cudaError_t launch_mask_metrics(const uint8_t* left, const uint8_t* right, const float* taxonomy, const uint8_t* gt,
+                                const int* gt_index, int P, int H, int W, int64_t* counts, uint8_t* pred_out,
+                                int n_sm, cudaStream_t s) {
+  if (P <= 0) return cudaSuccess;
+  if (P > 65535) return cudaErrorInvalidValue;
+  const long HW = (long)H * W;
+  cudaError_t e = cudaMemsetAsync(counts, 0, sizeof(int64_t) * 3 * P, s);
+  if (e != cudaSuccess) return e;
+  auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  const int vec_ok = HW % 16 == 0 && al(left) && al(right) && al(gt) && (!pred_out || al(pred_out));
+  long per = (HW / 16 + 255) / 256;                      // blocks that would give one vector per thread
+  long want = (8L * n_sm + P - 1) / P;                   // ~8 resident blocks per SM over the whole grid
+  int ctas = (int)(per < want ? (per > 0 ? per : 1) : want);
+  dim3 grid(ctas, P);
+  mask_metrics_kernel<<<grid, 256, 0, s>>>(left, right, taxonomy, gt, gt_index, HW,
+                                           reinterpret_cast<unsigned long long*>(counts), pred_out, vec_ok);
+  return cudaGetLastError();
+}
+
+}  // namespace bsam

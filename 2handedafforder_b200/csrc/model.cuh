@@ -8,6 +8,7 @@
 #include <string>
 #include <vector>
 
+#include "aux.cuh"
 #include "gemm_tc.cuh"
 #include "kernels.cuh"
 
@@ -123,4 +124,12 @@ struct b200sam {
   float* tok_kv = nullptr;           // (P, 6, 256) [k | v] of the tokens for i2t
   float* hyper = nullptr;            // (P, 32) mask-0 hypernetwork output
   float* emb_in = nullptr;           // (B*4096, 256) staging when decode() is given an external embedding
+
+  // callers either side of the branch (aux.cu); grown on first use / new input size, never on a repeated call
+  int n_sm = 148;
+  std::map<std::pair<int, int>, bsam::ResampleTables> resample;   // (H, W) of the raw frame -> Pillow tables
+  int* seg_rows = nullptr;           // (seg_cap_rows) flat row index of every [SEG] token
+  int* seg_counts = nullptr;         // (1025) prompts per image, then the total
+  float* seg_hidden = nullptr;       // (seg_cap_rows, seg_cap_h) ReLU(fc1)
+  int seg_cap_rows = 0, seg_cap_h = 0;
 };

@@ -21,6 +21,7 @@ from torch import nn
 
 from . import _lib
 from ._manifest import GRID, OUT_CH, manifest
+from .callers import CallersMixin
 
 IMG_SIZE = 1024   # build_sam.py:68
 
@@ -126,7 +127,7 @@ class MaskDecoderB200(_Component):
                                             dense_prompt_embeddings)
 
 
-class B200Sam(nn.Module):
+class B200Sam(CallersMixin, nn.Module):
     """The `visual_model` drop-in.  See module docstring."""
 
     mask_threshold: float = 0.0    # sam.py:19
@@ -184,7 +185,7 @@ class B200Sam(nn.Module):
         except Exception:
             pass
 
-    def _ensure(self, device: torch.device, batch: int = 0, prompts: int = 0) -> C.c_void_p:
+    def _ensure(self, device: torch.device, batch: int = 0, prompts: int = 0, sync: bool = True) -> C.c_void_p:
         if device.type != "cuda":
             raise RuntimeError("B200Sam needs a CUDA (sm_100a) device: there is no CPU fallback")
         lib = _lib.load()
@@ -207,9 +208,13 @@ class B200Sam(nn.Module):
                 raise RuntimeError(f"b200sam_create failed (status {rc}): {msg}")
             self._handle, self._handle_device = h, idx
             self._sig = None
-        if not (self._frozen and self._sig is not None):
+        if sync and not (self._frozen and self._sig is not None):
             self._sync_weights()
         return self._handle
+
+    def _ensure_handle_only(self, device: torch.device) -> C.c_void_p:
+        """Handle for the entry points that read no SAM weights (preprocess / seg_project / mask_metrics)."""
+        return self._ensure(device, sync=False)
 
     def _sync_weights(self) -> None:
         tensors = self._tensors()

@@ -38,7 +38,7 @@ VIT_H = dict(dim=1280, depth=32, heads=16, global_idx=(7, 15, 23, 31))
 
 PC_NAMES = ["elementwise", "gemm_patch", "layernorm", "gemm_qkv", "attn_window", "attn_global", "gemm_proj",
             "gemm_lin1", "gemm_lin2", "neck", "dec_elementwise", "dec_token", "dec_gemm", "dec_upscale",
-            "postprocess"]
+            "postprocess", "preprocess", "seg_project", "metrics"]
 
 
 def flops_per_frame(n_prompts: int) -> dict:

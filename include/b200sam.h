@@ -77,6 +77,38 @@ int b200sam_decode(b200sam_t* h, const void* emb, int emb_dtype, int B, const fl
 int b200sam_postprocess(b200sam_t* h, const float* lowres, int n_masks, int in_h, int in_w, int out_h, int out_w,
                         float* logits_out, uint8_t* mask_out, float threshold, void* stream);
 
+/* ---- the callers either side of the branch ---- */
+
+/* ResizeLongestSide(1024).apply_image (segment_anything/utils/transforms.py:27-34: torchvision resize of a PIL image
+ * = Pillow's antialiased 8-bit bilinear resample) + preprocess (inference.py:91-105 = chat.py:49-63: (x - mean) / std,
+ * zero pad bottom/right to 1024^2) + the callers' cast to the model dtype (inference.py:251-256), bit-exact.
+ * frames_rgb: (B,H,W,3) uint8 RGB; out: (B,3,1024,1024) in out_dtype (f32 / bf16 / f16).
+ * host_resize_hw (host, 2 ints, may be NULL) receives get_preprocess_shape(H, W) (transforms.py:103-113), the
+ * `resize_list` entry the callers pass on to postprocess_masks. */
+int b200sam_preprocess(b200sam_t* h, const uint8_t* frames_rgb, int B, int H, int W, void* out, int out_dtype,
+                       int* host_resize_hw, void* stream);
+
+/* text_hidden_fcs[0] (LISA.py:95-101: Linear(h,h) - ReLU - Linear(h,256)) evaluated on the [SEG] rows only, with the
+ * row selection of LISAForCausalLM.evaluate (LISA.py:457-485): mask = output_ids[:,1:] == seg_token_idx shifted by the
+ * 255 extra image-token positions.  hidden: (b,L,hdim) last hidden states in hidden_dtype, L >= 255 + T - 1;
+ * output_ids: (b,T) int64; w1 (hdim,hdim), b1 (hdim), w2 (256,hdim), b2 (256) all in w_dtype (f32 or bf16).
+ * emb_out: (max_rows,256) f32, rows [0,total) written in row-major [SEG] order; counts_out: device (b+1) ints =
+ * prompts per image, then the total (if the total exceeds max_rows only max_rows rows are written: the caller checks). */
+int b200sam_seg_project(b200sam_t* h, const void* hidden, int hidden_dtype, int b, int L, int hdim,
+                        const int64_t* output_ids, int T, int64_t seg_token_idx, const void* w1, const void* b1,
+                        const void* w2, const void* b2, int w_dtype, float* emb_out, int max_rows, int* counts_out,
+                        void* stream);
+
+/* Evaluation of train_ds.py::validate on the device (train_ds.py:662-709,761-796).  masks_left / masks_right:
+ * (P,H,W) u8 thresholded masks (b200sam_postprocess mask_out); taxonomy (P,4) f32; gt: (G,H,W) u8 ground-truth masks,
+ * prompt p is compared with gt[gt_index[p]] (gt_index == NULL: gt[p]).  The predicted mask is left (taxonomy argmax
+ * 0), right (1) or left|right (2,3).  counts_out: (P,3) int64 = {intersection, union, predicted area} in pixels, from
+ * which IoU = I / U and the reference's IoCM = I / (255 * area) follow; pred_out (nullable): (P,H,W) u8 gated mask
+ * with values {0,255}. */
+int b200sam_mask_metrics(b200sam_t* h, const uint8_t* masks_left, const uint8_t* masks_right, const float* taxonomy,
+                         const uint8_t* gt, const int* gt_index, int P, int H, int W, int64_t* counts_out,
+                         uint8_t* pred_out, void* stream);
+
 /* PromptEncoder.get_dense_pe (prompt_encoder.py:67-76): writes (1,256,64,64) f32. */
 int b200sam_dense_pe(b200sam_t* h, float* out, void* stream);
 
@@ -103,7 +135,10 @@ enum b200sam_profile_class {
   B200SAM_PC_DEC_GEMM = 12,
   B200SAM_PC_DEC_UPSCALE = 13,
   B200SAM_PC_POSTPROCESS = 14,
-  B200SAM_PC_COUNT = 15
+  B200SAM_PC_PREPROCESS = 15,
+  B200SAM_PC_SEG_PROJECT = 16,
+  B200SAM_PC_METRICS = 17,
+  B200SAM_PC_COUNT = 18
 };
 /* Measurement aid for bench.py: while enabled, every kernel launch of this handle is bracketed by a pair of CUDA
  * events on the launching stream.  b200sam_profile_read synchronises on them, writes the summed milliseconds and

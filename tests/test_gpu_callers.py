@@ -1,0 +1,159 @@
+"""GPU parity of the callers either side of the SAM branch against the CPU oracles and the
+golden outputs of the reference (tests/golden/make_golden_aux.py).  Integer / byte work is compared bit-exactly."""
+import glob
+import hashlib
+import os
+
+import numpy as np
+import pytest
+import torch
+from torch import nn
+
+from oracle import aux_oracle as A
+from oracle import preprocess_oracle as PO
+from oracle.synth import synth_image
+from tests import gpu_util as G
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.fixture(scope="module")
+def sam():
+    return G.pkg()._build_sam(256, 2, 4, [1], max_batch=1, max_prompts=8).cuda()
+
+
+PRE = sorted(glob.glob(os.path.join(GOLD, "preprocess_*.npz")))
+
+
+@pytest.mark.parametrize("path", PRE, ids=[os.path.basename(p)[11:-4] for p in PRE])
+def test_preprocess_bit_exact_against_reference_golden(sam, path):
+    g = np.load(path)
+    H, W = (int(v) for v in g["hw"])
+    img = synth_image(H, W, int(g["seed"]))
+    x, resize = sam.preprocess_frames(torch.from_numpy(img).cuda(), dtype=torch.float32)
+    assert resize == tuple(int(v) for v in g["resize"])
+    x = x[0].cpu().numpy()
+    assert np.array_equal(x.reshape(-1)[g["sample_idx"]], g["sample_val"])
+    assert _sha(x) == str(g["sha_f32"])                       # every bit of the reference's fp32 tensor
+    xb, _ = sam.preprocess_frames(torch.from_numpy(img).cuda(), dtype=torch.bfloat16)
+    assert _sha(xb[0].view(torch.int16).cpu().numpy()) == str(g["sha_bf16"])
+
+
+@pytest.mark.parametrize("hw", [(97, 211), (1024, 1000), (640, 1024), (3000, 1700), (1, 1024), (9, 5)])
+def test_preprocess_bit_exact_against_oracle_odd_sizes(sam, hw):
+    frames = np.stack([synth_image(hw[0], hw[1], 40 + i) for i in range(2)])
+    x, resize = sam.preprocess_frames(torch.from_numpy(frames).cuda(), dtype=torch.float32)
+    for i in range(2):
+        ref, r = PO.preprocess_frame(frames[i])
+        assert r == resize
+        assert np.array_equal(x[i].cpu().numpy(), ref)
+    xh, _ = sam.preprocess_frames(torch.from_numpy(frames).cuda(), dtype=torch.float16)
+    assert torch.equal(xh.cpu(), x.cpu().half())
+
+
+def test_preprocess_rejects_bad_input(sam):
+    with pytest.raises(ValueError):
+        sam.preprocess_frames(torch.zeros((4, 4, 4), dtype=torch.uint8, device="cuda"))
+    with pytest.raises(ValueError):
+        sam.preprocess_frames(torch.zeros((1, 8, 8, 3), dtype=torch.float32, device="cuda"))
+    out, resize = sam.preprocess_frames(torch.zeros((0, 8, 16, 3), dtype=torch.uint8, device="cuda"))
+    assert out.shape == (0, 3, 1024, 1024) and resize == (512, 1024)
+
+
+def _fcs(h, seed, dtype=torch.float32):
+    torch.manual_seed(seed)
+    return nn.ModuleList([nn.Sequential(nn.Linear(h, h), nn.ReLU(inplace=True), nn.Linear(h, 256), nn.Dropout(0.0))]
+                         ).to(dtype).cuda()
+
+
+def test_seg_project_against_reference_golden(sam):
+    g = np.load(os.path.join(GOLD, "aux_segproj.npz"))
+    fcs = _fcs(512, 0)
+    with torch.no_grad():
+        fcs[0][0].weight.copy_(torch.from_numpy(g["w_0_weight"]))
+        fcs[0][0].bias.copy_(torch.from_numpy(g["w_0_bias"]))
+        fcs[0][2].weight.copy_(torch.from_numpy(g["w_2_weight"]))
+        fcs[0][2].bias.copy_(torch.from_numpy(g["w_2_bias"]))
+    embs, offsets = sam.seg_project(torch.from_numpy(g["hidden"]).cuda(), torch.from_numpy(g["output_ids"]).cuda(),
+                                    int(g["seg_idx"]), fcs)
+    assert offsets == g["offsets"].tolist()
+    assert [tuple(e.shape) for e in embs] == [(3, 256), (0, 256), (1, 256)]
+    got = torch.cat(embs).cpu().numpy()
+    # fp32 weights and rows, fp32 accumulation: only the summation order differs from the reference's addmm
+    assert np.abs(got - g["pred"]).max() <= 2e-5 * np.abs(g["pred"]).max()
+
+
+@pytest.mark.parametrize("h,dtype", [(4096, torch.bfloat16), (5120, torch.bfloat16), (1024, torch.float16)])
+def test_seg_project_model_dtypes_and_many_prompts(sam, h, dtype):
+    """LLaVA-7B / 13B hidden sizes in the model dtype; 19 prompts over 4 images (> one 8-row chunk)."""
+    fcs = _fcs(h, 3, torch.float32 if dtype == torch.float16 else dtype)
+    g = torch.Generator().manual_seed(5)
+    b, T, seg = 4, 64, 32003
+    ids = torch.randint(0, 32000, (b, T), generator=g)
+    for bi, n in enumerate((7, 0, 11, 1)):
+        ids[bi, torch.randperm(T - 1, generator=g)[:n] + 1] = seg
+    hidden = torch.randn((b, 255 + T - 1 + 3, h), generator=g).to(dtype)     # L may exceed 255 + T - 1
+    embs, offsets = sam.seg_project(hidden.cuda(), ids.cuda(), seg, fcs, max_prompts=24)
+    w = [t.detach().float().cpu().numpy() for t in (fcs[0][0].weight, fcs[0][0].bias, fcs[0][2].weight, fcs[0][2].bias)]
+    ref, roff = A.seg_project(hidden.float().numpy(), ids.numpy(), seg, *w)
+    assert offsets == roff.tolist() == [0, 7, 7, 18, 19]
+    for e, r in zip(embs, ref):
+        assert e.shape == r.shape
+        if r.size:
+            assert np.abs(e.cpu().numpy() - r).max() <= 1e-4 * np.abs(np.concatenate(ref)).max()
+    with pytest.raises(RuntimeError, match="exceed"):
+        sam.seg_project(hidden.cuda(), ids.cuda(), seg, fcs, max_prompts=16)
+
+
+def test_mask_metrics_against_reference_golden(sam):
+    g = np.load(os.path.join(GOLD, "aux_metrics.npz"))
+    out = sam.mask_metrics(torch.from_numpy(g["left"]).cuda(), torch.from_numpy(g["right"]).cuda(),
+                           torch.from_numpy(g["tax"]).cuda(), torch.from_numpy(g["gt"]).cuda(), return_pred=True)
+    assert np.array_equal(out["pred"].cpu().numpy().astype(np.int32), g["pred"])
+    assert np.array_equal(out["iou"].cpu().numpy(), g["iou"])          # integer counts, one double division
+    assert np.array_equal(out["iocm"].cpu().numpy(), g["iocm"])
+
+
+@pytest.mark.parametrize("hw", [(1080, 1920), (135, 241), (7, 3)])
+def test_mask_metrics_counts_full_size_and_unaligned(sam, hw):
+    H, W = hw
+    rng = np.random.default_rng(3)
+    P = 5
+    left = (rng.random((P, H, W)) > 0.6).astype(np.uint8)
+    right = (rng.random((P, H, W)) > 0.7).astype(np.uint8) * 255        # any non-zero byte counts as set
+    gt = (rng.random((2, H, W)) > 0.5).astype(np.uint8)
+    tax = rng.random((P, 4)).astype(np.float32)
+    tax[0] = [0.3, 0.3, 0.1, 0.1]                                       # tie -> first index, like torch.argmax
+    gi = [0, 1, 1, 0, 1]
+    out = sam.mask_metrics(torch.from_numpy(left).cuda(), torch.from_numpy(right).cuda(), torch.from_numpy(tax).cuda(),
+                           torch.from_numpy(gt).cuda(), gt_index=gi, return_pred=True)
+    for p in range(P):
+        pred = A.gated_mask(left[p], right[p], tax[p])
+        assert np.array_equal(out["pred"][p].cpu().numpy(), pred.astype(np.uint8))
+        assert tuple(out["counts"][p].tolist()) == A.mask_counts(pred, gt[gi[p]])
+        iou, iocm = A.iou_iocm(pred, gt[gi[p]])
+        assert float(out["iou"][p]) == iou and float(out["iocm"][p]) == iocm
+    # size-independent property: counts are consistent, |P| + |G| = I + U
+    c = out["counts"].cpu().numpy()
+    garea = np.array([int(gt[i].astype(bool).sum()) for i in gi])
+    assert np.array_equal(c[:, 0] + c[:, 1], c[:, 2] + garea)
+
+
+def test_end_to_end_raw_frame_to_metrics(sam):
+    """Raw uint8 frame -> preprocess -> segment -> metrics, all on the device, runs and is self-consistent."""
+    from oracle import synth
+    sam2, arch, sd = G.build_sam_from_synth("tiny64", max_batch=1, max_prompts=2)
+    img = synth_image(270, 480, 9)
+    x, resize = sam2.preprocess_frames(torch.from_numpy(img).cuda(), dtype=torch.float32)
+    assert resize == (576, 1024)
+    seg = synth.make_seg_embeds(0, 2).cuda()
+    out = sam2.segment(x, [seg], [resize], [(270, 480)], threshold=0.0)
+    ml, mr = out["masks_left_packed"], out["masks_right_packed"]
+    m = sam2.mask_metrics(ml, mr, out["taxonomy"], ml | mr, return_pred=True)
+    assert torch.all(m["counts"][:, 0] == m["counts"][:, 2])            # pred is a subset of left|right
+    assert torch.all(m["iou"] <= 1.0)
