@@ -216,6 +216,53 @@ def workload_config(args, frames_per_step: int) -> dict:
 
 # ----------------------------------------------------------------------------------------------- GPU arm
 
+def measure_callers(torch, sam, dev, last_out, B, NP, iters=20):
+    """The HBM-bound kernels either side of the branch, each timed alone with CUDA events
+    and set against the measured copy bandwidth with ALGORITHMIC bytes: preprocess = raw u8 frame in + bf16 1024^2
+    tensor out; seg_project = one read of the two weight matrices; mask_metrics = three u8 masks in."""
+    from torch import nn
+    peaks = load_peaks()
+    H, W = ORIGINAL
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+
+    res = {}
+    g = torch.Generator().manual_seed(77)
+    raw = torch.randint(0, 256, (B, H, W, 3), dtype=torch.uint8, generator=g).to(dev)
+    ms = timed(lambda: sam.preprocess_frames(raw, torch.bfloat16))
+    by = B * (H * W * 3 + 3 * IMG * IMG * 2)
+    res["preprocess"] = {"ms": ms, "bytes": by, "gbs": by / ms / 1e6, "frac_hbm": by / ms / 1e6 / peaks["hbm_gbs"],
+                         "what": f"{B} raw {H}x{W} RGB u8 frames -> (B,3,1024,1024) bf16"}
+    hdim, T, seg = 4096, 64, 32003
+    fcs = nn.ModuleList([nn.Sequential(nn.Linear(hdim, hdim), nn.ReLU(), nn.Linear(hdim, OUT_CH), nn.Dropout(0.0))]
+                        ).to(torch.bfloat16).to(dev)
+    ids = torch.randint(0, 32000, (B, T), generator=g)
+    ids[:, T - NP:] = seg
+    ids = ids.to(dev)
+    hidden = torch.randn((B, 255 + T - 1, hdim), generator=g).to(torch.bfloat16).to(dev)
+    ms = timed(lambda: sam.seg_project(hidden, ids, seg, fcs, max_prompts=B * NP))
+    by = (hdim * hdim + OUT_CH * hdim) * 2
+    res["seg_project"] = {"ms": ms, "bytes": by, "gbs": by / ms / 1e6, "frac_hbm": by / ms / 1e6 / peaks["hbm_gbs"],
+                          "what": f"{B * NP} [SEG] rows, LLaVA-7B hidden {hdim}, bf16 weights (includes the count read-back)"}
+    ml, mr, tx = last_out["masks_left_packed"], last_out["masks_right_packed"], last_out["taxonomy"]
+    gt = (ml | mr).contiguous()
+    ms = timed(lambda: sam.mask_metrics(ml, mr, tx, gt))
+    by = 3 * ml.numel()
+    res["mask_metrics"] = {"ms": ms, "bytes": by, "gbs": by / ms / 1e6, "frac_hbm": by / ms / 1e6 / peaks["hbm_gbs"],
+                           "what": f"{ml.shape[0]} prompts x {H}x{W} u8 masks (left, right, gt)"}
+    return res
+
+
 def read_profile(lib, handle):
     ms = (C.c_float * len(PC_NAMES))()
     cnt = (C.c_int64 * len(PC_NAMES))()
@@ -293,7 +340,7 @@ def run_gpu_arm(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
-    run_steps(args.steps, resident)
+    out = run_steps(args.steps, resident)
     ev1.record()
     barrier()
     ms_total = ev0.elapsed_time(ev1)
@@ -374,6 +421,8 @@ def run_gpu_arm(args):
                     "whole_step_tflops": fl["total"] * B / (ms_total / args.steps * 1e-3) / 1e12,
                     "whole_step_frac": fl["total"] * B / (ms_total / args.steps * 1e-3) / 1e12 / peaks["bf16_sustained"]}
 
+    aux = measure_callers(torch, sam, dev, out, B, NP) if (rank == 0 and world == 1) else None
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         sd = {k: v.detach().float().cpu() for k, v in sam.state_dict().items()}
@@ -389,7 +438,7 @@ def run_gpu_arm(args):
             "config": workload_config(args, B),
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-            "kernels": kernels,
+            "kernels": kernels, "callers": aux,
         }
         print(json.dumps(line))
     if world > 1:
