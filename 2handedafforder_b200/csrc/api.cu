@@ -357,17 +357,23 @@ int alloc_workspace(b200sam_t* h) {
   CU(dalloc(h, &h->emb_in, B * kTokens * 256));
   if (P > 0) {
     CU(dalloc(h, &h->prompt_frame, P));
-    CU(dalloc(h, &h->keys, P * kTokens * 256));
-    CU(dalloc(h, &h->kv, P * kTokens * 256));
-    CU(dalloc(h, &h->qimg, P * kTokens * 128));
-    CU(dalloc(h, &h->oimg, P * kTokens * 128));
-    CU(dalloc(h, &h->up1, P * 16384 * 64));
-    CU(dalloc(h, &h->tok_state, P * 6 * 256));
-    CU(dalloc(h, &h->tok_pe, P * 6 * 256));
-    CU(dalloc(h, &h->tok_q, P * 6 * 128));
-    CU(dalloc(h, &h->tok_o, P * 6 * 128));
-    CU(dalloc(h, &h->tok_kv, P * 6 * 256));
-    CU(dalloc(h, &h->hyper, P * 32));
+    for (int i = 0; i < 2; ++i) {
+      DecWorkspace& w = h->dws[i];
+      CU(dalloc(h, &w.keys, P * kTokens * 256));
+      CU(dalloc(h, &w.kv, P * kTokens * 256));
+      CU(dalloc(h, &w.qimg, P * kTokens * 128));
+      CU(dalloc(h, &w.oimg, P * kTokens * 128));
+      CU(dalloc(h, &w.up1, P * 16384 * 64));
+      CU(dalloc(h, &w.tok_state, P * 6 * 256));
+      CU(dalloc(h, &w.tok_pe, P * 6 * 256));
+      CU(dalloc(h, &w.tok_q, P * 6 * 128));
+      CU(dalloc(h, &w.tok_o, P * 6 * 128));
+      CU(dalloc(h, &w.tok_kv, P * 6 * 256));
+      CU(dalloc(h, &w.hyper, P * 32));
+    }
+    CU(cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
   }
   return 0;
 }
@@ -454,6 +460,9 @@ extern "C" void b200sam_destroy(b200sam_t* h) {
   {
     DeviceGuard g(h->device);
     for (void* p : h->owned) cudaFree(p);
+    if (h->side_stream) cudaStreamDestroy(h->side_stream);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
     for (auto& ev : h->prof_ev) {
       cudaEventDestroy(ev.first);
       cudaEventDestroy(ev.second);
@@ -747,10 +756,11 @@ namespace {
 int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, int P, float* lowres, float* iou,
                 float* tax, cudaStream_t s) {
   const DecSide& d = h->side[sidx];
+  const DecWorkspace& w = h->dws[sidx];   // one workspace per side: the two decoders run concurrently
   const long rows = (long)P * kTokens;
   // src = image_embeddings (repeat_interleave per prompt) + dense_prompt_embeddings      (mask_decoder.py:143-144)
   h->pc = B200SAM_PC_DEC_ELEMENTWISE;
-  KL(launch_keys_init(emb_tok, h->no_mask, h->prompt_frame, P, h->keys, s));
+  KL(launch_keys_init(emb_tok, h->no_mask, h->prompt_frame, P, w.keys, s));
   for (int l = 0; l < 2; ++l) {
     const DecLayer& L = d.layer[l];
     TokStageA a;
@@ -763,9 +773,9 @@ int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, 
     a.n1b = L.n1b;
     a.t2i_qw = L.t2i.qw;
     a.t2i_qb = L.t2i.qb;
-    a.tok_state = h->tok_state;
-    a.tok_pe = h->tok_pe;
-    a.tok_q = h->tok_q;
+    a.tok_state = w.tok_state;
+    a.tok_pe = w.tok_pe;
+    a.tok_q = w.tok_q;
     h->pc = B200SAM_PC_DEC_TOKEN;
     KL(launch_dec_stage_a(a, P, s));
     {
@@ -773,64 +783,64 @@ int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, 
       e.addend = L.kv_tab;
       e.ld_add = 256;
       e.add_mod = kTokens;
-      e.out = h->kv;
+      e.out = w.kv;
       e.ld_out = 256;
       h->pc = B200SAM_PC_DEC_GEMM;
-      if (int r = run_gemm(h, true, GM_F32, h->keys, 256, L.kv_w, 256, rows, 256, 256, e, s)) return r;
+      if (int r = run_gemm(h, true, GM_F32, w.keys, 256, L.kv_w, 256, rows, 256, 256, e, s)) return r;
     }
     h->pc = B200SAM_PC_DEC_TOKEN;
-    KL(launch_dec_t2i(h->tok_q, h->kv, h->tok_o, P, s));
+    KL(launch_dec_t2i(w.tok_q, w.kv, w.tok_o, P, s));
     TokStageB b;
     b.t2i_ow = L.t2i.ow; b.t2i_ob = L.t2i.ob;
     b.n2g = L.n2g; b.n2b = L.n2b; b.n3g = L.n3g; b.n3b = L.n3b;
     b.mlp1w = L.mlp1w; b.mlp1b = L.mlp1b; b.mlp2w = L.mlp2w; b.mlp2b = L.mlp2b;
     b.i2t_kw = L.i2t.kw; b.i2t_kb = L.i2t.kb; b.i2t_vw = L.i2t.vw; b.i2t_vb = L.i2t.vb;
-    b.tok_o = h->tok_o;
-    b.tok_pe = h->tok_pe;
-    b.tok_state = h->tok_state;
-    b.tok_kv = h->tok_kv;
+    b.tok_o = w.tok_o;
+    b.tok_pe = w.tok_pe;
+    b.tok_state = w.tok_state;
+    b.tok_kv = w.tok_kv;
     KL(launch_dec_stage_b(b, P, s));
     {
       GemmEpi e;   // image->token queries
       e.addend = L.q_tab;
       e.ld_add = 128;
       e.add_mod = kTokens;
-      e.out = h->qimg;
+      e.out = w.qimg;
       e.ld_out = 128;
       h->pc = B200SAM_PC_DEC_GEMM;
-      if (int r = run_gemm(h, true, GM_F32, h->keys, 256, L.i2t.qw, 256, rows, 128, 256, e, s)) return r;
+      if (int r = run_gemm(h, true, GM_F32, w.keys, 256, L.i2t.qw, 256, rows, 128, 256, e, s)) return r;
     }
     h->pc = B200SAM_PC_DEC_TOKEN;
-    KL(launch_dec_i2t(h->qimg, h->tok_kv, h->oimg, P, s));
+    KL(launch_dec_i2t(w.qimg, w.tok_kv, w.oimg, P, s));
     {
       GemmEpi e;   // keys = norm4(keys + out_proj(attn))                                  (transformer.py:176-180)
       e.bias = L.i2t.ob;
-      e.addend = h->keys;
+      e.addend = w.keys;
       e.ld_add = 256;
-      e.out = h->keys;
+      e.out = w.keys;
       e.ld_out = 256;
       e.ln_g = L.n4g;
       e.ln_b = L.n4b;
       e.ln_eps = 1e-5f;
       h->pc = B200SAM_PC_DEC_GEMM;
-      if (int r = run_gemm(h, true, GM_LN, h->oimg, 128, L.i2t.ow, 128, rows, 256, 128, e, s)) return r;
+      if (int r = run_gemm(h, true, GM_LN, w.oimg, 128, L.i2t.ow, 128, rows, 256, 128, e, s)) return r;
     }
   }
   // final token->image attention (transformer.py:100-104)
   h->pc = B200SAM_PC_DEC_TOKEN;
-  KL(launch_dec_stage_q(h->tok_state, h->tok_pe, d.final_attn.qw, d.final_attn.qb, h->tok_q, P, s));
+  KL(launch_dec_stage_q(w.tok_state, w.tok_pe, d.final_attn.qw, d.final_attn.qb, w.tok_q, P, s));
   {
     GemmEpi e;
     e.addend = d.final_kv_tab;
     e.ld_add = 256;
     e.add_mod = kTokens;
-    e.out = h->kv;
+    e.out = w.kv;
     e.ld_out = 256;
     h->pc = B200SAM_PC_DEC_GEMM;
-    if (int r = run_gemm(h, true, GM_F32, h->keys, 256, d.final_kv_w, 256, rows, 256, 256, e, s)) return r;
+    if (int r = run_gemm(h, true, GM_F32, w.keys, 256, d.final_kv_w, 256, rows, 256, 256, e, s)) return r;
   }
   h->pc = B200SAM_PC_DEC_TOKEN;
-  KL(launch_dec_t2i(h->tok_q, h->kv, h->tok_o, P, s));
+  KL(launch_dec_t2i(w.tok_q, w.kv, w.tok_o, P, s));
   TokHeads th;
   th.ow = d.final_attn.ow; th.ob = d.final_attn.ob; th.nfg = d.nfg; th.nfb = d.nfb;
   for (int j = 0; j < 3; ++j) {
@@ -838,9 +848,9 @@ int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, 
     th.iou_w[j] = d.iou_w[j]; th.iou_b[j] = d.iou_b[j];
     th.tax_w[j] = d.tax_w[j]; th.tax_b[j] = d.tax_b[j];
   }
-  th.tok_state = h->tok_state;
-  th.tok_o = h->tok_o;
-  th.hyper = h->hyper;
+  th.tok_state = w.tok_state;
+  th.tok_o = w.tok_o;
+  th.hyper = w.hyper;
   th.iou_out = iou;
   th.tax_out = d.has_taxonomy ? tax : nullptr;
   KL(launch_dec_heads(th, P, s));
@@ -852,16 +862,16 @@ int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, 
       e.ln_g = d.up1_lng;
       e.ln_b = d.up1_lnb;
       e.ln_eps = 1e-6f;
-      e.out = h->up1;
+      e.out = w.up1;
       h->pc = B200SAM_PC_DEC_UPSCALE;
-      if (int r = run_gemm(h, true, GM_UPS1, h->keys, 256, d.up0_w, 256, rows, 256, 256, e, s)) return r;
+      if (int r = run_gemm(h, true, GM_UPS1, w.keys, 256, d.up0_w, 256, rows, 256, 256, e, s)) return r;
     }
     {
       GemmEpi e;
       e.bias = d.up3_b;
-      e.hyper = h->hyper;
+      e.hyper = w.hyper;
       e.out = lowres;
-      if (int r = run_gemm(h, true, GM_UPS2, h->up1, 64, d.up3_w, 64, (long)P * 16384, 128, 64, e, s)) return r;
+      if (int r = run_gemm(h, true, GM_UPS2, w.up1, 64, d.up3_w, 64, (long)P * 16384, 128, 64, e, s)) return r;
     }
   }
   return 0;
@@ -900,10 +910,24 @@ extern "C" int b200sam_decode(b200sam_t* h, const void* emb, int emb_dtype, int 
     for (int p = host_prompt_offsets[i]; p < host_prompt_offsets[i + 1]; ++p) pf[p] = i;
   // small pageable H2D copy, stream ordered: returns once the data is staged, so `pf` may go out of scope
   CU(cudaMemcpyAsync(h->prompt_frame, pf.data(), (size_t)P * sizeof(int), cudaMemcpyHostToDevice, s));
-  if (lowres_left || iou_left || taxonomy)
+  const bool left = lowres_left || iou_left || taxonomy, right = lowres_right || iou_right;
+  // The two mask decoders are independent (mask_decoder_left / _right, LISA.py:505-530) and individually too small
+  // to fill the GPU: the right one is forked onto the handle's side stream and joined back into the caller's
+  // stream (event fork/join: no host sync, graph-capturable).  The per-launch profile needs one stream.
+  const bool fork = left && right && !h->prof_on && h->side_stream;
+  if (fork) {
+    CU(cudaEventRecord(h->ev_fork, s));
+    CU(cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
+  }
+  if (left)
     if (int r = decode_side(h, 0, emb_tok, seg_embeds, P, lowres_left, iou_left, taxonomy, s)) return r;
-  if (lowres_right || iou_right)
-    if (int r = decode_side(h, 1, emb_tok, seg_embeds, P, lowres_right, iou_right, nullptr, s)) return r;
+  if (right)
+    if (int r = decode_side(h, 1, emb_tok, seg_embeds, P, lowres_right, iou_right, nullptr, fork ? h->side_stream : s))
+      return r;
+  if (fork) {
+    CU(cudaEventRecord(h->ev_join, h->side_stream));
+    CU(cudaStreamWaitEvent(s, h->ev_join, 0));
+  }
   return 0;
 }
 

@@ -64,6 +64,21 @@ struct DecSide {
   const float* tax_b[3];
 };
 
+// decoder workspace of ONE side, sized for max_prompts
+struct DecWorkspace {
+  float* keys = nullptr;             // (P*4096, 256)
+  float* kv = nullptr;               // (P*4096, 256)  [k | v] of the image side
+  float* qimg = nullptr;             // (P*4096, 128)
+  float* oimg = nullptr;             // (P*4096, 128)
+  float* up1 = nullptr;              // (P*16384, 64)
+  float* tok_state = nullptr;        // (P, 6, 256) queries
+  float* tok_pe = nullptr;           // (P, 6, 256) initial tokens (= query PE)
+  float* tok_q = nullptr;            // (P, 6, 128) projected queries for t2i
+  float* tok_o = nullptr;            // (P, 6, 128) t2i attention output before out_proj
+  float* tok_kv = nullptr;           // (P, 6, 256) [k | v] of the tokens for i2t
+  float* hyper = nullptr;            // (P, 32) mask-0 hypernetwork output
+};
+
 }  // namespace bsam
 
 struct b200sam {
@@ -112,17 +127,9 @@ struct b200sam {
   float* emb_tok = nullptr;          // (B*4096, 256) fp32 image embedding, token-major
   // decoder workspace
   int* prompt_frame = nullptr;       // (P) device
-  float* keys = nullptr;             // (P*4096, 256)
-  float* kv = nullptr;               // (P*4096, 256)  [k | v] of the image side
-  float* qimg = nullptr;             // (P*4096, 128)
-  float* oimg = nullptr;             // (P*4096, 128)
-  float* up1 = nullptr;              // (P*16384, 64)
-  float* tok_state = nullptr;        // (P, 6, 256) queries
-  float* tok_pe = nullptr;           // (P, 6, 256) initial tokens (= query PE)
-  float* tok_q = nullptr;            // (P, 6, 128) projected queries for t2i
-  float* tok_o = nullptr;            // (P, 6, 128) t2i attention output before out_proj
-  float* tok_kv = nullptr;           // (P, 6, 256) [k | v] of the tokens for i2t
-  float* hyper = nullptr;            // (P, 32) mask-0 hypernetwork output
+  bsam::DecWorkspace dws[2];         // one per mask decoder (left / right run concurrently)
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   float* emb_in = nullptr;           // (B*4096, 256) staging when decode() is given an external embedding
 
   // callers either side of the branch (aux.cu); grown on first use / new input size, never on a repeated call
