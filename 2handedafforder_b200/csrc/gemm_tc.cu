@@ -353,6 +353,8 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
 
   const bool has_add = MODE == GM_F32 && e.addend != nullptr;
   float4 nxt[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   auto fetch = [&](int c) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -362,9 +364,17 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
       }
     }
   };
+  auto bias4 = [&](int c) {
+    return (MODE != GM_F16 && e.bias) ? __ldg(reinterpret_cast<const float4*>(e.bias + n0 + c * 32 + cg * 4))
+                                      : make_float4(0.f, 0.f, 0.f, 0.f);
+  };
   if (has_add && c_lo < c_hi) fetch(c_lo);
+  float4 b_nxt = c_lo < c_hi ? bias4(c_lo) : make_float4(0.f, 0.f, 0.f, 0.f);
   wait_acc();
-  float v[32];
+  // Software pipeline, one chunk deep: the accumulator registers are dead as soon as they sit in the transposition
+  // tile, so the tcgen05.ld of chunk c+1 (and its bias / addend loads) is in flight while chunk c is finished.
+  uint32_t v[32];
+  if (c_lo < c_hi) tmem_ld_32x32(src.taddr + c_lo * 32, v);
   for (int c = c_lo; c < c_hi; ++c) {
     float4 cur[8];
     if (has_add) {
@@ -372,13 +382,18 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
       for (int i = 0; i < 8; ++i) cur[i] = nxt[i];
       if (c + 1 < c_hi) fetch(c + 1);
     }
-    src.load(c, v);
+    tmem_wait_ld();
 #pragma unroll
     for (int g = 0; g < 8; ++g)
-      stage[lane * 8 + (g ^ (lane & 7))] = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+      stage[lane * 8 + (g ^ (lane & 7))] =
+          make_float4(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]), __uint_as_float(v[4 * g + 2]),
+                      __uint_as_float(v[4 * g + 3]));
     __syncwarp();
-    float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (MODE != GM_F16 && e.bias) b4 = __ldg(reinterpret_cast<const float4*>(e.bias + n0 + c * 32 + cg * 4));
+    const float4 b4 = b_nxt;
+    if (c + 1 < c_hi) {
+      tmem_ld_32x32(src.taddr + (c + 1) * 32, v);
+      b_nxt = bias4(c + 1);
+    }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int r = i * 4 + sub;
@@ -387,7 +402,7 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
       x.y += b4.y;
       x.z += b4.z;
       x.w += b4.w;
-      if (orow[i] < 0) continue;
+      const bool st = orow[i] >= 0;   // predicated stores (no branch: the 8 row slices interleave)
       const long col = n0 + c * 32 + cg * 4;
       if constexpr (MODE == GM_F32) {
         if (has_add) {
@@ -396,13 +411,13 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
           x.z += cur[i].z;
           x.w += cur[i].w;
         }
-        *reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + orow[i] * (long)e.ld_out + col) = x;
+        if (st) *reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + orow[i] * (long)e.ld_out + col) = x;
       } else if constexpr (MODE == GM_F16) {
         __half2 h0 = __floats2half2_rn(x.x, x.y), h1 = __floats2half2_rn(x.z, x.w);
         uint2 t;
         t.x = *reinterpret_cast<uint32_t*>(&h0);
         t.y = *reinterpret_cast<uint32_t*>(&h1);
-        *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(e.out) + orow[i] * (long)e.ld_out + col + out_off) = t;
+        if (st) *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(e.out) + orow[i] * (long)e.ld_out + col + out_off) = t;
       } else {
         if constexpr (MODE == GM_BIAS_GELU_BF16) {
           x.x = gelu_erf_fast(x.x);
@@ -413,7 +428,7 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
         uint2 t;
         t.x = pack_bf16(x.x, x.y);
         t.y = pack_bf16(x.z, x.w);
-        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(e.out) + orow[i] * (long)e.ld_out + col) = t;
+        if (st) *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(e.out) + orow[i] * (long)e.ld_out + col) = t;
       }
     }
     __syncwarp();
