@@ -92,6 +92,36 @@ __device__ __forceinline__ void store4<__half>(__half* p, float a, float b, floa
   *reinterpret_cast<uint2*>(p) = v;
 }
 
+// Horizontal pass of one (output column, channel) down `nrows` input rows with an N-tap window held in registers.
+template <int N>
+__device__ __forceinline__ void hpass_col(const uint8_t* __restrict__ col, const int* __restrict__ k,
+                                          uint8_t* __restrict__ dst, int nrows, int W) {
+  int kk[N];
+#pragma unroll
+  for (int j = 0; j < N; ++j) kk[j] = k[j];
+  const long pitch = (long)W * 3;
+  int r = 0;
+  for (; r + 1 < nrows; r += 2) {                  // two rows per trip: 2N independent loads in flight
+    const uint8_t* r0p = col + r * pitch;
+    const uint8_t* r1p = r0p + pitch;
+    int a0 = 1 << (kResamplePrecisionBits - 1), a1 = a0;
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+      a0 += (int)r0p[j * 3] * kk[j];
+      a1 += (int)r1p[j * 3] * kk[j];
+    }
+    dst[r * kTileW * 3] = clip8(a0);
+    dst[(r + 1) * kTileW * 3] = clip8(a1);
+  }
+  if (r < nrows) {
+    const uint8_t* r0p = col + r * pitch;
+    int a0 = 1 << (kResamplePrecisionBits - 1);
+#pragma unroll
+    for (int j = 0; j < N; ++j) a0 += (int)r0p[j * 3] * kk[j];
+    dst[r * kTileW * 3] = clip8(a0);
+  }
+}
+
 struct PreArgs {
   const uint8_t* in;     // (B, H, W, 3)
   int H, W, new_h, new_w;
@@ -121,21 +151,38 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_kernel(PreArgs a, T* _
       nrows = a.ylo[y0 + th - 1] + a.ycnt[y0 + th - 1] - r0;
     }
     const uint8_t* src = a.in + b * (long)a.H * a.W * 3;
-    const int items = nrows * tw * 3;
-    for (int i = threadIdx.x; i < items; i += kPreThreads) {
-      const int c = i % 3, x = (i / 3) % tw, r = i / (3 * tw);
-      const uint8_t* row = src + ((long)(r0 + r) * a.W) * 3 + c;
-      uint8_t v;
+    // one thread = one (output column, channel) of the tile; its window and fixed-point weights stay in registers
+    // while it walks down the input rows (adjacent threads read adjacent bytes of the interleaved RGB row)
+    for (int i = threadIdx.x; i < tw * 3; i += kPreThreads) {
+      const int x = i / 3, c = i - x * 3;
+      uint8_t* dst = tile + x * 3 + c;
       if (a.ident_x) {
-        v = row[(x0 + x) * 3];
+        const uint8_t* col = src + (long)r0 * a.W * 3 + (x0 + x) * 3 + c;
+        for (int r = 0; r < nrows; ++r) dst[r * kTileW * 3] = col[(long)r * a.W * 3];
       } else {
         const int lo = a.xlo[x0 + x], n = a.xcnt[x0 + x];
         const int* k = a.xkk + (long)(x0 + x) * a.kx;
-        int acc = 1 << (kResamplePrecisionBits - 1);
-        for (int j = 0; j < n; ++j) acc += (int)row[(lo + j) * 3] * k[j];
-        v = clip8(acc);
+        const uint8_t* col = src + (long)r0 * a.W * 3 + lo * 3 + c;
+        if (n <= 8) {
+          switch (n) {
+            case 1: hpass_col<1>(col, k, dst, nrows, a.W); break;
+            case 2: hpass_col<2>(col, k, dst, nrows, a.W); break;
+            case 3: hpass_col<3>(col, k, dst, nrows, a.W); break;
+            case 4: hpass_col<4>(col, k, dst, nrows, a.W); break;
+            case 5: hpass_col<5>(col, k, dst, nrows, a.W); break;
+            case 6: hpass_col<6>(col, k, dst, nrows, a.W); break;
+            case 7: hpass_col<7>(col, k, dst, nrows, a.W); break;
+            default: hpass_col<8>(col, k, dst, nrows, a.W); break;
+          }
+        } else {
+          for (int r = 0; r < nrows; ++r) {
+            const uint8_t* row = col + (long)r * a.W * 3;
+            int acc = 1 << (kResamplePrecisionBits - 1);
+            for (int j = 0; j < n; ++j) acc += (int)row[j * 3] * k[j];
+            dst[r * kTileW * 3] = clip8(acc);
+          }
+        }
       }
-      tile[(r * kTileW + x) * 3 + c] = v;
     }
   }
   __syncthreads();
@@ -274,7 +321,7 @@ __global__ void __launch_bounds__(1024) seg_scan_kernel(const int64_t* __restric
   }
 }
 
-constexpr int kFcRows = 8, kFcWarps = 8;
+constexpr int kFcRows = 8, kFcWarps = 16;
 
 __device__ __forceinline__ void load8(const float* p, float (&w)[8]) {
   const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
@@ -293,7 +340,7 @@ __device__ __forceinline__ float ld_scalar(const float* p, long i) { return __ld
 __device__ __forceinline__ float ld_scalar(const __nv_bfloat16* p, long i) { return __bfloat162float(p[i]); }
 
 // y[p, j] = act(bias[j] + sum_k x[row(p), k] * Wt[j, k]) for the (device-side) n = *n_ptr gathered rows.
-// grid (ctas, ceil(max_rows / 8)); block = 8 warps; the 8 input rows of the chunk are staged once in shared memory as
+// grid (ctas, ceil(max_rows / 8)); block = 16 warps; the 8 input rows of the chunk are staged once in shared memory as
 // fp32 (8 * K * 4 bytes), each warp then streams whole weight rows with 16-byte loads (the kernel is bound by the
 // one read of W: K * N * sizeof(W) bytes) and reduces 8 dot products by warp shuffle.
 template <typename WT>
@@ -325,6 +372,7 @@ rows_fc_kernel(const void* __restrict__ x, int x_dtype, long x_ld, const int* __
 #pragma unroll
     for (int r = 0; r < kFcRows; ++r) acc[r] = 0.f;
     const WT* wrow = Wt + (long)j * K;
+#pragma unroll 4                                   // 4 x 16-byte weight loads in flight per lane
     for (int k = lane * 8; k < K; k += 256) {
       float w[8];
       load8(wrow + k, w);

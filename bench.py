@@ -224,7 +224,12 @@ def measure_callers(torch, sam, dev, last_out, B, NP, iters=20):
     peaks = load_peaks()
     H, W = ORIGINAL
 
-    def timed(fn):
+    _lib = importlib.import_module(PKG + "._lib")
+    lib, handle = _lib.load(), sam._handle
+
+    def timed(fn, cls):
+        """(ms per call through the Python API, ms of this library's kernels alone per call: CUDA events around
+        every launch of the class, b200sam_profile_*)."""
         for _ in range(3):
             fn()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -234,15 +239,25 @@ def measure_callers(torch, sam, dev, last_out, B, NP, iters=20):
             fn()
         e1.record()
         torch.cuda.synchronize()
-        return e0.elapsed_time(e1) / iters
+        api_ms = e0.elapsed_time(e1) / iters
+        lib.b200sam_profile_enable(handle, 1)
+        for _ in range(iters):
+            fn()
+        torch.cuda.synchronize()
+        prof = read_profile(lib, handle)
+        lib.b200sam_profile_enable(handle, 0)
+        return api_ms, prof[cls][0] / iters
+
+    def entry(api_ms, k_ms, by, what):
+        return {"ms": k_ms, "api_ms": api_ms, "bytes": by, "gbs": by / k_ms / 1e6,
+                "frac_hbm": by / k_ms / 1e6 / peaks["hbm_gbs"], "what": what}
 
     res = {}
     g = torch.Generator().manual_seed(77)
     raw = torch.randint(0, 256, (B, H, W, 3), dtype=torch.uint8, generator=g).to(dev)
-    ms = timed(lambda: sam.preprocess_frames(raw, torch.bfloat16))
-    by = B * (H * W * 3 + 3 * IMG * IMG * 2)
-    res["preprocess"] = {"ms": ms, "bytes": by, "gbs": by / ms / 1e6, "frac_hbm": by / ms / 1e6 / peaks["hbm_gbs"],
-                         "what": f"{B} raw {H}x{W} RGB u8 frames -> (B,3,1024,1024) bf16"}
+    a, k = timed(lambda: sam.preprocess_frames(raw, torch.bfloat16), "preprocess")
+    res["preprocess"] = entry(a, k, B * (H * W * 3 + 3 * IMG * IMG * 2),
+                              f"{B} raw {H}x{W} RGB u8 frames -> (B,3,1024,1024) bf16")
     hdim, T, seg = 4096, 64, 32003
     fcs = nn.ModuleList([nn.Sequential(nn.Linear(hdim, hdim), nn.ReLU(), nn.Linear(hdim, OUT_CH), nn.Dropout(0.0))]
                         ).to(torch.bfloat16).to(dev)
@@ -250,16 +265,14 @@ def measure_callers(torch, sam, dev, last_out, B, NP, iters=20):
     ids[:, T - NP:] = seg
     ids = ids.to(dev)
     hidden = torch.randn((B, 255 + T - 1, hdim), generator=g).to(torch.bfloat16).to(dev)
-    ms = timed(lambda: sam.seg_project(hidden, ids, seg, fcs, max_prompts=B * NP))
-    by = (hdim * hdim + OUT_CH * hdim) * 2
-    res["seg_project"] = {"ms": ms, "bytes": by, "gbs": by / ms / 1e6, "frac_hbm": by / ms / 1e6 / peaks["hbm_gbs"],
-                          "what": f"{B * NP} [SEG] rows, LLaVA-7B hidden {hdim}, bf16 weights (includes the count read-back)"}
+    a, k = timed(lambda: sam.seg_project(hidden, ids, seg, fcs, max_prompts=B * NP), "seg_project")
+    res["seg_project"] = entry(a, k, (hdim * hdim + OUT_CH * hdim) * 2,
+                               f"{B * NP} [SEG] rows, LLaVA-7B hidden {hdim}, bf16 weights (scan + 2 FC kernels; "
+                               "api_ms includes the count read-back)")
     ml, mr, tx = last_out["masks_left_packed"], last_out["masks_right_packed"], last_out["taxonomy"]
     gt = (ml | mr).contiguous()
-    ms = timed(lambda: sam.mask_metrics(ml, mr, tx, gt))
-    by = 3 * ml.numel()
-    res["mask_metrics"] = {"ms": ms, "bytes": by, "gbs": by / ms / 1e6, "frac_hbm": by / ms / 1e6 / peaks["hbm_gbs"],
-                           "what": f"{ml.shape[0]} prompts x {H}x{W} u8 masks (left, right, gt)"}
+    a, k = timed(lambda: sam.mask_metrics(ml, mr, tx, gt), "metrics")
+    res["mask_metrics"] = entry(a, k, 3 * ml.numel(), f"{ml.shape[0]} prompts x {H}x{W} u8 masks (left, right, gt)")
     return res
 
 

@@ -1,0 +1,35 @@
+"""GPU check of the clip path (2handedafforder_b200/clip.py) with the real kernels on one rank: what segment_clip
+collects equals direct B200Sam.segment calls, for a ragged clip with a variable number of [SEG] prompts per frame
+(the multi-rank exchange itself is covered by tests/test_clip_gloo.py on CPU and by `bench.py --gpus N`)."""
+import importlib
+
+import pytest
+import torch
+
+from oracle import synth
+from tests import gpu_util as G
+
+pytestmark = pytest.mark.gpu
+
+
+def test_clip_equals_direct_segment_calls():
+    clip = importlib.import_module(G.PKG + ".clip")
+    sam, arch, sd = G.build_sam_from_synth("tiny64", max_batch=2, max_prompts=6)
+    n_frames, mb = 5, 2
+    frames = synth.make_frames(0, n_frames).cuda()
+    counts = [2, 0, 3, 1, 2]                       # frame 1 has no [SEG] at all (chat.py:227)
+    segs = [synth.make_seg_embeds(i, 3)[:counts[i]].cuda() for i in range(n_frames)]
+    resize, original = (576, 1024), (135, 240)
+    seen = []
+    res = clip.segment_clip(sam.segment, lambda lo, hi: (frames[lo:hi], segs[lo:hi]), n_frames, resize, original,
+                            micro_batch=mb, max_prompts_per_frame=3,
+                            sink=lambda f, ml, mr, tx, il, ir: seen.append((f, ml.shape[0])))
+    torch.cuda.synchronize()
+    assert res.frames_done == n_frames and seen == [(i, counts[i]) for i in range(n_frames)]
+    for i in range(n_frames):
+        ref = sam.segment(frames[i:i + 1], [segs[i]], [resize], [original], threshold=0.0)
+        assert res.masks_left[i].shape == (counts[i], *original)
+        assert torch.equal(res.masks_left[i], ref["masks_left"][0])
+        assert torch.equal(res.masks_right[i], ref["masks_right"][0])
+        assert torch.equal(res.taxonomy[i], ref["taxonomy"])
+        assert torch.equal(res.iou_left[i], ref["iou_left"]) and torch.equal(res.iou_right[i], ref["iou_right"])
