@@ -187,3 +187,69 @@ class _NullCtx:
 
     def __exit__(self, *a):
         return False
+
+
+class HostPipeline:
+    """Host-to-host segmentation of a stream of micro-batches with the PCIe copies off the critical path.
+
+    The reference moves one image at a time (`.cuda()` before `evaluate`, `.cpu().numpy()` after,
+    inference.py:247-297) and so serialises copy - compute - copy.  Here micro-batch k+1 is uploaded from pinned host
+    memory and the masks of micro-batch k-1 are downloaded on two copy streams while the kernels of micro-batch k run;
+    two input and two output slots, event-ordered, no host synchronisation inside the loop.
+
+        pipe = HostPipeline(sam.segment, batch, prompts_per_frame, resize, original, device)
+        for k in range(n): pipe.submit(host_frames_k, host_seg_k)   # pinned (B,3,1024,1024) / (B*NP,256)
+        pipe.flush()                                                 # results of submit k are in pipe.host_out[k % 2]
+    """
+
+    def __init__(self, segment_fn, batch: int, prompts_per_frame: int, resize, original, device: torch.device,
+                 frame_dtype: torch.dtype = torch.bfloat16, threshold: float = 0.0):
+        self.segment_fn, self.B, self.NP = segment_fn, int(batch), int(prompts_per_frame)
+        self.resize, self.original, self.device, self.threshold = resize, original, device, threshold
+        P, (H, W) = self.B * self.NP, (int(original[0]), int(original[1]))
+        self.up = torch.cuda.Stream(device=device)       # H2D and D2H run on their own streams (two copy engines)
+        self.down = torch.cuda.Stream(device=device)
+        self.d_frames = [torch.empty((self.B, 3, 1024, 1024), dtype=frame_dtype, device=device) for _ in range(2)]
+        self.d_seg = [torch.empty((P, OUT_CH), dtype=torch.float32, device=device) for _ in range(2)]
+        self.host_out = [{"masks": torch.empty((2, P, H, W), dtype=torch.uint8).pin_memory(),
+                          "heads": torch.empty((3, P, 4), dtype=torch.float32).pin_memory()} for _ in range(2)]
+        self.up_done = [torch.cuda.Event() for _ in range(2)]        # upload of slot finished
+        self.in_free = [torch.cuda.Event() for _ in range(2)]        # kernels that read the input slot finished
+        self.down_done = [torch.cuda.Event() for _ in range(2)]      # download into host_out[slot] finished
+        self.k = 0
+        self.h2d_bytes = self.d_frames[0].numel() * self.d_frames[0].element_size() + self.d_seg[0].numel() * 4
+        self.d2h_bytes = self.host_out[0]["masks"].numel() + self.host_out[0]["heads"].numel() * 4
+
+    def submit(self, host_frames: torch.Tensor, host_seg: torch.Tensor) -> int:
+        s = self.k % 2
+        main = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(self.up):
+            if self.k >= 2:
+                self.up.wait_event(self.in_free[s])                  # the step that last read this slot is done
+            self.d_frames[s].copy_(host_frames, non_blocking=True)
+            self.d_seg[s].copy_(host_seg, non_blocking=True)
+            self.up_done[s].record(self.up)
+        main.wait_event(self.up_done[s])
+        segs = [self.d_seg[s][i * self.NP:(i + 1) * self.NP] for i in range(self.B)]
+        out = self.segment_fn(self.d_frames[s], segs, [self.resize] * self.B, [self.original] * self.B,
+                              threshold=self.threshold)
+        self.in_free[s].record(main)
+        with torch.cuda.stream(self.down):
+            self.down.wait_event(self.in_free[s])
+            ho = self.host_out[s]
+            ho["masks"][0].copy_(out["masks_left_packed"], non_blocking=True)
+            ho["masks"][1].copy_(out["masks_right_packed"], non_blocking=True)
+            ho["heads"][0].copy_(out["taxonomy"], non_blocking=True)
+            ho["heads"][1].copy_(out["iou_left"], non_blocking=True)
+            ho["heads"][2].copy_(out["iou_right"], non_blocking=True)
+            self.down_done[s].record(self.down)
+            for t in (out["masks_left_packed"], out["masks_right_packed"], out["taxonomy"], out["iou_left"],
+                      out["iou_right"]):
+                t.record_stream(self.down)                           # allocator: do not recycle before the download
+        self.k += 1
+        return s
+
+    def flush(self) -> None:
+        self.up.synchronize()
+        self.down.synchronize()
+        torch.cuda.current_stream(self.device).synchronize()

@@ -392,11 +392,23 @@ def run_gpu_arm(args):
         host_heads[1, a:a + NP].copy_(il, non_blocking=True)
         host_heads[2, a:a + NP].copy_(ir, non_blocking=True)
 
-    e2e_sink = to_host_1 if world == 1 else to_host_n
-    run_steps(1, from_host, e2e_sink)
+    # N = 1: the public host-to-host API (clip.HostPipeline): every step uploads ITS frames + prompts from pinned host
+    # memory and downloads ITS masks + heads, with the copies of neighbouring steps overlapping the kernels.
+    # N > 1: segment_clip with host loads and a host sink on rank 0.
+    pipe = clip.HostPipeline(sam.segment, B, NP, RESIZE, ORIGINAL, dev) if world == 1 else None
+
+    def e2e_run(k):
+        if world == 1:
+            for _ in range(k):
+                pipe.submit(host_frames, host_seg)
+            pipe.flush()                         # the caller consumes the masks on the host
+        else:
+            run_steps(k, from_host, to_host_n)
+
+    e2e_run(2)
     barrier()
     t0 = time.perf_counter()
-    run_steps(args.steps, from_host, e2e_sink)
+    e2e_run(args.steps)
     barrier()
     e2e_s = time.perf_counter() - t0
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
