@@ -71,6 +71,16 @@ def load_peaks() -> dict:
     return {"bf16_burst": 1590.0, "bf16_sustained": 1400.0, "hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
 
 
+def ncu_traffic(kernel_class):
+    """DRAM bytes per launch of a kernel class from the committed `ncu --set full` capture (profiles/ncu_traffic.json,
+    written by scripts/ncu_summarise.py), or None."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as fh:
+        return json.load(fh).get(kernel_class)
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -439,7 +449,7 @@ def run_gpu_arm(args):
         dom = max((n for n in kernels if n in fl), key=lambda n: kernels[n]["ms_per_step"])
         kd = kernels[dom]
         roofline = {"bound": "tensor", "kernel": dom, "achieved": kd["tflops"], "peak": peaks["bf16_sustained"],
-                    "unit": "TFLOP/s", "frac": kd["tflops"] / peaks["bf16_sustained"], "traffic": None,
+                    "unit": "TFLOP/s", "frac": kd["tflops"] / peaks["bf16_sustained"], "traffic": ncu_traffic(dom),
                     "peak_source": peaks["source"] + ", sustained figure (kernel timed inside a long step)",
                     "flops_per_launch": fl[dom] * B / kd["launches_per_step"],
                     "avg_launch_ms": kd["ms_per_step"] / kd["launches_per_step"],

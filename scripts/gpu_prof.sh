@@ -18,6 +18,7 @@ cap ln 'layernorm' 70 2
 cap post 'postprocess' 2 2
 cap dec 'dec_' 22 22
 rm -f $O/${TAG}_dec.ncu-rep
+cap aux 'preprocess_kernel|rows_fc_kernel|mask_metrics_kernel|seg_scan_kernel' 0 10
 # gpurun copies back at most 64 MiB: the CSV exports are what gets committed, drop the largest reports until we fit
 while [ $(du -sm $O | cut -f1) -ge 48 ]; do
   big=$(ls -S $O/*.ncu-rep 2>/dev/null | head -1); [ -z "$big" ] && break; rm -f "$big"; echo "dropped $big"
