@@ -78,7 +78,7 @@ def segment_clip(segment_fn: Callable[..., Dict[str, object]],
                  device: Optional[torch.device] = None, group=None, dst: int = 0,
                  sink: Optional[Callable[[int, torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor,
                                           torch.Tensor], None]] = None,
-                 keep: bool = True) -> ClipResult:
+                 keep: bool = True, prefetch: bool = False) -> ClipResult:
     """Segment frames [0, n_frames) of a clip on all ranks of `group`; rank `dst` collects the results.
 
     segment_fn: `B200Sam.segment` (frames, seg_embeds, resize_list, original_size_list, threshold=...) -> dict.
@@ -87,6 +87,8 @@ def segment_clip(segment_fn: Callable[..., Dict[str, object]],
     sink(frame, masks_left, masks_right, taxonomy, iou_left, iou_right): called on rank `dst` once per frame, in
         arrival order, with views into the receive buffers (valid only during the call) - streaming consumers
         (config 5) pass keep=False so nothing accumulates.
+    prefetch: on GPUs, call load_frames for round r+1 on an upload stream while round r computes (for loaders that
+        copy from pinned host memory with non_blocking=True: the H2D copy leaves the critical path).
     Every frame of the clip shares (resize, original), as a video does.
     """
     world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -136,14 +138,38 @@ def segment_clip(segment_fn: Callable[..., Dict[str, object]],
                     res.frames_done += 1
                     off += n
 
+    up = torch.cuda.Stream(device=device) if (prefetch and on_gpu) else None
+
+    def fetch(rnd: int):
+        """This rank's input of round `rnd` (None when its shard is exhausted), loaded on the upload stream."""
+        a, b = round_frames(n_frames, rank, world, micro_batch, rnd)
+        if rnd >= rounds or b <= a:
+            return None
+        if up is None:
+            return load_frames(a, b) + (None,)
+        with torch.cuda.stream(up):
+            frames, segs = load_frames(a, b)
+            ev = torch.cuda.Event()
+            ev.record(up)
+        return frames, segs, ev
+
+    nxt = fetch(0)
     for rnd in range(rounds):
         slot = slots[rnd % 2]
         if not is_dst:
             slot.wait()                               # the gather that last read this slot (round rnd-2) is done
         a, b = round_frames(n_frames, rank, world, micro_batch, rnd)
         slot.counts.zero_()
+        cur, nxt = nxt, (fetch(rnd + 1) if up is not None else None)
         if b > a:
-            frames, segs = load_frames(a, b)
+            if cur is None:
+                cur = fetch(rnd)
+            frames, segs, ev = cur
+            if ev is not None:                        # loaded on the upload stream: order it before the kernels
+                main = torch.cuda.current_stream(device)
+                main.wait_event(ev)
+                for t in [frames, *segs]:
+                    t.record_stream(main)
             if len(segs) != b - a or frames.shape[0] != b - a:
                 raise ValueError("load_frames returned the wrong number of frames")
             counts = [int(s.shape[0]) for s in segs]

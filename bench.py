@@ -329,7 +329,7 @@ def run_gpu_arm(args):
     def step(fr, sg):
         return sam.segment(fr, sg, resize, original, threshold=0.0, return_logits=False)
 
-    def run_steps(k, load, sink=None):
+    def run_steps(k, load, sink=None, prefetch=False):
         """k steps.  N = 1: k segment() calls.  N > 1: the product clip path - a clip of world*B*k frames sharded
         over the ranks, one micro-batch of B frames per rank per step, u8 masks + heads gathered to rank 0 over
         NCCL asynchronously behind the next micro-batch."""
@@ -341,7 +341,8 @@ def run_gpu_arm(args):
                     sink(out)
             return out
         return clip.segment_clip(sam.segment, load, world * B * k, RESIZE, ORIGINAL, micro_batch=B,
-                                 max_prompts_per_frame=NP, threshold=0.0, device=dev, sink=sink, keep=False)
+                                 max_prompts_per_frame=NP, threshold=0.0, device=dev, sink=sink, keep=False,
+                                 prefetch=prefetch)
 
     def resident(lo, hi):
         return frames, segs
@@ -413,7 +414,7 @@ def run_gpu_arm(args):
                 pipe.submit(host_frames, host_seg)
             pipe.flush()                         # the caller consumes the masks on the host
         else:
-            run_steps(k, from_host, to_host_n)
+            run_steps(k, from_host, to_host_n, prefetch=True)
 
     e2e_run(2)
     barrier()

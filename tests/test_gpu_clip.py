@@ -21,8 +21,13 @@ def test_clip_equals_direct_segment_calls():
     segs = [synth.make_seg_embeds(i, 3)[:counts[i]].cuda() for i in range(n_frames)]
     resize, original = (576, 1024), (135, 240)
     seen = []
-    res = clip.segment_clip(sam.segment, lambda lo, hi: (frames[lo:hi], segs[lo:hi]), n_frames, resize, original,
-                            micro_batch=mb, max_prompts_per_frame=3,
+    host_frames = frames.cpu().pin_memory()        # loader copies from pinned host memory on the upload stream
+
+    def load(lo, hi):
+        return host_frames[lo:hi].to("cuda", non_blocking=True), segs[lo:hi]
+
+    res = clip.segment_clip(sam.segment, load, n_frames, resize, original,
+                            micro_batch=mb, max_prompts_per_frame=3, prefetch=True,
                             sink=lambda f, ml, mr, tx, il, ir: seen.append((f, ml.shape[0])))
     torch.cuda.synchronize()
     assert res.frames_done == n_frames and seen == [(i, counts[i]) for i in range(n_frames)]
