@@ -157,3 +157,35 @@ def test_end_to_end_raw_frame_to_metrics(sam):
     m = sam2.mask_metrics(ml, mr, out["taxonomy"], ml | mr, return_pred=True)
     assert torch.all(m["counts"][:, 0] == m["counts"][:, 2])            # pred is a subset of left|right
     assert torch.all(m["iou"] <= 1.0)
+
+
+def test_config4_chain_hidden_states_to_masks(sam):
+    """BASELINE configs[3] at the SAM boundary: LLM last hidden states + output ids -> text_hidden_fcs on the [SEG]
+    rows -> prompt encoder -> both decoders -> postprocess, all on the device, against the oracle chain
+    (LISA.py:457-532 restated by aux_oracle.seg_project + sam_oracle.segment) on the same seeded inputs."""
+    from oracle import sam_oracle as O
+    from oracle import synth
+    sam2, arch, sd = G.build_sam_from_synth("tiny64", max_batch=2, max_prompts=4)
+    h, T, seg_idx = 512, 24, 32003
+    fcs = _fcs(h, 11)
+    g = torch.Generator().manual_seed(12)
+    ids = torch.randint(0, 32000, (2, T), generator=g)
+    ids[0, [3, 9]] = seg_idx
+    ids[1, [20]] = seg_idx
+    hidden = torch.randn((2, 255 + T - 1, h), generator=g)
+    frames = synth.make_frames(0, 2)
+    resize, original = (576, 1024), (270, 480)
+    embs, offsets = sam2.seg_project(hidden.cuda(), ids.cuda(), seg_idx, fcs)
+    assert offsets == [0, 2, 3]
+    out = sam2.segment(frames.cuda(), embs, [resize] * 2, [original] * 2, threshold=0.0, return_logits=True)
+    w = [t.detach().float().cpu().numpy() for t in (fcs[0][0].weight, fcs[0][0].bias, fcs[0][2].weight, fcs[0][2].bias)]
+    ref_embs, _ = A.seg_project(hidden.numpy(), ids.numpy(), seg_idx, *w)
+    ref = O.segment(sd, arch, frames, [torch.from_numpy(e) for e in ref_embs], [resize] * 2, [original] * 2, O.FP32)
+    for i in range(2):
+        for side in ("left", "right"):
+            got = out[f"logits_{side}"][i].cpu()
+            for n in range(got.shape[0]):
+                assert O.logit_rel_err(got[n], ref[i][f"masks_{side}"][n]) <= 2e-2
+                assert O.mask_iou(got[n], ref[i][f"masks_{side}"][n]) >= 0.99
+        lo, hi = offsets[i], offsets[i + 1]
+        assert torch.equal(out["taxonomy"][lo:hi].cpu().argmax(-1), ref[i]["taxonomy"].argmax(-1))
