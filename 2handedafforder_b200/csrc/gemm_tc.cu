@@ -420,10 +420,8 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
         if (st) *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(e.out) + orow[i] * (long)e.ld_out + col + out_off) = t;
       } else {
         if constexpr (MODE == GM_BIAS_GELU_BF16) {
-          x.x = gelu_erf_fast(x.x);
-          x.y = gelu_erf_fast(x.y);
-          x.z = gelu_erf_fast(x.z);
-          x.w = gelu_erf_fast(x.w);
+          gelu_erf_poly2(x.x, x.y);
+          gelu_erf_poly2(x.z, x.w);
         }
         uint2 t;
         t.x = pack_bf16(x.x, x.y);
