@@ -330,6 +330,26 @@ __device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
   asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
   return r;
 }
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// float4 += float4 as two packed adds (bit-identical to four scalar adds)
+__device__ __forceinline__ void add4(float4& x, const float4& y) {
+  const uint64_t lo = add2(f32x2(x.x, x.y), f32x2(y.x, y.y)), hi = add2(f32x2(x.z, x.w), f32x2(y.z, y.w));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(x.x), "=f"(x.y) : "l"(lo));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(x.z), "=f"(x.w) : "l"(hi));
+}
+// explicit shared-space 16-byte accesses (a generic pointer into dynamic smem compiles to generic LD/ST)
+__device__ __forceinline__ void sts128(uint32_t addr, float a, float b, float c, float d) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
+}
 __device__ __forceinline__ void gelu_erf_poly2(float& a, float& b) {
   const uint64_t x = f32x2(a, b);
   const uint64_t xc = f32x2(fminf(fmaxf(a, -4.75f), 4.75f), fminf(fmaxf(b, -4.75f), 4.75f));

@@ -373,6 +373,7 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
   wait_acc();
   // Software pipeline, one chunk deep: the accumulator registers are dead as soon as they sit in the transposition
   // tile, so the tcgen05.ld of chunk c+1 (and its bias / addend loads) is in flight while chunk c is finished.
+  const uint32_t stage_s = smem_u32(stage);
   uint32_t v[32];
   if (c_lo < c_hi) tmem_ld_32x32(src.taddr + c_lo * 32, v);
   for (int c = c_lo; c < c_hi; ++c) {
@@ -385,9 +386,8 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
     tmem_wait_ld();
 #pragma unroll
     for (int g = 0; g < 8; ++g)
-      stage[lane * 8 + (g ^ (lane & 7))] =
-          make_float4(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]), __uint_as_float(v[4 * g + 2]),
-                      __uint_as_float(v[4 * g + 3]));
+      sts128(stage_s + (lane * 8 + (g ^ (lane & 7))) * 16, __uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]),
+             __uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
     __syncwarp();
     const float4 b4 = b_nxt;
     if (c + 1 < c_hi) {
@@ -397,20 +397,12 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int r = i * 4 + sub;
-      float4 x = stage[r * 8 + (cg ^ (r & 7))];
-      x.x += b4.x;
-      x.y += b4.y;
-      x.z += b4.z;
-      x.w += b4.w;
+      float4 x = lds128(stage_s + (r * 8 + (cg ^ (r & 7))) * 16);
+      add4(x, b4);
       const bool st = orow[i] >= 0;   // predicated stores (no branch: the 8 row slices interleave)
       const long col = n0 + c * 32 + cg * 4;
       if constexpr (MODE == GM_F32) {
-        if (has_add) {
-          x.x += cur[i].x;
-          x.y += cur[i].y;
-          x.z += cur[i].z;
-          x.w += cur[i].w;
-        }
+        if (has_add) add4(x, cur[i]);
         if (st) *reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + orow[i] * (long)e.ld_out + col) = x;
       } else if constexpr (MODE == GM_F16) {
         __half2 h0 = __floats2half2_rn(x.x, x.y), h1 = __floats2half2_rn(x.z, x.w);
