@@ -285,8 +285,8 @@ __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, l
         const float rstd = rsqrtf(q * (1.f / 64.f) + e.ln_eps);
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          v[j] = gelu_erf((v[j] - mean) * rstd * __ldg(e.ln_g + j) + __ldg(e.ln_b + j));
-          w[j] = gelu_erf((w[j] - mean) * rstd * __ldg(e.ln_g + 32 + j) + __ldg(e.ln_b + 32 + j));
+          v[j] = gelu_erf_poly((v[j] - mean) * rstd * __ldg(e.ln_g + j) + __ldg(e.ln_b + j));
+          w[j] = gelu_erf_poly((w[j] - mean) * rstd * __ldg(e.ln_g + 32 + j) + __ldg(e.ln_b + 32 + j));
         }
         int ky = g >> 1, kx = g & 1;
         float* o = reinterpret_cast<float*>(e.out) + ((p * 128 + 2 * y + ky) * 128 + 2 * x + kx) * 64;
@@ -307,7 +307,7 @@ __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, l
         add_vec32(v, e.bias + g * 32);
         float dot = 0.f;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) dot += gelu_erf(v[j]) * __ldg(h + j);
+        for (int j = 0; j < 32; ++j) dot += gelu_erf_poly(v[j]) * __ldg(h + j);
         int ky = g >> 1, kx = g & 1;
         reinterpret_cast<float*>(e.out)[p * 65536 + (2 * y + ky) * 256 + 2 * x + kx] = dot;
       }

@@ -4,8 +4,9 @@
 // The reference resamples twice with a crop in between and materialises the 1024^2 intermediate:
 //   a = bilinear(m 256^2 -> 1024^2) ; a = a[:h, :w] ; out = bilinear(a -> H x W)          (both align_corners=False)
 // A single direct 256^2 -> (H, W) resample is NOT equivalent, so every output pixel
-// evaluates the four 1024-grid taps it needs, each from four low-res taps, in registers: 16 cached low-res reads
-// (a 256 KB mask stays in L1/L2) and one coalesced 16-byte store per 4 output pixels.  No 1024^2 tensor touches HBM.
+// composes the two resamplings exactly (four 1024-grid taps, each from four low-res taps); the row direction is
+// collapsed once per output row in shared memory.  One coalesced 16-byte store per 4 output pixels; no 1024^2
+// tensor touches HBM.
 //
 // ATen index rule (UpSampleBilinear2d): src = max(0, scale * (dst + 0.5) - 0.5), scale = float(in) / out,
 // i0 = int(src), i1 = i0 + (i0 < in - 1), lambda = src - i0.
@@ -32,38 +33,44 @@ __device__ __forceinline__ Tap make_tap(int dst, float scale, int n_in) {
   return t;
 }
 
-// value of the virtual 1024^2 intermediate at (y, x): bilinear from the 256^2 low-res mask
-__device__ __forceinline__ float mid_value(const float* __restrict__ m, const Tap& ty, const Tap& tx) {
-  const float* r0 = m + ty.i0 * 256;
-  const float* r1 = m + ty.i1 * 256;
-  const float top = tx.l0 * __ldg(r0 + tx.i0) + tx.l1 * __ldg(r0 + tx.i1);
-  const float bot = tx.l0 * __ldg(r1 + tx.i0) + tx.l1 * __ldg(r1 + tx.i1);
-  return ty.l0 * top + ty.l1 * bot;
-}
-
-__device__ __forceinline__ float out_value(const float* __restrict__ m, int Y, int X, float sy, float sx, int h,
-                                           int w) {
-  const Tap oy = make_tap(Y, sy, h), ox = make_tap(X, sx, w);
-  constexpr float kUp = 256.f / 1024.f;
-  const Tap y0 = make_tap(oy.i0, kUp, 256), y1 = make_tap(oy.i1, kUp, 256);
-  const Tap x0 = make_tap(ox.i0, kUp, 256), x1 = make_tap(ox.i1, kUp, 256);
-  const float top = ox.l0 * mid_value(m, y0, x0) + ox.l1 * mid_value(m, y0, x1);
-  const float bot = ox.l0 * mid_value(m, y1, x0) + ox.l1 * mid_value(m, y1, x1);
-  return oy.l0 * top + oy.l1 * bot;
-}
-
+// Both resamplings are separable, so the row direction is collapsed first: for one output row Y the (at most four)
+// low-res rows it touches are blended into ONE 256-float row in shared memory,
+//   R[q] = sum_a oy.l[a] * sum_p ty_a.l[p] * m[ty_a.i[p]][q],
+// and every output pixel is then 4 shared-memory reads: out = sum_b ox.l[b] * sum_q tx_b.l[q] * R[tx_b.i[q]].
 // grid: (ceil(W/4/128), H, n).  One thread = 4 consecutive output pixels of one row.
 __global__ void __launch_bounds__(128)
 postprocess_kernel(const float* __restrict__ lowres, int h, int w, int H, int W, float sy, float sx,
                    float* __restrict__ logits, uint8_t* __restrict__ mask, float thr) {
-  const int X0 = (blockIdx.x * 128 + threadIdx.x) * 4;
-  if (X0 >= W) return;
+  __shared__ float R[256];
   const int Y = blockIdx.y;
   const long n = blockIdx.z;
   const float* m = lowres + n * 65536;
+  constexpr float kUp = 256.f / 1024.f;
+  {
+    const Tap oy = make_tap(Y, sy, h);
+    const Tap y0 = make_tap(oy.i0, kUp, 256), y1 = make_tap(oy.i1, kUp, 256);
+    const float* r00 = m + y0.i0 * 256;
+    const float* r01 = m + y0.i1 * 256;
+    const float* r10 = m + y1.i0 * 256;
+    const float* r11 = m + y1.i1 * 256;
+#pragma unroll
+    for (int q = threadIdx.x; q < 256; q += 128)
+      R[q] = oy.l0 * (y0.l0 * __ldg(r00 + q) + y0.l1 * __ldg(r01 + q)) +
+             oy.l1 * (y1.l0 * __ldg(r10 + q) + y1.l1 * __ldg(r11 + q));
+  }
+  __syncthreads();
+  const int X0 = (blockIdx.x * 128 + threadIdx.x) * 4;
+  if (X0 >= W) return;
   float v[4];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) v[j] = (X0 + j < W) ? out_value(m, Y, X0 + j, sy, sx, h, w) : 0.f;
+  for (int j = 0; j < 4; ++j) {
+    v[j] = 0.f;
+    if (X0 + j < W) {
+      const Tap ox = make_tap(X0 + j, sx, w);
+      const Tap x0 = make_tap(ox.i0, kUp, 256), x1 = make_tap(ox.i1, kUp, 256);
+      v[j] = ox.l0 * (x0.l0 * R[x0.i0] + x0.l1 * R[x0.i1]) + ox.l1 * (x1.l0 * R[x1.i0] + x1.l1 * R[x1.i1]);
+    }
+  }
   const long base = (n * H + Y) * (long)W + X0;
   const bool full = X0 + 3 < W;
   if (logits) {
