@@ -347,6 +347,17 @@ int alloc_workspace(b200sam_t* h) {
   CU(dalloc(h, &h->qkv, B * kWinRowsPerFrame * 3 * D));
   CU(dalloc(h, &h->attn_o, B * kWinRowsPerFrame * D));
   {
+    std::vector<int> pads;
+    for (int rem = 0; rem < kWinRowsPerFrame; ++rem) {
+      const int win = rem / kWinTokens, t = rem - win * kWinTokens;
+      const int y = (win / kWinPerSide) * kWin + t / kWin, x = (win % kWinPerSide) * kWin + t % kWin;
+      if (y >= kGrid || x >= kGrid) pads.push_back(rem);
+    }
+    h->n_pad_rows = (int)pads.size();
+    CU(dalloc(h, &h->pad_rows, pads.size()));
+    CU(cudaMemcpy(h->pad_rows, pads.data(), pads.size() * sizeof(int), cudaMemcpyHostToDevice));
+  }
+  {
     __half* g = nullptr;
     CU(dalloc(h, &g, B * kTokens * (size_t)h->heads * 256));
     h->gbuf = g;
@@ -648,7 +659,7 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   h->prof_stream = s;
   const int D = h->dim, heads = h->heads, hd = h->hd;
-  const long T = (long)B * kTokens, TW = (long)B * kWinRowsPerFrame;
+  const long T = (long)B * kTokens;
 
   // PatchEmbed + pos_embed (image_encoder.py:111-113): im2col index map, GEMM, bias + pos_embed in the epilogue
   h->pc = B200SAM_PC_ELEMENTWISE;
@@ -667,34 +678,36 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
   const int nblocks = (h->debug_stop_block >= 0 && h->debug_stop_block < h->depth) ? h->debug_stop_block : h->depth;
   for (int i = 0; i < nblocks; ++i) {
     const EncBlock& b = h->blk[i];
-    // norm1 (+ window_partition folded into the store; pad rows of ln_win are zero = F.pad after the norm)
-    const __nv_bfloat16* a_in = b.global ? h->ln_plain : h->ln_win;
+    // norm1 in token order.  The windowed blocks never materialise the zero-padded window tensor: the qkv epilogue
+    // scatters the 4096 real rows of a frame into the 4900-row window layout (window_partition, image_encoder.py:263-288),
+    // the 804 pad rows (zero after norm1 => qkv = bias, :179-183) are filled by a small kernel, and the attention
+    // kernel stores straight back into token order (window_unpartition), so qkv and proj run on 4096 rows per frame.
     h->pc = B200SAM_PC_LAYERNORM;
-    KL(launch_layernorm_bf16(h->X, T, D, b.ln1g, b.ln1b, 1e-6f, b.global ? h->ln_plain : h->ln_win, !b.global, s));
-    const long rows = b.global ? T : TW;
+    KL(launch_layernorm_bf16(h->X, T, D, b.ln1g, b.ln1b, 1e-6f, h->ln_plain, false, s));
     {
       GemmEpi e;
       e.bias = b.qkv_b;
       e.out = h->qkv;
       e.ld_out = 3 * D;
+      e.rowmap = b.global ? RM_IDENT : RM_TOKEN_TO_WINDOW;
       h->pc = B200SAM_PC_GEMM_QKV;
-      if (int r = run_gemm(h, false, GM_BIAS_BF16, a_in, D, b.qkv_w, D, rows, 3 * D, D, e, s)) return r;
+      if (int r = run_gemm(h, false, GM_BIAS_BF16, h->ln_plain, D, b.qkv_w, D, T, 3 * D, D, e, s)) return r;
+      if (!b.global) KL(launch_fill_pad_rows(h->qkv, b.qkv_b, h->pad_rows, h->n_pad_rows, B, 3 * D, s));
     }
     h->pc = b.global ? B200SAM_PC_ATTN_GLOBAL : B200SAM_PC_ATTN_WINDOW;
     KL(launch_attention(h->qkv, b.global ? B : B * kWinPerSide * kWinPerSide, b.global ? kGrid : kWin, heads, hd, b.relh,
-                        b.relw, b.relg, h->gbuf, h->attn_o, s));
+                        b.relw, b.relg, h->gbuf, h->attn_o, s, /*window_token_out=*/true));
     if (b.global) ++h->launches;   // the batched bias-projection GEMM in front of the global kernel
     {
-      // proj + window_unpartition + residual: x = shortcut + attn(x)             (image_encoder.py:187-190)
+      // proj + residual: x = shortcut + attn(x)                                    (image_encoder.py:187-190)
       GemmEpi e;
       e.bias = b.proj_b;
       e.addend = h->X;
       e.ld_add = D;
       e.out = h->X;
       e.ld_out = D;
-      e.rowmap = b.global ? RM_IDENT : RM_WINDOW_TO_TOKEN;
       h->pc = B200SAM_PC_GEMM_PROJ;
-      if (int r = run_gemm(h, false, GM_F32, h->attn_o, D, b.proj_w, D, rows, D, D, e, s)) return r;
+      if (int r = run_gemm(h, false, GM_F32, h->attn_o, D, b.proj_w, D, T, D, D, e, s)) return r;
     }
     // x = x + lin2(GELU(lin1(norm2(x))))                                          (image_encoder.py:191, common.py:25-26)
     h->pc = B200SAM_PC_LAYERNORM;

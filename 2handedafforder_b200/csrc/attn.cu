@@ -13,13 +13,13 @@ cudaError_t attention_init() { return cudaSuccess; }
 
 cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int heads, int hd,
                              const __nv_bfloat16* relh, const __nv_bfloat16* relw, const __nv_bfloat16* relg,
-                             void* gbuf, __nv_bfloat16* out, cudaStream_t s) {
+                             void* gbuf, __nv_bfloat16* out, cudaStream_t s, bool window_token_out) {
   if (nbatch <= 0) return cudaSuccess;
   if (hd != 64 && hd != 80) return cudaErrorInvalidValue;
   if (S == kWin) {
     // the two padded tables must be contiguous: [relh (32 rows); relw (32 rows)]
     if (relw != relh + 32 * hd) return cudaErrorInvalidValue;
-    return launch_attention_window_tc(qkv, nbatch, heads, hd, relh, out, s);
+    return launch_attention_window_tc(qkv, nbatch, heads, hd, relh, out, s, window_token_out);
   }
   if (S == kGrid) {
     if (!relg || !gbuf) return cudaErrorInvalidValue;

@@ -55,7 +55,7 @@ template <int HD>
 __global__ void __launch_bounds__(kThreadsWin, 1)
 attn_window_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tm32,
                       const __grid_constant__ CUtensorMap tmR128, const __grid_constant__ CUtensorMap tmR32,
-                      __nv_bfloat16* __restrict__ out, int nwin, int heads, float scale) {
+                      __nv_bfloat16* __restrict__ out, int nwin, int heads, float scale, int token_out) {
   using C = WinCfg<HD>;
   constexpr bool kHasRem = C::kRem > 0;
   extern __shared__ uint8_t smem_raw[];
@@ -290,14 +290,24 @@ attn_window_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
       mbar_wait(&o_full[t], ph);
       tc_fence_after();
       const float inv = 1.f / sum;
-      __nv_bfloat16* go = out + ((long)win * kT + rr) * ldo + head * HD;
+      // token_out: window_unpartition (image_encoder.py:291-318) folded into the store - rows go to b*4096 + y*64 + x and
+      // the window-pad rows are dropped, so the projection GEMM runs on 4096 instead of 4900 rows per frame
+      long orow = (long)win * kT + rr;
+      bool vst = valid;
+      if (token_out) {
+        const int bfr = win / (kWinPerSide * kWinPerSide), wi = win - bfr * (kWinPerSide * kWinPerSide);
+        const int y = (wi / kWinPerSide) * kWin + qy, x = (wi % kWinPerSide) * kWin + qx;
+        vst = valid && y < kGrid && x < kGrid;
+        orow = (long)bfr * kTokens + y * kGrid + x;
+      }
+      __nv_bfloat16* go = out + orow * ldo + head * HD;
       {
         uint32_t v[32];
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           tmem_ld_32x32(tl + t * kSCols + kOCol + c * 32, v);
           tmem_wait_ld();
-          if (valid) {
+          if (vst) {
             uint4* o4 = reinterpret_cast<uint4*>(go + c * 32);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -314,7 +324,7 @@ attn_window_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
           uint32_t w[16];
           tmem_ld_32x32_16(tl + t * kSCols + kOCol + 64, w);
           tmem_wait_ld();
-          if (valid) {
+          if (vst) {
             uint4* o4 = reinterpret_cast<uint4*>(go + 64);
 #pragma unroll
             for (int j = 0; j < 2; ++j) {
@@ -342,7 +352,7 @@ attn_window_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
 
 template <int HD>
 cudaError_t launch_window(const __nv_bfloat16* qkv, int nwin, int heads, const __nv_bfloat16* rel, __nv_bfloat16* out,
-                          cudaStream_t s) {
+                          bool token_out, cudaStream_t s) {
   using C = WinCfg<HD>;
   static bool attr = false;
   if (!attr) {
@@ -369,7 +379,7 @@ cudaError_t launch_window(const __nv_bfloat16* qkv, int nwin, int heads, const _
   const int nprob = nwin * heads;
   const int grid = nprob < gemm_num_sms() ? nprob : gemm_num_sms();
   attn_window_tc_kernel<HD><<<grid, kThreadsWin, C::kSmem, s>>>(tm128, tm32, tmR128, tmR32, out, nwin, heads,
-                                                              1.0f / sqrtf((float)HD));
+                                                              1.0f / sqrtf((float)HD), token_out ? 1 : 0);
   return cudaGetLastError();
 }
 
@@ -377,10 +387,10 @@ cudaError_t launch_window(const __nv_bfloat16* qkv, int nwin, int heads, const _
 
 // qkv: (nwin*196, 3*heads*hd) bf16; rel: (64, hd) bf16 = [rel_pos_h (27 rows, zero padded to 32); rel_pos_w (same)].
 cudaError_t launch_attention_window_tc(const __nv_bfloat16* qkv, int nwin, int heads, int hd, const __nv_bfloat16* rel,
-                                       __nv_bfloat16* out, cudaStream_t s) {
+                                       __nv_bfloat16* out, cudaStream_t s, bool token_out) {
   if (nwin <= 0) return cudaSuccess;
-  if (hd == 80) return launch_window<80>(qkv, nwin, heads, rel, out, s);
-  if (hd == 64) return launch_window<64>(qkv, nwin, heads, rel, out, s);
+  if (hd == 80) return launch_window<80>(qkv, nwin, heads, rel, out, token_out, s);
+  if (hd == 64) return launch_window<64>(qkv, nwin, heads, rel, out, token_out, s);
   return cudaErrorInvalidValue;
 }
 

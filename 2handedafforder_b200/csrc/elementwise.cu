@@ -227,6 +227,30 @@ cudaError_t launch_layernorm_bf16(const float* x, long rows, int D, const float*
   return cudaGetLastError();
 }
 
+// One block per (window-pad row, frame): pad_rows lists the 804 pad positions of the 4900-row window layout.
+__global__ void __launch_bounds__(128) fill_pad_rows_kernel(__nv_bfloat16* __restrict__ qkv,
+                                                            const float* __restrict__ bias,
+                                                            const int* __restrict__ pad_rows, int cols) {
+  const int rem = pad_rows[blockIdx.x];
+  uint2* o = reinterpret_cast<uint2*>(qkv + ((long)blockIdx.y * kWinRowsPerFrame + rem) * cols);
+  const float4* b4 = reinterpret_cast<const float4*>(bias);
+  for (int i = threadIdx.x; i < cols / 4; i += 128) {
+    const float4 v = __ldg(b4 + i);
+    uint2 w;
+    w.x = pack_bf16(v.x, v.y);
+    w.y = pack_bf16(v.z, v.w);
+    o[i] = w;
+  }
+}
+
+cudaError_t launch_fill_pad_rows(__nv_bfloat16* qkv, const float* bias, const int* pad_rows, int n_pad, int B,
+                                 int cols, cudaStream_t s) {
+  if (B <= 0 || n_pad <= 0) return cudaSuccess;
+  if (cols % 4 != 0) return cudaErrorInvalidValue;
+  fill_pad_rows_kernel<<<dim3(n_pad, B), 128, 0, s>>>(qkv, bias, pad_rows, cols);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_im2col_patch(const void* frames, int dtype, int B, __nv_bfloat16* out, cudaStream_t s) {
   if (B <= 0) return cudaSuccess;
   const long total = (long)B * 3 * kImg * (kImg / 8);

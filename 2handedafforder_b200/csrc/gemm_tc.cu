@@ -39,6 +39,15 @@ struct TileCfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + 32768 /*epilogue tiles*/;
 };
 
+// token row (b*4096 + y*64 + x) -> row of the 14x14-window layout (b*4900 + window*196 + in-window index);
+// window_partition of image_encoder.py:263-288 as an index map
+__device__ __forceinline__ long token_to_window_row(long row) {
+  const long b = row / kTokens;
+  const int t = (int)(row - b * kTokens);
+  const int y = t / kGrid, x = t % kGrid;
+  return b * kWinRowsPerFrame + ((y / kWin) * kWinPerSide + x / kWin) * kWinTokens + (y % kWin) * kWin + x % kWin;
+}
+
 struct TmemSrc {
   uint32_t taddr;  // lane offset | first column of this accumulator buffer
   __device__ __forceinline__ void load(int chunk, float (&v)[32]) const {
@@ -138,7 +147,8 @@ __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, l
   float v[32];
 
   if constexpr (MODE == GM_BIAS_BF16 || MODE == GM_BIAS_GELU_BF16) {
-    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + row * (long)e.ld_out + n0;
+    const long orow_b = e.rowmap == RM_TOKEN_TO_WINDOW ? token_to_window_row(row_in ? row : 0) : row;
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + orow_b * (long)e.ld_out + n0;
     wait_acc();
     for (int c = c_lo; c < c_hi; ++c) {
       src.load(c, v);
@@ -344,6 +354,8 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
       ok = ok && (y < kGrid) && (x < kGrid);
       orow = b * kTokens + y * kGrid + x;
     }
+    if ((MODE == GM_BIAS_BF16 || MODE == GM_BIAS_GELU_BF16) && e.rowmap == RM_TOKEN_TO_WINDOW && ok)
+      orow = token_to_window_row(row);
     orow_own = ok ? (int)orow : -1;
   }
   const int sub = lane >> 3, cg = lane & 7;     // transposed role: rows i*4 + sub (i < 8), columns cg*4 .. cg*4+3

@@ -15,6 +15,9 @@ cudaError_t launch_im2col_patch(const void* frames, int dtype, int B, __nv_bfloa
 cudaError_t launch_im2col_3x3(const __nv_bfloat16* z, int B, __nv_bfloat16* out, cudaStream_t s);
 cudaError_t launch_tokens_to_nchw(const float* tok, int B, void* out, int dtype, cudaStream_t s);
 cudaError_t launch_nchw_to_tokens(const void* in, int dtype, int B, float* tok, cudaStream_t s);
+// window-pad rows of the packed qkv buffer (B*4900, 3D) := bias (qkv of a zero row, image_encoder.py:179-183 pads after norm1)
+cudaError_t launch_fill_pad_rows(__nv_bfloat16* qkv, const float* bias, const int* pad_rows, int n_pad, int B,
+                                 int cols, cudaStream_t s);
 cudaError_t launch_cast_f32_bf16(const float* in, __nv_bfloat16* out, long n, cudaStream_t s);
 cudaError_t launch_to_f32(const void* in, int dtype, float* out, long n, cudaStream_t s);
 cudaError_t launch_dense_pe(const float* gauss, float* pe_tok, cudaStream_t s);
@@ -31,13 +34,14 @@ cudaError_t launch_relpos_pack_g(const float* rel_h, const float* rel_w, int hd,
 // >= hd zero (launch_relpos_pack_g), and gbuf = (nbatch*4096, heads*256) fp16 scratch for the bias projections.
 cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int heads, int hd,
                              const __nv_bfloat16* relh, const __nv_bfloat16* relw, const __nv_bfloat16* relg,
-                             void* gbuf, __nv_bfloat16* out, cudaStream_t s);
+                             void* gbuf, __nv_bfloat16* out, cudaStream_t s, bool window_token_out = false);
 cudaError_t attention_init();
 // ---- attn_tc.cu (tcgen05): windowed attention; rel = (64, hd) bf16 [rel_pos_h padded to 32 rows; rel_pos_w padded]
 cudaError_t launch_attention_global_tc(const __nv_bfloat16* qkv, int nbatch, int heads, int hd, const __half* G,
                                        __nv_bfloat16* out, cudaStream_t s);
+// token_out: rows are written in token order (b*4096 + y*64 + x, window-pad rows dropped) instead of window order
 cudaError_t launch_attention_window_tc(const __nv_bfloat16* qkv, int nwin, int heads, int hd, const __nv_bfloat16* rel,
-                                       __nv_bfloat16* out, cudaStream_t s);
+                                       __nv_bfloat16* out, cudaStream_t s, bool token_out = false);
 
 // ---- decoder.cu
 struct DecSideWeights;   // device pointers of one mask decoder (api.cu owns it)

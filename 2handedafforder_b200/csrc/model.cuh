@@ -121,6 +121,8 @@ struct b200sam {
   __nv_bfloat16* ln_win = nullptr;   // (B*4900, D) windowed LN1 output, pad rows stay zero
   __nv_bfloat16* ln_plain = nullptr; // (B*4096, D)
   __nv_bfloat16* qkv = nullptr;      // (B*4900, 3D)
+  int* pad_rows = nullptr;           // (n_pad_rows = 804) window-pad positions inside one frame's 4900-row window layout
+  int n_pad_rows = 0;
   __nv_bfloat16* attn_o = nullptr;   // (B*4900, D)
   void* gbuf = nullptr;              // (B*4096, heads*256) fp16 rel-pos projections of the global blocks
   __nv_bfloat16* hid = nullptr;      // (B*4096, 4D) MLP hidden; also im2col scratch
