@@ -342,7 +342,6 @@ int finalize_side(b200sam_t* h, int s) {
 int alloc_workspace(b200sam_t* h) {
   const size_t B = h->max_batch, P = h->max_prompts, D = h->dim;
   CU(dalloc(h, &h->X, B * kTokens * D));
-  CU(dalloc(h, &h->ln_win, B * kWinRowsPerFrame * D, /*zero=*/true));   // pad rows stay zero forever
   CU(dalloc(h, &h->ln_plain, B * kTokens * D));
   CU(dalloc(h, &h->qkv, B * kWinRowsPerFrame * 3 * D));
   CU(dalloc(h, &h->attn_o, B * kWinRowsPerFrame * D));

@@ -118,7 +118,6 @@ struct b200sam {
 
   // workspace (sized for max_batch / max_prompts)
   float* X = nullptr;                // (B*4096, D) fp32 residual stream
-  __nv_bfloat16* ln_win = nullptr;   // (B*4900, D) windowed LN1 output, pad rows stay zero
   __nv_bfloat16* ln_plain = nullptr; // (B*4096, D)
   __nv_bfloat16* qkv = nullptr;      // (B*4900, 3D)
   int* pad_rows = nullptr;           // (n_pad_rows = 804) window-pad positions inside one frame's 4900-row window layout
