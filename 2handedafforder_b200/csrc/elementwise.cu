@@ -19,8 +19,11 @@ __global__ void __launch_bounds__(256) layernorm_bf16_kernel(const float* __rest
                                                              const float* __restrict__ b, float eps,
                                                              __nv_bfloat16* __restrict__ out, int windowed) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long row = (long)blockIdx.x * 8 + warp;
-  if (row >= rows) return;
+  // rows are walked from the END of the residual stream: the GEMM epilogue that produced X wrote it front to back,
+  // so its last ~100 MB are still in the 126 MB L2 when this kernel starts - reading those first (before this
+  // kernel's own traffic evicts them) turns most of the fp32 read into L2 hits
+  const long row = rows - 1 - ((long)blockIdx.x * 8 + warp);
+  if (row < 0) return;
   const int nvec = D >> 2;
   const float4* xr = reinterpret_cast<const float4*>(x + row * D);
   float4 v[NJ];
