@@ -30,7 +30,7 @@ constexpr int kGT = kTokens;          // 4096
 constexpr int kBKeys = 128;           // keys per tile = two image rows
 constexpr int kNIter = kGT / kBKeys;  // 32
 constexpr int kQBlocks = kGT / 256;   // 16 work items per (frame, head)
-constexpr int kStagesG = 4;
+constexpr int kStagesG = 3;
 constexpr int kThreadsG = 384;
 constexpr int kOColG = 256;           // O_t at kOColG + t * 128
 
@@ -40,13 +40,18 @@ struct GlbCfg {
   static constexpr int kMain = 128 * 128;                 // one 128-row tile, 64 columns: 16 KB
   static constexpr int kRemB = kRem ? 128 * 32 : 0;       // 16 columns: 4 KB
   static constexpr int kTile = kMain + kRemB;
+  // V's second box is 64 columns wide too (head columns [HD-64, HD)): with the two boxes one LBO apart a single
+  // N = 128 MN-major MMA per 16 keys covers the whole head (columns 64..HD-1 land in O columns 128-kRem..127) instead
+  // of an N = 64 and an N = 16 instruction - the single issuing thread is the bottleneck of the P.V step
+  static constexpr int kVRemB = kRem ? kMain : 0;
+  static constexpr int kVTile = kMain + kVRemB;
   static constexpr int oQm = 0;                           // 2 tiles
   static constexpr int oKm = 2 * kMain;                   // kStagesG tiles
   static constexpr int oVm = oKm + kStagesG * kMain;
   static constexpr int oQr = oVm + kStagesG * kMain;
   static constexpr int oKr = oQr + 2 * kRemB;
   static constexpr int oVr = oKr + kStagesG * kRemB;
-  static constexpr int oBar = oVr + kStagesG * kRemB;
+  static constexpr int oBar = oVr + kStagesG * kVRemB;
   static constexpr int kSmem = oBar + 512 + 1024;
 };
 
@@ -113,7 +118,8 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
     if (lane == 0) {
       int it = 0, kc = 0;
       for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
-        const int bh = item / kQBlocks, qb = item - bh * kQBlocks;
+        const int ir = nitems - 1 - item;   // back to front: the qkv GEMM's last tiles are still in L2
+        const int bh = ir / kQBlocks, qb = ir - bh * kQBlocks;
         const int b = bh / heads, head = bh - b * heads;
         const int row0 = b * kGT;
         const int cq = head * HD, ck = heads * HD + head * HD, cv = 2 * heads * HD + head * HD;
@@ -131,9 +137,9 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
           tma_load_2d(smem + C::oKm + s * C::kMain, &tm128, &k_full[s], ck, row0 + j * kBKeys);
           if (kHasRem) tma_load_2d(smem + C::oKr + s * C::kRemB, &tm32, &k_full[s], ck + 64, row0 + j * kBKeys);
           mbar_wait(&v_empty[s], ph ^ 1);
-          mbar_expect_tx(&v_full[s], C::kTile);
+          mbar_expect_tx(&v_full[s], C::kVTile);
           tma_load_2d(smem + C::oVm + s * C::kMain, &tm128, &v_full[s], cv, row0 + j * kBKeys);
-          if (kHasRem) tma_load_2d(smem + C::oVr + s * C::kRemB, &tm32, &v_full[s], cv + 64, row0 + j * kBKeys);
+          if (kHasRem) tma_load_2d(smem + C::oVr + s * C::kVRemB, &tm128, &v_full[s], cv + HD - 64, row0 + j * kBKeys);
         }
       }
     }
@@ -142,7 +148,7 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
     if (lane == 0) {
       constexpr uint32_t idS = umma_idesc_bf16(128, kBKeys, false, false);
       constexpr uint32_t idO64 = umma_idesc_bf16(128, 64, false, true);
-      constexpr uint32_t idO16 = umma_idesc_bf16(128, 16, false, true);
+      constexpr uint32_t idO128 = umma_idesc_bf16(128, 128, false, true);
       const uint32_t sQm = smem_u32(smem + C::oQm), sQr = smem_u32(smem + C::oQr);
       const uint32_t sKm = smem_u32(smem + C::oKm), sKr = smem_u32(smem + C::oKr);
       const uint32_t sVm = smem_u32(smem + C::oVm), sVr = smem_u32(smem + C::oVr);
@@ -182,13 +188,12 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
             ++np[t];
             tc_fence_after();
             const uint32_t dO = tmem + kOColG + t * 128, aP = tmem + t * 128;
-            const uint32_t bM = sVm + sv * C::kMain, bR = sVr + sv * C::kRemB;
+            const uint32_t bM = sVm + sv * C::kMain;
+            const uint32_t lbo = kHasRem ? (sVr - sVm) : 1024;   // main box -> second box of the same stage
 #pragma unroll
-            for (int ks = 0; ks < kBKeys / 16; ++ks) {
-              umma_ts_bf16(dO, aP + ks * 8, umma_desc(bM + ks * 2048, 1024, 1024, 2), idO64, (j | ks) != 0);
-              if (kHasRem)
-                umma_ts_bf16(dO + 64, aP + ks * 8, umma_desc(bR + ks * 512, 256, 256, 6), idO16, (j | ks) != 0);
-            }
+            for (int ks = 0; ks < kBKeys / 16; ++ks)
+              umma_ts_bf16(dO, aP + ks * 8, umma_desc(bM + ks * 2048, 1024, lbo, 2), kHasRem ? idO128 : idO64,
+                           (j | ks) != 0);
             if (t == 1) umma_commit(&v_empty[sv]);
             if (more) {
               issue_S(t, sk);
@@ -218,7 +223,8 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
     uint32_t ns = 0;                                     // score tiles consumed (parity of s_full[t])
     int it = 0;
     for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
-      const int bhh = item / kQBlocks, qb = item - bhh * kQBlocks;
+      const int ir = nitems - 1 - item;
+      const int bhh = ir / kQBlocks, qb = ir - bhh * kQBlocks;
       const int b = bhh / heads, head = bhh - b * heads;
       const int qrow = qb * 256 + t * 128 + rl;          // token index inside the frame
       const int qy = qrow >> 6, qx = qrow & 63;
@@ -287,11 +293,11 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
             }
             if (kHasRem) {
               uint32_t w[16];
-              tmem_ld_32x32_16(tO + 64, w);
+              tmem_ld_32x32_16(tO + 128 - C::kRem, w);
               tmem_wait_ld();
 #pragma unroll
               for (int i = 0; i < 16; ++i) w[i] = __float_as_uint(__uint_as_float(w[i]) * f);
-              tmem_st_32x32_16(tO + 64, w);
+              tmem_st_32x32_16(tO + 128 - C::kRem, w);
             }
           }
         }
@@ -351,7 +357,7 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
         }
         if (kHasRem) {
           uint32_t w[16];
-          tmem_ld_32x32_16(tO + 64, w);
+          tmem_ld_32x32_16(tO + 128 - C::kRem, w);
           tmem_wait_ld();
           uint4* o4 = reinterpret_cast<uint4*>(go + 64);
 #pragma unroll

@@ -112,7 +112,8 @@ attn_window_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
       if (kHasRem) tma_load_2d(smem + C::oRr, &tmR32, r_full, 64, 0);
       int it = 0;
       for (int p = blockIdx.x; p < nprob; p += gridDim.x, ++it) {
-        const int win = p / heads, head = p - win * heads;
+        const int pr = nprob - 1 - p;      // back to front: the qkv GEMM's last tiles are still in L2
+        const int win = pr / heads, head = pr - win * heads;
         const int row0 = win * kT;
         const int cq = head * HD, ck = heads * HD + head * HD, cv = 2 * heads * HD + head * HD;
         mbar_wait(qk_empty, (it & 1) ^ 1);
@@ -196,7 +197,8 @@ attn_window_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
     int it = 0;
     for (int p = blockIdx.x; p < nprob; p += gridDim.x, ++it) {
       const uint32_t ph = it & 1;
-      const int win = p / heads, head = p - win * heads;
+      const int pr = nprob - 1 - p;      // back to front: the qkv GEMM's last tiles are still in L2
+        const int win = pr / heads, head = pr - win * heads;
       mbar_wait(&s_full[t], ph);
       tc_fence_after();
       // ---- bias tables: bh[ky] = G[qy - ky + 13], bw[kx] = G[32 + qx - kx + 13] (pre-multiplied by log2 e)
