@@ -37,9 +37,14 @@ struct WinCfg {
   static constexpr int kOperand = kMain + kRemB;
   static constexpr int kRMain = 64 * 128, kRRem = kRem ? 64 * 32 : 0;
   // shared-memory map (offsets from a 1024-byte aligned base): swizzle-128 parts first, then swizzle-32 parts
-  static constexpr int oQm = 0, oKm = kMain, oV0m = 2 * kMain, oV1m = 3 * kMain, oRm = 4 * kMain;
-  static constexpr int oQr = oRm + kRMain, oKr = oQr + kRemB, oV0r = oKr + kRemB, oV1r = oV0r + kRemB,
-                       oRr = oV1r + kRemB;
+  // V's second box is a full 64-column swizzle-128 box over head columns [HD-32, HD+32): one LBO after the first it
+  // lets a single N = 96 MN-major MMA per 16 keys produce the whole head (columns 64..HD-1 land in O columns
+  // 96-kRem..95) instead of an N = 64 plus an N = 16 instruction - MMA issue is what bounds the P.V step
+  static constexpr int kVRemB = kRem ? kMain : 0;
+  static constexpr int kVOperand = kMain + kVRemB;
+  static constexpr int oQm = 0, oKm = kMain, oV0m = 2 * kMain, oV1m = 3 * kMain, oV0r = 4 * kMain,
+                       oV1r = oV0r + kVRemB, oRm = oV1r + kVRemB;
+  static constexpr int oQr = oRm + kRMain, oKr = oQr + kRemB, oRr = oKr + kRemB;
   static constexpr int oStage = oRr + kRRem;                // 256 threads x 27 floats
   static constexpr int oBar = oStage + 256 * 27 * 4;
   static constexpr int kSmem = oBar + 256 + 1024;
@@ -126,9 +131,9 @@ attn_window_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
         }
         const int s = it & 1;
         mbar_wait(&v_empty[s], ((it >> 1) & 1) ^ 1);
-        mbar_expect_tx(&v_full[s], C::kOperand);
+        mbar_expect_tx(&v_full[s], C::kVOperand);
         tma_load_2d(smem + (s ? C::oV1m : C::oV0m), &tm128, &v_full[s], cv, row0);
-        if (kHasRem) tma_load_2d(smem + (s ? C::oV1r : C::oV0r), &tm32, &v_full[s], cv + 64, row0);
+        if (kHasRem) tma_load_2d(smem + (s ? C::oV1r : C::oV0r), &tm128, &v_full[s], cv + HD - 32, row0);
       }
     }
   } else if (warp == 1) {
@@ -136,7 +141,7 @@ attn_window_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
       constexpr uint32_t idS = umma_idesc_bf16(128, kRowsPad, false, false);
       constexpr uint32_t idG = umma_idesc_bf16(128, 64, false, false);
       constexpr uint32_t idO64 = umma_idesc_bf16(128, 64, false, true);
-      constexpr uint32_t idO16 = umma_idesc_bf16(128, 16, false, true);
+      constexpr uint32_t idO96 = umma_idesc_bf16(128, 96, false, true);
       const uint32_t sQm = smem_u32(smem + C::oQm), sKm = smem_u32(smem + C::oKm), sRm = smem_u32(smem + C::oRm);
       const uint32_t sQr = smem_u32(smem + C::oQr), sKr = smem_u32(smem + C::oKr), sRr = smem_u32(smem + C::oRr);
       mbar_wait(r_full, 0);
@@ -174,10 +179,9 @@ attn_window_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
           tc_fence_after();
           const uint32_t dO = tmem + t * kSCols + kOCol, aP = tmem + t * kSCols;
 #pragma unroll
-          for (int ks = 0; ks < kRowsPad / 16; ++ks) {
-            umma_ts_bf16(dO, aP + ks * 8, umma_desc(sVm + ks * 2048, 1024, 1024, 2), idO64, ks != 0);
-            if (kHasRem) umma_ts_bf16(dO + 64, aP + ks * 8, umma_desc(sVr + ks * 512, 256, 256, 6), idO16, ks != 0);
-          }
+          for (int ks = 0; ks < kRowsPad / 16; ++ks)
+            umma_ts_bf16(dO, aP + ks * 8, umma_desc(sVm + ks * 2048, 1024, kHasRem ? sVr - sVm : 1024, 2),
+                         kHasRem ? idO96 : idO64, ks != 0);
           umma_commit(&o_full[t]);
         }
         umma_commit(&v_empty[s]);
@@ -324,7 +328,7 @@ attn_window_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
         }
         if (kHasRem) {
           uint32_t w[16];
-          tmem_ld_32x32_16(tl + t * kSCols + kOCol + 64, w);
+          tmem_ld_32x32_16(tl + t * kSCols + kOCol + 96 - C::kRem, w);
           tmem_wait_ld();
           if (vst) {
             uint4* o4 = reinterpret_cast<uint4*>(go + 64);
