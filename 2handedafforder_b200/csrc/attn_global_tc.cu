@@ -82,7 +82,7 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
   uint64_t* o_full = p_full + 2;                  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = (int)uniform_u32(threadIdx.x >> 5), lane = threadIdx.x & 31;
   const int nitems = nbatch * heads * kQBlocks;
 
   if (warp == 0 && lane == 0) {
@@ -145,66 +145,77 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
     }
   } else if (warp == 1) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-    if (lane == 0) {
-      constexpr uint32_t idS = umma_idesc_bf16(128, kBKeys, false, false);
-      constexpr uint32_t idO64 = umma_idesc_bf16(128, 64, false, true);
-      constexpr uint32_t idO128 = umma_idesc_bf16(128, 128, false, true);
-      const uint32_t sQm = smem_u32(smem + C::oQm), sQr = smem_u32(smem + C::oQr);
-      const uint32_t sKm = smem_u32(smem + C::oKm), sKr = smem_u32(smem + C::oKr);
-      const uint32_t sVm = smem_u32(smem + C::oVm), sVr = smem_u32(smem + C::oVr);
-      auto issue_S = [&](int t, int ks) {
-        const uint32_t aM = sQm + t * C::kMain, aR = sQr + t * C::kRemB;
-        const uint32_t bM = sKm + ks * C::kMain, bR = sKr + ks * C::kRemB;
+    // All 32 lanes run the loops (warp-uniform control flow, uniform-register descriptors); one elected lane issues
+    // the tcgen05 instructions.
+    const bool leader = elect_one();
+    const uint32_t tm = uniform_u32(tmem);
+    constexpr uint32_t idS = umma_idesc_bf16(128, kBKeys, false, false);
+    constexpr uint32_t idO64 = umma_idesc_bf16(128, 64, false, true);
+    constexpr uint32_t idO128 = umma_idesc_bf16(128, 128, false, true);
+    const uint32_t sQm = smem_u32(smem + C::oQm), sQr = smem_u32(smem + C::oQr);
+    const uint32_t sKm = smem_u32(smem + C::oKm), sKr = smem_u32(smem + C::oKr);
+    const uint32_t sVm = smem_u32(smem + C::oVm), sVr = smem_u32(smem + C::oVr);
+    const uint32_t lbo = kHasRem ? (sVr - sVm) : 1024;   // V main box -> second box of the same stage
+    auto issue_S = [&](int t, int ks) {
+      const uint32_t aM = sQm + t * C::kMain, aR = sQr + t * C::kRemB;
+      const uint32_t bM = sKm + ks * C::kMain, bR = sKr + ks * C::kRemB;
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          umma_ss<false>(tmem + t * 128, umma_desc(aM + k * 32, 1024, 0, 2), umma_desc(bM + k * 32, 1024, 0, 2), idS,
-                         k != 0);
-        if (kHasRem) umma_ss<false>(tmem + t * 128, umma_desc(aR, 256, 0, 6), umma_desc(bR, 256, 0, 6), idS, 1);
-      };
-      int it = 0, kc = 0;          // kc: index of the K/V tile of iteration 0 of this item in the rings
-      uint32_t np[2] = {0, 0};     // P tiles consumed per M tile (parity of p_full)
-      for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it, kc += kNIter) {
-        mbar_wait(q_full, it & 1);
-        {
-          const int s = kc % kStagesG;
-          mbar_wait(&k_full[s], (kc / kStagesG) & 1);
-          tc_fence_after();
-          issue_S(0, s);
-          umma_commit(&s_full[0]);
-          issue_S(1, s);
+      for (int k = 0; k < 4; ++k) {
+        const uint64_t da = umma_desc(aM + k * 32, 1024, 0, 2), db = umma_desc(bM + k * 32, 1024, 0, 2);
+        if (leader) umma_ss<false>(tm + t * 128, da, db, idS, k != 0);
+      }
+      if (kHasRem) {
+        const uint64_t da = umma_desc(aR, 256, 0, 6), db = umma_desc(bR, 256, 0, 6);
+        if (leader) umma_ss<false>(tm + t * 128, da, db, idS, 1);
+      }
+    };
+    int it = 0, kc = 0;          // kc: index of the K/V tile of iteration 0 of this item in the rings
+    uint32_t np0 = 0, np1 = 0;   // P tiles consumed per M tile (parity of p_full)
+    for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it, kc += kNIter) {
+      mbar_wait(q_full, it & 1);
+      {
+        const int s = kc % kStagesG;
+        mbar_wait(&k_full[s], (kc / kStagesG) & 1);
+        tc_fence_after();
+        issue_S(0, s);
+        if (leader) umma_commit(&s_full[0]);
+        issue_S(1, s);
+        if (leader) {
           umma_commit(&s_full[1]);
           umma_commit(&k_empty[s]);
         }
+      }
 #pragma unroll 1
-        for (int j = 0; j < kNIter; ++j) {
-          const int sv = (kc + j) % kStagesG;
-          const int sk = (kc + j + 1) % kStagesG;
-          const bool more = j + 1 < kNIter;
-          if (more) mbar_wait(&k_full[sk], ((kc + j + 1) / kStagesG) & 1);
-          mbar_wait(&v_full[sv], ((kc + j) / kStagesG) & 1);
-#pragma unroll 1
-          for (int t = 0; t < 2; ++t) {
-            mbar_wait(&p_full[t], np[t] & 1);
-            ++np[t];
-            tc_fence_after();
-            const uint32_t dO = tmem + kOColG + t * 128, aP = tmem + t * 128;
-            const uint32_t bM = sVm + sv * C::kMain;
-            const uint32_t lbo = kHasRem ? (sVr - sVm) : 1024;   // main box -> second box of the same stage
+      for (int j = 0; j < kNIter; ++j) {
+        const int sv = (kc + j) % kStagesG;
+        const int sk = (kc + j + 1) % kStagesG;
+        const bool more = j + 1 < kNIter;
+        if (more) mbar_wait(&k_full[sk], ((kc + j + 1) / kStagesG) & 1);
+        mbar_wait(&v_full[sv], ((kc + j) / kStagesG) & 1);
 #pragma unroll
-            for (int ks = 0; ks < kBKeys / 16; ++ks)
-              umma_ts_bf16(dO, aP + ks * 8, umma_desc(bM + ks * 2048, 1024, lbo, 2), kHasRem ? idO128 : idO64,
-                           (j | ks) != 0);
-            if (t == 1) umma_commit(&v_empty[sv]);
-            if (more) {
-              issue_S(t, sk);
+        for (int t = 0; t < 2; ++t) {
+          mbar_wait(&p_full[t], (t ? np1 : np0) & 1);
+          if (t) ++np1; else ++np0;
+          tc_fence_after();
+          const uint32_t dO = tm + kOColG + t * 128, aP = tm + t * 128;
+          const uint32_t bM = sVm + sv * C::kMain;
+#pragma unroll
+          for (int ks = 0; ks < kBKeys / 16; ++ks) {
+            const uint64_t db = umma_desc(bM + ks * 2048, 1024, lbo, 2);
+            if (leader) umma_ts_bf16(dO, aP + ks * 8, db, kHasRem ? idO128 : idO64, (j | ks) != 0);
+          }
+          if (t == 1 && leader) umma_commit(&v_empty[sv]);
+          if (more) {
+            issue_S(t, sk);
+            if (leader) {
               umma_commit(&s_full[t]);
               if (t == 1) {
                 umma_commit(&k_empty[sk]);
                 if (j + 2 == kNIter) umma_commit(q_empty);   // last score MMAs of this item: Q tiles are dead
               }
-            } else {
-              umma_commit(&o_full[t]);
             }
+          } else {
+            if (leader) umma_commit(&o_full[t]);
           }
         }
       }

@@ -101,6 +101,17 @@ __device__ __forceinline__ void umma_ss(uint32_t tmem_d, uint64_t adesc, uint64_
   }
 }
 // Arrive on an mbarrier once all previously issued tcgen05.mma of this thread have completed.
+// One lane of a converged warp (elect.sync).  The MMA warps run their loops with all 32 lanes and wrap only the
+// tcgen05 instructions in `if (leader)`: descriptors and TMEM addresses computed in warp-uniform code stay in uniform
+// registers, whereas inside an `if (lane == 0)` region every operand goes through an ELECT / R2UR.BROADCAST waterfall
+// (about a dozen dependent instructions per MMA, which bounds kernels that issue many small MMAs).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t p;
+  asm volatile("{\n.reg .pred e;\nelect.sync _|e, 0xffffffff;\nselp.u32 %0, 1, 0, e;\n}\n" : "=r"(p));
+  return p != 0;
+}
+// warp-uniform copy of a value (lane 0's): lets the compiler prove uniformity
+__device__ __forceinline__ uint32_t uniform_u32(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
