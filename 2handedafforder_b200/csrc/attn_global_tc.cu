@@ -7,8 +7,9 @@
 // Flash-style, the 4096 x 4096 score matrix never exists in HBM (the reference materialises it, 1 GB fp32 per frame,
 // and touches it ~5x).  A persistent CTA owns 256 query rows (two M = 128 tiles that ping-pong on the tensor core)
 // of one (frame, head) and streams 128-key tiles:
-//   warp 0      TMA producer: Q tiles once per work item; K and V tiles through two 4-stage rings
-//               (head dim 80 = one SWIZZLE_128B box of 64 columns + one SWIZZLE_32B box of 16)
+//   warp 0      TMA producer: Q tiles once per work item; K and V tiles through two 3-stage rings
+//               (head dim 80: Q / K = one SWIZZLE_128B box of 64 columns + one SWIZZLE_32B box of 16;
+//               V = two SWIZZLE_128B boxes, columns [0,64) and [16,80), consumed by one N = 128 MMA)
 //   warp 1      tcgen05.mma issuer: S_t = Q_t K_j^T into TMEM, then O_t += P_t V_j with P read from TMEM and V as an
 //               MN-major B operand; S_t(j+1) is issued right behind it so the tensor core works while the other
 //               tile's softmax runs
@@ -238,18 +239,27 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
       const int bhh = ir / kQBlocks, qb = ir - bhh * kQBlocks;
       const int b = bhh / heads, head = bhh - b * heads;
       const int qrow = qb * 256 + t * 128 + rl;          // token index inside the frame
-      const int qy = qrow >> 6, qx = qrow & 63;
+      const int qy = qrow >> 6;
       const __half* g = G + ((long)b * kGT + qrow) * ldg + head * 256;
-      // w-bias: bw[kx] = G[128 + qx - kx + 63], pre-multiplied by log2 e
+      // w-bias: the G GEMM stores bw[kx] = q . Rw[qx - kx + 63] at G[128 + kx] (RM_RELW_SHIFT): eight 16-byte loads;
+      // pre-multiplied by log2 e
       float bw[64];
       float bwmax = -INFINITY;
       {
-        const __half* gw = g + 128 + qx;
+        const uint4* gw = reinterpret_cast<const uint4*>(g + 128);
 #pragma unroll
-        for (int kx = 0; kx < 64; ++kx) {
-          bw[kx] = __half2float(__ldg(gw + 63 - kx)) * kLog2e;
-          bwmax = fmaxf(bwmax, bw[kx]);
+        for (int i = 0; i < 8; ++i) {
+          const uint4 u = __ldg(gw + i);
+          const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w4[q]));
+            bw[8 * i + 2 * q] = f.x * kLog2e;
+            bw[8 * i + 2 * q + 1] = f.y * kLog2e;
+          }
         }
+#pragma unroll
+        for (int kx = 0; kx < 64; ++kx) bwmax = fmaxf(bwmax, bw[kx]);
       }
       const __half* gh = g + qy + 63;                    // h-bias of key row ky: gh[-ky]
       float bh0 = __half2float(__ldg(gh)) * kLog2e, bh1 = __half2float(__ldg(gh - 1)) * kLog2e;

@@ -209,7 +209,7 @@ __global__ void relpos_pack_g_kernel(const float* __restrict__ rel_h, const floa
   float v = 0.f;
   if (c < hd) {
     if (r < 127) v = rel_h[r * hd + c];
-    else if (r >= 128 && r < 255) v = rel_w[(r - 128) * hd + c];
+    else if (r >= 128 && r < 255) v = rel_w[(254 - r) * hd + c];   // w table reversed: row 128 + j = Rw[126 - j]
   }
   out[i] = __float2bfloat16(v);
 }

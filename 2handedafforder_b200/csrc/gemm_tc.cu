@@ -421,7 +421,17 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
         uint2 t;
         t.x = *reinterpret_cast<uint32_t*>(&h0);
         t.y = *reinterpret_cast<uint32_t*>(&h1);
-        if (st) *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(e.out) + orow[i] * (long)e.ld_out + col + out_off) = t;
+        __half* orp = reinterpret_cast<__half*>(e.out) + orow[i] * (long)e.ld_out + out_off;
+        if (e.rowmap == RM_RELW_SHIFT && col >= 128) {
+          // per-row shift: source column 128 + j goes to 128 + (j - 63 + qx) when that lands in [0, 64)
+          const int kx0 = (int)col - 191 + (orow[i] & 63);
+          const __half hv[4] = {__low2half(h0), __high2half(h0), __low2half(h1), __high2half(h1)};
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            if (st && (unsigned)(kx0 + q) < 64u) orp[128 + kx0 + q] = hv[q];
+        } else if (st) {
+          *reinterpret_cast<uint2*>(orp + col) = t;
+        }
       } else {
         if constexpr (MODE == GM_BIAS_GELU_BF16) {
           gelu_erf_poly2(x.x, x.y);

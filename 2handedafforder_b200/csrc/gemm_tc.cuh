@@ -20,6 +20,8 @@ enum GemmMode : int {
 enum RowMap : int {
   RM_IDENT = 0,
   RM_WINDOW_TO_TOKEN = 1,  // input rows are in 14x14-window order (25 windows x 196 per frame, pad rows skipped)
+  RM_RELW_SHIFT = 3,       // fp16 mode, global rel-pos projections: columns >= 128 of token row r hold q.Rw[126-j];
+                           // they are stored shifted by qx = r % 64 so that out[128 + kx] = q.Rw[qx - kx + 63], kx < 64
   RM_TOKEN_TO_WINDOW = 2,  // bf16 modes: input rows in token order (B*4096), output rows scattered into 14x14-window order (B*4900)
 };
 

@@ -30,7 +30,7 @@ cudaError_t launch_relpos_pack_g(const float* rel_h, const float* rel_w, int hd,
 // ---- attn.cu
 // qkv: (nbatch*S*S, 3*heads*hd) bf16 packed [q | k | v] per row, heads-major inside each; out (rows, heads*hd).
 // relh/relw: bf16 tables from launch_relpos_pack.
-// S == 64 additionally needs relg = (256, 128) bf16 [rel_pos_h (127 rows) ; 0 ; rel_pos_w (127 rows) ; 0], columns
+// S == 64 additionally needs relg = (256, 128) bf16 [rel_pos_h (127 rows) ; 0 ; rel_pos_w REVERSED (127 rows) ; 0], columns
 // >= hd zero (launch_relpos_pack_g), and gbuf = (nbatch*4096, heads*256) fp16 scratch for the bias projections.
 cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int heads, int hd,
                              const __nv_bfloat16* relh, const __nv_bfloat16* relw, const __nv_bfloat16* relg,
