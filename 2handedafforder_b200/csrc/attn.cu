@@ -31,7 +31,10 @@ cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int he
     e.batch = heads;
     e.a_batch_off = hd;
     e.out_batch_off = 256;
-    e.rowmap = RM_RELW_SHIFT;   // w part stored as the 64 biases of the row's own qx (attn_global_tc.cu reads 128 B)
+    // w part stored as the 64 biases of the row's own qx, in units of the softmax scale (x sqrt(hd)): the attention
+    // kernel adds them to q.k on the tensor core (S += Gw E) before scaling by hd^-1/2
+    e.rowmap = RM_RELW_SHIFT;
+    e.relw_scale = sqrtf((float)hd);
     cudaError_t err = gemm_tc(false, GM_F16, qkv, 3 * heads * hd, relg, 128, nbatch * kTokens, 256, 128, e, s);
     if (err != cudaSuccess) return err;
     return launch_attention_global_tc(qkv, nbatch, heads, hd, reinterpret_cast<const __half*>(gbuf), out, s);

@@ -14,7 +14,8 @@
 //               MN-major B operand; S_t(j+1) is issued right behind it so the tensor core works while the other
 //               tile's softmax runs
 //   warps 4-7 / 8-11   softmax of tile 0 / tile 1, one thread per query row: a 128-key tile is two image rows, so
-//               the h-bias is two scalars per tile and the w-bias 64 registers; lazy rescaling (O and the row sum are
+//               the h-bias is two scalars per tile; the w-bias is added on the tensor core (S_t += Gw_t E with a
+//               one-hot E, see GlbCfg); lazy rescaling (O and the row sum are
 //               only rescaled when the running maximum grows by more than 2^8); P (bf16) goes back into the S columns
 // The bias projections G = Q [Rh; Rw]^T come from a batched tcgen05 GEMM (gemm_tc GM_F16) as fp16.
 #include <cudaTypedefs.h>
@@ -31,7 +32,8 @@ constexpr int kGT = kTokens;          // 4096
 constexpr int kBKeys = 128;           // keys per tile = two image rows
 constexpr int kNIter = kGT / kBKeys;  // 32
 constexpr int kQBlocks = kGT / 256;   // 16 work items per (frame, head)
-constexpr int kStagesG = 3;
+constexpr int kStagesK = 2;   // K tiles in flight (20 KB each)
+constexpr int kStagesV = 3;   // V tiles in flight (32 KB each)
 constexpr int kThreadsG = 384;
 constexpr int kOColG = 256;           // O_t at kOColG + t * 128
 
@@ -46,13 +48,18 @@ struct GlbCfg {
   // of an N = 64 and an N = 16 instruction - the single issuing thread is the bottleneck of the P.V step
   static constexpr int kVRemB = kRem ? kMain : 0;
   static constexpr int kVTile = kMain + kVRemB;
+  // w-bias through the tensor core: S_t += Gw_t E, Gw_t = the 128 x 64 fp16 tile of the row's w-biases (stored by the
+  // G GEMM as q . Rw[qx - kx + 63] * sqrt(hd), kx < 64) and E the constant 64 x 128 one-hot matrix E[kx][n] = (n % 64
+  // == kx): exact in fp32, and the softmax threads keep no per-column bias registers
   static constexpr int oQm = 0;                           // 2 tiles
-  static constexpr int oKm = 2 * kMain;                   // kStagesG tiles
-  static constexpr int oVm = oKm + kStagesG * kMain;
-  static constexpr int oQr = oVm + kStagesG * kMain;
+  static constexpr int oGw = 2 * kMain;                   // 2 tiles (fp16)
+  static constexpr int oE = oGw + 2 * kMain;              // 128 rows (n) x 64 (kx) fp16, K-major, swizzle-128
+  static constexpr int oKm = oE + kMain;                  // kStagesK tiles
+  static constexpr int oVm = oKm + kStagesK * kMain;      // kStagesV tiles
+  static constexpr int oVr = oVm + kStagesV * kMain;      // kStagesV second boxes
+  static constexpr int oQr = oVr + kStagesV * kVRemB;
   static constexpr int oKr = oQr + 2 * kRemB;
-  static constexpr int oVr = oKr + kStagesG * kRemB;
-  static constexpr int oBar = oVr + kStagesG * kVRemB;
+  static constexpr int oBar = oKr + kStagesK * kRemB;
   static constexpr int kSmem = oBar + 512 + 1024;
 };
 
@@ -65,6 +72,7 @@ __device__ __forceinline__ float ex2_fast(float x) {
 template <int HD>
 __global__ void __launch_bounds__(kThreadsG, 1)
 attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tm32,
+                      const __grid_constant__ CUtensorMap tmG,
                       const __half* __restrict__ G, __nv_bfloat16* __restrict__ out, int nbatch, int heads,
                       float scale) {
   using C = GlbCfg<HD>;
@@ -74,11 +82,11 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::oBar);
   uint64_t* q_full = bars + 0;
   uint64_t* q_empty = bars + 1;
-  uint64_t* k_full = bars + 2;                    // [kStagesG]
-  uint64_t* k_empty = k_full + kStagesG;
-  uint64_t* v_full = k_empty + kStagesG;
-  uint64_t* v_empty = v_full + kStagesG;
-  uint64_t* s_full = v_empty + kStagesG;          // [2]
+  uint64_t* k_full = bars + 2;                    // [kStagesK]
+  uint64_t* k_empty = k_full + kStagesK;
+  uint64_t* v_full = k_empty + kStagesK;          // [kStagesV]
+  uint64_t* v_empty = v_full + kStagesV;
+  uint64_t* s_full = v_empty + kStagesV;          // [2]
   uint64_t* p_full = s_full + 2;                  // [2]
   uint64_t* o_full = p_full + 2;                  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
@@ -89,13 +97,16 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm128);
     if (kHasRem) tma_prefetch_desc(&tm32);
+    tma_prefetch_desc(&tmG);
   }
   if (warp == 1 && lane == 0) {
     mbar_init(q_full, 1);
     mbar_init(q_empty, 1);
-    for (int i = 0; i < kStagesG; ++i) {
+    for (int i = 0; i < kStagesK; ++i) {
       mbar_init(&k_full[i], 1);
       mbar_init(&k_empty[i], 1);
+    }
+    for (int i = 0; i < kStagesV; ++i) {
       mbar_init(&v_full[i], 1);
       mbar_init(&v_empty[i], 1);
     }
@@ -107,6 +118,16 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
     mbar_fence_init();
   }
   if (warp == 2) tmem_alloc(tmem_slot, 512);
+  // one-hot B operand of the w-bias MMA: row n (key inside the tile) holds fp16 1.0 at column n % 64
+  // (K-major, 128-byte rows, 16-byte chunk index XOR row % 8 = the SWIZZLE_128B pattern the descriptor expects)
+  for (int i = threadIdx.x; i < C::kMain / 16; i += kThreadsG)
+    reinterpret_cast<uint4*>(smem + C::oE)[i] = make_uint4(0u, 0u, 0u, 0u);
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    const int n = threadIdx.x, kx = n & 63;
+    *reinterpret_cast<uint16_t*>(smem + C::oE + n * 128 + (((kx >> 3) ^ (n & 7)) << 4) + (kx & 7) * 2) = 0x3C00;
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -125,19 +146,20 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
         const int row0 = b * kGT;
         const int cq = head * HD, ck = heads * HD + head * HD, cv = 2 * heads * HD + head * HD;
         mbar_wait(q_empty, (it & 1) ^ 1);
-        mbar_expect_tx(q_full, 2 * C::kTile);
+        mbar_expect_tx(q_full, 2 * C::kTile + 2 * C::kMain);
         for (int t = 0; t < 2; ++t) {
+          tma_load_2d(smem + C::oGw + t * C::kMain, &tmG, q_full, head * 256 + 128, row0 + qb * 256 + t * 128);
           tma_load_2d(smem + C::oQm + t * C::kMain, &tm128, q_full, cq, row0 + qb * 256 + t * 128);
           if (kHasRem) tma_load_2d(smem + C::oQr + t * C::kRemB, &tm32, q_full, cq + 64, row0 + qb * 256 + t * 128);
         }
         for (int j = 0; j < kNIter; ++j, ++kc) {
-          const int s = kc % kStagesG;
-          const uint32_t ph = (kc / kStagesG) & 1;
-          mbar_wait(&k_empty[s], ph ^ 1);
-          mbar_expect_tx(&k_full[s], C::kTile);
-          tma_load_2d(smem + C::oKm + s * C::kMain, &tm128, &k_full[s], ck, row0 + j * kBKeys);
-          if (kHasRem) tma_load_2d(smem + C::oKr + s * C::kRemB, &tm32, &k_full[s], ck + 64, row0 + j * kBKeys);
-          mbar_wait(&v_empty[s], ph ^ 1);
+          const int sk = kc % kStagesK;
+          mbar_wait(&k_empty[sk], ((kc / kStagesK) & 1) ^ 1);
+          mbar_expect_tx(&k_full[sk], C::kTile);
+          tma_load_2d(smem + C::oKm + sk * C::kMain, &tm128, &k_full[sk], ck, row0 + j * kBKeys);
+          if (kHasRem) tma_load_2d(smem + C::oKr + sk * C::kRemB, &tm32, &k_full[sk], ck + 64, row0 + j * kBKeys);
+          const int s = kc % kStagesV;
+          mbar_wait(&v_empty[s], ((kc / kStagesV) & 1) ^ 1);
           mbar_expect_tx(&v_full[s], C::kVTile);
           tma_load_2d(smem + C::oVm + s * C::kMain, &tm128, &v_full[s], cv, row0 + j * kBKeys);
           if (kHasRem) tma_load_2d(smem + C::oVr + s * C::kVRemB, &tm128, &v_full[s], cv + HD - 64, row0 + j * kBKeys);
@@ -153,6 +175,9 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
     constexpr uint32_t idS = umma_idesc_bf16(128, kBKeys, false, false);
     constexpr uint32_t idO64 = umma_idesc_bf16(128, 64, false, true);
     constexpr uint32_t idO128 = umma_idesc_bf16(128, 128, false, true);
+    // fp16 x fp16 -> fp32, both K-major, M = 128, N = 128 (a_format = b_format = 0)
+    constexpr uint32_t idB = (1u << 4) | (uint32_t(kBKeys >> 3) << 17) | (uint32_t(128 >> 4) << 24);
+    const uint32_t sGw = smem_u32(smem + C::oGw), sE = smem_u32(smem + C::oE);
     const uint32_t sQm = smem_u32(smem + C::oQm), sQr = smem_u32(smem + C::oQr);
     const uint32_t sKm = smem_u32(smem + C::oKm), sKr = smem_u32(smem + C::oKr);
     const uint32_t sVm = smem_u32(smem + C::oVm), sVr = smem_u32(smem + C::oVr);
@@ -169,14 +194,20 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
         const uint64_t da = umma_desc(aR, 256, 0, 6), db = umma_desc(bR, 256, 0, 6);
         if (leader) umma_ss<false>(tm + t * 128, da, db, idS, 1);
       }
+      // + w-bias: S_t += Gw_t E
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint64_t da = umma_desc(sGw + t * C::kMain + k * 32, 1024, 0, 2), db = umma_desc(sE + k * 32, 1024, 0, 2);
+        if (leader) umma_ss<false>(tm + t * 128, da, db, idB, 1);
+      }
     };
     int it = 0, kc = 0;          // kc: index of the K/V tile of iteration 0 of this item in the rings
     uint32_t np0 = 0, np1 = 0;   // P tiles consumed per M tile (parity of p_full)
     for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it, kc += kNIter) {
       mbar_wait(q_full, it & 1);
       {
-        const int s = kc % kStagesG;
-        mbar_wait(&k_full[s], (kc / kStagesG) & 1);
+        const int s = kc % kStagesK;
+        mbar_wait(&k_full[s], (kc / kStagesK) & 1);
         tc_fence_after();
         issue_S(0, s);
         if (leader) umma_commit(&s_full[0]);
@@ -188,11 +219,11 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
       }
 #pragma unroll 1
       for (int j = 0; j < kNIter; ++j) {
-        const int sv = (kc + j) % kStagesG;
-        const int sk = (kc + j + 1) % kStagesG;
+        const int sv = (kc + j) % kStagesV;
+        const int sk = (kc + j + 1) % kStagesK;
         const bool more = j + 1 < kNIter;
-        if (more) mbar_wait(&k_full[sk], ((kc + j + 1) / kStagesG) & 1);
-        mbar_wait(&v_full[sv], ((kc + j) / kStagesG) & 1);
+        if (more) mbar_wait(&k_full[sk], ((kc + j + 1) / kStagesK) & 1);
+        mbar_wait(&v_full[sv], ((kc + j) / kStagesV) & 1);
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
           mbar_wait(&p_full[t], (t ? np1 : np0) & 1);
@@ -241,26 +272,6 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
       const int qrow = qb * 256 + t * 128 + rl;          // token index inside the frame
       const int qy = qrow >> 6;
       const __half* g = G + ((long)b * kGT + qrow) * ldg + head * 256;
-      // w-bias: the G GEMM stores bw[kx] = q . Rw[qx - kx + 63] at G[128 + kx] (RM_RELW_SHIFT): eight 16-byte loads;
-      // pre-multiplied by log2 e
-      float bw[64];
-      float bwmax = -INFINITY;
-      {
-        const uint4* gw = reinterpret_cast<const uint4*>(g + 128);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const uint4 u = __ldg(gw + i);
-          const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w4[q]));
-            bw[8 * i + 2 * q] = f.x * kLog2e;
-            bw[8 * i + 2 * q + 1] = f.y * kLog2e;
-          }
-        }
-#pragma unroll
-        for (int kx = 0; kx < 64; ++kx) bwmax = fmaxf(bwmax, bw[kx]);
-      }
       const __half* gh = g + qy + 63;                    // h-bias of key row ky: gh[-ky]
       float bh0 = __half2float(__ldg(gh)) * kLog2e, bh1 = __half2float(__ldg(gh - 1)) * kLog2e;
       float m_used = -INFINITY, l = 0.f;
@@ -290,7 +301,7 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
           mx3 = fmaxf(mx3, __uint_as_float(v[i + 3]));
         }
         const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-        const float Mt = mx * cs + bwmax + fmaxf(bh0, bh1);
+        const float Mt = mx * cs + fmaxf(bh0, bh1);   // the scores already hold the w-bias (in units of 1/cs)
         const bool grow = Mt > m_used + 8.f;
         if (__any_sync(0xffffffffu, grow)) {
           const float m_new = grow ? Mt : m_used;
@@ -323,7 +334,8 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
           }
         }
         const float c0 = bh0 - m_used, c1 = bh1 - m_used;
-        // ---- p = 2^(s*cs + bw + bh - m), row sum (4 partial chains), P (bf16 pairs) into the first 64 columns of S_t
+        // ---- p = 2^(s*cs + bh - m) (s holds q.k + w-bias), row sum (4 partial chains), P (bf16 pairs) into the
+        // first 64 columns of S_t
         float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -331,11 +343,10 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
           uint32_t u[16];
 #pragma unroll
           for (int i = 0; i < 32; i += 4) {
-            const int k = (c & 1) * 32 + i;
-            const float p0 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i]), cs, bw[k]) + cc);
-            const float p1 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 1]), cs, bw[k + 1]) + cc);
-            const float p2 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 2]), cs, bw[k + 2]) + cc);
-            const float p3 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 3]), cs, bw[k + 3]) + cc);
+            const float p0 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i]), cs, cc));
+            const float p1 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 1]), cs, cc));
+            const float p2 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 2]), cs, cc));
+            const float p3 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 3]), cs, cc));
             sum0 += p0;
             sum1 += p1;
             sum2 += p2;
@@ -422,9 +433,12 @@ cudaError_t launch_global(const __nv_bfloat16* qkv, int nbatch, int heads, const
   } else {
     tm32 = tm128;
   }
+  CUtensorMap tmG;   // fp16 bias projections (rows, heads * 256): the 64 w-biases of a row start at column 128
+  e = make_tmap_2d(&tmG, G, 2, rows, (long)heads * 256, (long)heads * 256, 64, 128, 128);
+  if (e != cudaSuccess) return e;
   const int nitems = nbatch * heads * kQBlocks;
   const int grid = nitems < gemm_num_sms() ? nitems : gemm_num_sms();
-  attn_global_tc_kernel<HD><<<grid, kThreadsG, C::kSmem, s>>>(tm128, tm32, G, out, nbatch, heads,
+  attn_global_tc_kernel<HD><<<grid, kThreadsG, C::kSmem, s>>>(tm128, tm32, tmG, G, out, nbatch, heads,
                                                             1.0f / sqrtf((float)HD));
   return cudaGetLastError();
 }

@@ -425,7 +425,8 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
         if (e.rowmap == RM_RELW_SHIFT && col >= 128) {
           // per-row shift: source column 128 + j goes to 128 + (j - 63 + qx) when that lands in [0, 64)
           const int kx0 = (int)col - 191 + (orow[i] & 63);
-          const __half hv[4] = {__low2half(h0), __high2half(h0), __low2half(h1), __high2half(h1)};
+          const __half hv[4] = {__float2half_rn(x.x * e.relw_scale), __float2half_rn(x.y * e.relw_scale),
+                                __float2half_rn(x.z * e.relw_scale), __float2half_rn(x.w * e.relw_scale)};
 #pragma unroll
           for (int q = 0; q < 4; ++q)
             if (st && (unsigned)(kx0 + q) < 64u) orp[128 + kx0 + q] = hv[q];

@@ -34,6 +34,7 @@ struct GemmEpi {
   void* out2 = nullptr;           // GM_LN: optional bf16 copy
   int ld_out = 0;
   int rowmap = RM_IDENT;
+  float relw_scale = 1.f;      // RM_RELW_SHIFT: factor applied (in fp32) to the shifted w columns before the fp16 store
   const float* ln_g = nullptr;
   const float* ln_b = nullptr;
   float ln_eps = 0.f;
