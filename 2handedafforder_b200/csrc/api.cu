@@ -93,10 +93,22 @@ cudaError_t dalloc(b200sam_t* h, T** p, size_t count, bool zero = false) {
     e = cudaMemset(q, 0, count * sizeof(T));
     if (e != cudaSuccess) return e;
   }
-  h->owned.push_back(q);
+  h->alloc_into->push_back(q);
   *p = reinterpret_cast<T*>(q);
   return cudaSuccess;
 }
+
+void free_list(std::vector<void*>& v) {
+  for (void* p : v) cudaFree(p);
+  v.clear();
+}
+
+// routes dalloc() into one of the handle's derived-buffer lists for the lifetime of the scope
+struct AllocScope {
+  b200sam_t* h;
+  AllocScope(b200sam_t* h_, std::vector<void*>* list) : h(h_) { h->alloc_into = list; }
+  ~AllocScope() { h->alloc_into = &h->owned; }
+};
 
 struct ManifestEntry {
   std::string name;
@@ -339,6 +351,70 @@ int finalize_side(b200sam_t* h, int s) {
   return 0;
 }
 
+// bf16 GEMM operand packs, padded rel-pos tables and the permuted neck conv weight of the image encoder
+int finalize_encoder(b200sam_t* h) {
+  free_list(h->derived_enc);
+  AllocScope scope(h, &h->derived_enc);
+  const long D = h->dim;
+  const std::string e = "image_encoder.";
+  if (int r = make_bf16(h, W(h, e + "patch_embed.proj.weight"), D * 768, &h->patch_w)) return r;
+  h->patch_b = W(h, e + "patch_embed.proj.bias");
+  h->pos = W(h, e + "pos_embed");
+  h->blk.assign(h->depth, EncBlock());
+  for (int i = 0; i < h->depth; ++i) {
+    EncBlock& b = h->blk[i];
+    const std::string p = e + "blocks." + std::to_string(i) + ".";
+    for (int gi : h->global_idx) b.global |= (gi == i);
+    b.ln1g = W(h, p + "norm1.weight"); b.ln1b = W(h, p + "norm1.bias");
+    b.ln2g = W(h, p + "norm2.weight"); b.ln2b = W(h, p + "norm2.bias");
+    b.qkv_b = W(h, p + "attn.qkv.bias"); b.proj_b = W(h, p + "attn.proj.bias");
+    b.lin1_b = W(h, p + "mlp.lin1.bias"); b.lin2_b = W(h, p + "mlp.lin2.bias");
+    if (int r = make_bf16(h, W(h, p + "attn.qkv.weight"), 3 * D * D, &b.qkv_w)) return r;
+    if (int r = make_bf16(h, W(h, p + "attn.proj.weight"), D * D, &b.proj_w)) return r;
+    if (int r = make_bf16(h, W(h, p + "mlp.lin1.weight"), 4 * D * D, &b.lin1_w)) return r;
+    if (int r = make_bf16(h, W(h, p + "mlp.lin2.weight"), 4 * D * D, &b.lin2_w)) return r;
+    const int S = b.global ? kGrid : kWin;
+    const int RP = b.global ? 128 : 32;
+    CU(dalloc(h, &b.relh, (size_t)2 * RP * h->hd));   // [relh ; relw] contiguous: one tensor map covers both
+    b.relw = b.relh + (size_t)RP * h->hd;
+    KL(launch_relpos_pack(W(h, p + "attn.rel_pos_h"), S, h->hd, b.relh, 0));
+    KL(launch_relpos_pack(W(h, p + "attn.rel_pos_w"), S, h->hd, b.relw, 0));
+    if (b.global) {
+      CU(dalloc(h, &b.relg, (size_t)256 * 128));
+      KL(launch_relpos_pack_g(W(h, p + "attn.rel_pos_h"), W(h, p + "attn.rel_pos_w"), h->hd, b.relg, 0));
+    }
+  }
+  if (int r = make_bf16(h, W(h, e + "neck.0.weight"), 256 * D, &h->neck0_w)) return r;
+  {
+    // neck.2 Conv2d 3x3 weight (out, in, dy, dx) -> (out, dy, dx, in): the K order of launch_im2col_3x3
+    std::vector<float> w((size_t)256 * 256 * 9), wp(w.size());
+    CU(cudaMemcpy(w.data(), W(h, e + "neck.2.weight"), w.size() * 4, cudaMemcpyDeviceToHost));
+    for (int o = 0; o < 256; ++o)
+      for (int c = 0; c < 256; ++c)
+        for (int t = 0; t < 9; ++t) wp[((size_t)o * 9 + t) * 256 + c] = w[((size_t)o * 256 + c) * 9 + t];
+    float* tmp = nullptr;
+    CU(dalloc(h, &tmp, wp.size()));
+    CU(cudaMemcpy(tmp, wp.data(), wp.size() * 4, cudaMemcpyHostToDevice));
+    if (int r = make_bf16(h, tmp, (long)wp.size(), &h->neck2_w)) return r;
+  }
+  h->neck1g = W(h, e + "neck.1.weight"); h->neck1b = W(h, e + "neck.1.bias");
+  h->neck3g = W(h, e + "neck.3.weight"); h->neck3b = W(h, e + "neck.3.bias");
+  return 0;
+}
+
+// prompt-encoder constants + both mask decoders
+int finalize_decoders(b200sam_t* h) {
+  free_list(h->derived_dec);
+  AllocScope scope(h, &h->derived_dec);
+  // prompt encoder constants (prompt_encoder.py:67-76,182-184): dense PE once, in fp32 (SURVEY.md Appendix A8)
+  CU(dalloc(h, &h->pe_tok, (size_t)kTokens * 256));
+  KL(launch_dense_pe(W(h, "prompt_encoder.pe_layer.positional_encoding_gaussian_matrix"), h->pe_tok, 0));
+  h->no_mask = W(h, "prompt_encoder.no_mask_embed.weight");
+  for (int s = 0; s < 2; ++s)
+    if (int r = finalize_side(h, s)) return r;
+  return 0;
+}
+
 int alloc_workspace(b200sam_t* h) {
   const size_t B = h->max_batch, P = h->max_prompts, D = h->dim;
   CU(dalloc(h, &h->X, B * kTokens * D));
@@ -469,7 +545,9 @@ extern "C" void b200sam_destroy(b200sam_t* h) {
   if (!h) return;
   {
     DeviceGuard g(h->device);
-    for (void* p : h->owned) cudaFree(p);
+    free_list(h->owned);
+    free_list(h->derived_enc);
+    free_list(h->derived_dec);
     if (h->side_stream) cudaStreamDestroy(h->side_stream);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
@@ -554,6 +632,12 @@ extern "C" int b200sam_load_weight(b200sam_t* h, const char* name, const void* p
   for (auto v : shape) n *= v;
   const int esz = dtype == B200SAM_F32 ? 4 : (dtype == B200SAM_BF16 || dtype == B200SAM_F16 ? 2 : 0);
   if (!esz) return fail(h, B200SAM_ERR_INVALID, "bad dtype %d for '%s'", dtype, name);
+  // Not a hot-path call: the masters may still be read by kernels of an earlier compute call (the decoders use the
+  // fp32 masters directly) and the copies below run on the legacy stream, so quiesce the device when the first tensor
+  // of a re-load arrives.  The caller synchronises the stream that produced `ptr` (sam.py::_sync_weights does).
+  if (h->finalized) CU(cudaDeviceSynchronize());
+  if (strncmp(name, "image_encoder.", 14) == 0) h->dirty_enc = true;
+  else h->dirty_dec = true;
   Tensor& t = h->w[name];
   if (!t.d) {
     void* q = nullptr;
@@ -585,58 +669,17 @@ extern "C" int b200sam_finalize_weights(b200sam_t* h) {
   h->prof_on = false;   // one-time packing kernels are not part of any profile
   for (const auto& m : build_manifest(h))
     if (m.required && !h->w.count(m.name)) return fail(h, B200SAM_ERR_STATE, "missing weight '%s'", m.name.c_str());
-  // free derived buffers of a previous finalize (workspace is kept: it is allocated first, see below)
-  // -> simplest correct policy: derived buffers are appended to `owned`; a second finalize leaks nothing on destroy.
-  const long D = h->dim;
-  const std::string e = "image_encoder.";
-  if (int r = make_bf16(h, W(h, e + "patch_embed.proj.weight"), D * 768, &h->patch_w)) return r;
-  h->patch_b = W(h, e + "patch_embed.proj.bias");
-  h->pos = W(h, e + "pos_embed");
-  h->blk.assign(h->depth, EncBlock());
-  for (int i = 0; i < h->depth; ++i) {
-    EncBlock& b = h->blk[i];
-    const std::string p = e + "blocks." + std::to_string(i) + ".";
-    for (int gi : h->global_idx) b.global |= (gi == i);
-    b.ln1g = W(h, p + "norm1.weight"); b.ln1b = W(h, p + "norm1.bias");
-    b.ln2g = W(h, p + "norm2.weight"); b.ln2b = W(h, p + "norm2.bias");
-    b.qkv_b = W(h, p + "attn.qkv.bias"); b.proj_b = W(h, p + "attn.proj.bias");
-    b.lin1_b = W(h, p + "mlp.lin1.bias"); b.lin2_b = W(h, p + "mlp.lin2.bias");
-    if (int r = make_bf16(h, W(h, p + "attn.qkv.weight"), 3 * D * D, &b.qkv_w)) return r;
-    if (int r = make_bf16(h, W(h, p + "attn.proj.weight"), D * D, &b.proj_w)) return r;
-    if (int r = make_bf16(h, W(h, p + "mlp.lin1.weight"), 4 * D * D, &b.lin1_w)) return r;
-    if (int r = make_bf16(h, W(h, p + "mlp.lin2.weight"), 4 * D * D, &b.lin2_w)) return r;
-    const int S = b.global ? kGrid : kWin;
-    const int RP = b.global ? 128 : 32;
-    CU(dalloc(h, &b.relh, (size_t)2 * RP * h->hd));   // [relh ; relw] contiguous: one tensor map covers both
-    b.relw = b.relh + (size_t)RP * h->hd;
-    KL(launch_relpos_pack(W(h, p + "attn.rel_pos_h"), S, h->hd, b.relh, 0));
-    KL(launch_relpos_pack(W(h, p + "attn.rel_pos_w"), S, h->hd, b.relw, 0));
-    if (b.global) {
-      CU(dalloc(h, &b.relg, (size_t)256 * 128));
-      KL(launch_relpos_pack_g(W(h, p + "attn.rel_pos_h"), W(h, p + "attn.rel_pos_w"), h->hd, b.relg, 0));
-    }
+  // Buffers derived by a previous finalize are freed and rebuilt per group (encoder / prompt encoder + decoders),
+  // and only for a group one of whose tensors was re-loaded: sizes never change, the footprint stays flat.
+  CU(cudaDeviceSynchronize());
+  if (h->dirty_enc) {
+    if (int r = finalize_encoder(h)) return r;
+    h->dirty_enc = false;
   }
-  if (int r = make_bf16(h, W(h, e + "neck.0.weight"), 256 * D, &h->neck0_w)) return r;
-  {
-    // neck.2 Conv2d 3x3 weight (out, in, dy, dx) -> (out, dy, dx, in): the K order of launch_im2col_3x3
-    std::vector<float> w((size_t)256 * 256 * 9), wp(w.size());
-    CU(cudaMemcpy(w.data(), W(h, e + "neck.2.weight"), w.size() * 4, cudaMemcpyDeviceToHost));
-    for (int o = 0; o < 256; ++o)
-      for (int c = 0; c < 256; ++c)
-        for (int t = 0; t < 9; ++t) wp[((size_t)o * 9 + t) * 256 + c] = w[((size_t)o * 256 + c) * 9 + t];
-    float* tmp = nullptr;
-    CU(dalloc(h, &tmp, wp.size()));
-    CU(cudaMemcpy(tmp, wp.data(), wp.size() * 4, cudaMemcpyHostToDevice));
-    if (int r = make_bf16(h, tmp, (long)wp.size(), &h->neck2_w)) return r;
+  if (h->dirty_dec) {
+    if (int r = finalize_decoders(h)) return r;
+    h->dirty_dec = false;
   }
-  h->neck1g = W(h, e + "neck.1.weight"); h->neck1b = W(h, e + "neck.1.bias");
-  h->neck3g = W(h, e + "neck.3.weight"); h->neck3b = W(h, e + "neck.3.bias");
-  // prompt encoder constants (prompt_encoder.py:67-76,182-184): dense PE once, in fp32 (SURVEY.md Appendix A8)
-  CU(dalloc(h, &h->pe_tok, (size_t)kTokens * 256));
-  KL(launch_dense_pe(W(h, "prompt_encoder.pe_layer.positional_encoding_gaussian_matrix"), h->pe_tok, 0));
-  h->no_mask = W(h, "prompt_encoder.no_mask_embed.weight");
-  for (int s = 0; s < 2; ++s)
-    if (int r = finalize_side(h, s)) return r;
   CU(cudaDeviceSynchronize());
   h->prof_on = prof_was;
   h->finalized = true;

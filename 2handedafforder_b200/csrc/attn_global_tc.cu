@@ -417,15 +417,12 @@ template <int HD>
 cudaError_t launch_global(const __nv_bfloat16* qkv, int nbatch, int heads, const __half* G, __nv_bfloat16* out,
                           cudaStream_t s) {
   using C = GlbCfg<HD>;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(attn_global_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
-    if (e != cudaSuccess) return e;
-    attr = true;
-  }
+  static std::atomic<uint64_t> attr{0};
+  cudaError_t e = smem_opt_in(attn_global_tc_kernel<HD>, C::kSmem, attr);
+  if (e != cudaSuccess) return e;
   const long rows = (long)nbatch * kGT, cols = 3L * heads * HD;
   CUtensorMap tm128, tm32;
-  cudaError_t e = make_tmap_2d(&tm128, qkv, 2, rows, cols, cols, 64, 128, 128);
+  e = make_tmap_2d(&tm128, qkv, 2, rows, cols, cols, 64, 128, 128);
   if (e != cudaSuccess) return e;
   if (C::kRem) {
     e = make_tmap_2d(&tm32, qkv, 2, rows, cols, cols, 16, 128, 32);

@@ -360,16 +360,13 @@ template <int HD>
 cudaError_t launch_window(const __nv_bfloat16* qkv, int nwin, int heads, const __nv_bfloat16* rel, __nv_bfloat16* out,
                           bool token_out, cudaStream_t s) {
   using C = WinCfg<HD>;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(attn_window_tc_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
-    if (e != cudaSuccess) return e;
-    attr = true;
-  }
+  static std::atomic<uint64_t> attr{0};
+  cudaError_t e = smem_opt_in(attn_window_tc_kernel<HD>, C::kSmem, attr);
+  if (e != cudaSuccess) return e;
   const long rows = (long)nwin * kT;
   const long cols = 3L * heads * HD;
   CUtensorMap tm128, tm32, tmR128, tmR32;
-  cudaError_t e = make_tmap_2d(&tm128, qkv, 2, rows, cols, cols, 64, kRowsPad, 128);
+  e = make_tmap_2d(&tm128, qkv, 2, rows, cols, cols, 64, kRowsPad, 128);
   if (e != cudaSuccess) return e;
   e = make_tmap_2d(&tmR128, rel, 2, 64, HD, HD, 64, 64, 128);
   if (e != cudaSuccess) return e;

@@ -8,7 +8,24 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 namespace bsam {
+
+// Opt a kernel in to more than 48 KB of dynamic shared memory ONCE PER DEVICE: the attribute belongs to the
+// (function, device context) pair, so a process-wide flag would leave the second GPU of a process without it.
+// `done` is a per-kernel bitmask indexed by the current device ordinal.
+template <class Kernel>
+inline cudaError_t smem_opt_in(Kernel kernel, int bytes, std::atomic<uint64_t>& done) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const uint64_t bit = 1ull << (dev & 63);
+  if (done.load(std::memory_order_acquire) & bit) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) done.fetch_or(bit, std::memory_order_release);
+  return e;
+}
 
 // Fixed geometry of the path: 1024^2 frames, 16x16 patches, 14x14 windows
 // (reference: 2Haff/model/segment_anything/build_sam.py:67-84).

@@ -23,6 +23,9 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <atomic>
+#include <mutex>
+
 #include "common.cuh"
 
 namespace bsam {
@@ -724,9 +727,13 @@ __global__ void gemm_simt_debug_kernel(const void* A, int lda, const void* W, in
   epilogue_row<MODE, BN>(e, src, row, M, N, n0, 0, 0, 1, NoWait());
 }
 
-PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
-int g_num_sms = 148;
-bool g_pair_kernel = true;   // B200SAM_GEMM_PAIR=0 selects the single-CTA kernel (A/B measurements)
+// Process-wide state is limited to what really is process-wide: the driver entry point and a build-time A/B switch.
+// SM counts are kept per device ordinal (a second handle on another GPU must not inherit the first one's count).
+std::atomic<PFN_cuTensorMapEncodeTiled_v12000> g_encode{nullptr};
+constexpr int kMaxDevices = 64;
+std::atomic<int> g_num_sms[kMaxDevices];
+bool g_pair_kernel = true;   // B200SAM_GEMM_PAIR=0 selects the single-CTA kernel (A/B measurements); read once
+std::once_flag g_env_once;
 
 cudaError_t make_tmap(CUtensorMap* tm, const void* ptr, bool f32, long rows, long cols, long ld, int box_rows) {
   const int esz = f32 ? 4 : 2;
@@ -735,7 +742,7 @@ cudaError_t make_tmap(CUtensorMap* tm, const void* ptr, bool f32, long rows, lon
   cuuint32_t box[2] = {(cuuint32_t)(128 / esz), (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (strides[0] & 15)) return cudaErrorInvalidValue;
-  CUresult r = g_encode(tm, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+  CUresult r = g_encode.load()(tm, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
                         const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -751,20 +758,17 @@ cudaError_t launch(const void* A, int lda, const void* W, int ldw, int M, int N,
     gemm_simt_debug_kernel<kTf32, MODE, BN><<<grid, kBM, 0, stream>>>(A, lda, W, ldw, M, N, K, e);
     return cudaGetLastError();
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t err = cudaFuncSetAttribute(gemm_tc_kernel<kTf32, MODE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           TileCfg<BN>::kSmemBytes);
-    if (err != cudaSuccess) return err;
-    attr_set = true;
-  }
+  static std::atomic<uint64_t> attr_set{0};
+  cudaError_t err = smem_opt_in(gemm_tc_kernel<kTf32, MODE, BN>, TileCfg<BN>::kSmemBytes, attr_set);
+  if (err != cudaSuccess) return err;
   CUtensorMap tmA, tmB;
-  cudaError_t err = make_tmap(&tmA, A, kTf32, M, e.batch > 1 ? lda : K, lda, kBM);
+  err = make_tmap(&tmA, A, kTf32, M, e.batch > 1 ? lda : K, lda, kBM);
   if (err != cudaSuccess) return err;
   err = make_tmap(&tmB, W, kTf32, N, K, ldw, BN);
   if (err != cudaSuccess) return err;
   const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * e.batch;
-  const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+  const int n_sm = gemm_num_sms();
+  const int grid = tiles < n_sm ? tiles : n_sm;
   gemm_tc_kernel<kTf32, MODE, BN><<<grid, kThreads, TileCfg<BN>::kSmemBytes, stream>>>(tmA, tmB, M, N, K, e);
   return cudaGetLastError();
 }
@@ -772,19 +776,16 @@ cudaError_t launch(const void* A, int lda, const void* W, int ldw, int M, int N,
 template <int MODE>
 cudaError_t launch2(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const GemmEpi& e,
                     cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t err = cudaFuncSetAttribute(gemm_tc2_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes2);
-    if (err != cudaSuccess) return err;
-    attr_set = true;
-  }
+  static std::atomic<uint64_t> attr_set{0};
+  cudaError_t err = smem_opt_in(gemm_tc2_kernel<MODE>, kSmemBytes2, attr_set);
+  if (err != cudaSuccess) return err;
   CUtensorMap tmA, tmB;
-  cudaError_t err = make_tmap(&tmA, A, false, M, K, lda, 128);
+  err = make_tmap(&tmA, A, false, M, K, lda, 128);
   if (err != cudaSuccess) return err;
   err = make_tmap(&tmB, W, false, N, K, ldw, 128);
   if (err != cudaSuccess) return err;
   const int tiles = ((M + 255) / 256) * ((N + 255) / 256);
-  int pairs = g_num_sms / 2;
+  int pairs = gemm_num_sms() / 2;
   if (tiles < pairs) pairs = tiles;
   gemm_tc2_kernel<MODE><<<2 * pairs, kThreads, kSmemBytes2, stream>>>(tmA, tmB, M, N, K, e);
   return cudaGetLastError();
@@ -793,24 +794,31 @@ cudaError_t launch2(const void* A, int lda, const void* W, int ldw, int M, int N
 }  // namespace
 
 cudaError_t gemm_tc_init(int device) {
-  if (g_encode) return cudaSuccess;
-  void* fn = nullptr;
-  cudaDriverEntryPointQueryResult qres;
-  cudaError_t err = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
-  if (err != cudaSuccess) return err;
-  if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
-  g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
-  int sms = 0;
-  err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-  if (err != cudaSuccess) return err;
-  g_num_sms = sms;
-  if (const char* v = getenv("B200SAM_GEMM_PAIR")) g_pair_kernel = atoi(v) != 0;
+  if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+  cudaError_t err;
+  if (!g_encode.load(std::memory_order_acquire)) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    err = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (err != cudaSuccess) return err;
+    if (qres != cudaDriverEntryPointSuccess || !fn) return cudaErrorNotSupported;
+    g_encode.store(reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn), std::memory_order_release);
+  }
+  if (g_num_sms[device].load(std::memory_order_acquire) == 0) {
+    int sms = 0;
+    err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if (err != cudaSuccess) return err;
+    g_num_sms[device].store(sms, std::memory_order_release);
+  }
+  std::call_once(g_env_once, [] {
+    if (const char* v = getenv("B200SAM_GEMM_PAIR")) g_pair_kernel = atoi(v) != 0;
+  });
   return cudaSuccess;
 }
 
 cudaError_t make_tmap_2d(void* out, const void* ptr, int esz, long rows, long cols, long ld, int box_cols, int box_rows,
                          int swizzle_bytes) {
-  if (!g_encode) return cudaErrorInitializationError;
+  if (!g_encode.load()) return cudaErrorInitializationError;
   if (box_cols * esz != swizzle_bytes || box_rows > 256) return cudaErrorInvalidValue;
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)ld * esz};
@@ -819,18 +827,24 @@ cudaError_t make_tmap_2d(void* out, const void* ptr, int esz, long rows, long co
   if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (strides[0] & 15)) return cudaErrorInvalidValue;
   const CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
                                 : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
-  CUresult r = g_encode(reinterpret_cast<CUtensorMap*>(out),
+  CUresult r = g_encode.load()(reinterpret_cast<CUtensorMap*>(out),
                         esz == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
                         const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
-int gemm_num_sms() { return g_num_sms; }
+// SM count of the CURRENT device (every launcher runs under the handle's DeviceGuard)
+int gemm_num_sms() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return 148;
+  const int n = g_num_sms[dev].load(std::memory_order_acquire);
+  return n > 0 ? n : 148;
+}
 
 cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, int ldw, int M, int N, int K,
                     const GemmEpi& e, cudaStream_t s, bool dbg) {
-  if (!g_encode && !dbg) return cudaErrorInitializationError;
+  if (!g_encode.load() && !dbg) return cudaErrorInitializationError;
   if (N % 32 != 0 || K % 8 != 0) return cudaErrorInvalidValue;
   if (e.batch != 1 && (mode != GM_F16 || tf32 || dbg || e.batch < 1)) return cudaErrorInvalidValue;
   if ((mode == GM_LN || mode == GM_UPS1) && N != 256) return cudaErrorInvalidValue;

@@ -101,7 +101,13 @@ struct b200sam {
   int emb_batch = 0;
 
   std::map<std::string, bsam::Tensor> w;
-  std::vector<void*> owned;          // derived device buffers (freed in destroy)
+  std::vector<void*> owned;          // workspace + grow-on-demand buffers (freed in destroy)
+  // buffers derived from the weights by finalize_weights (bf16 packs, rel-pos / positional tables, permuted conv
+  // weights).  They are freed and rebuilt when a tensor of their group was re-loaded, so repeated
+  // load_weight + finalize cycles (validation between training epochs) keep the footprint flat.
+  std::vector<void*> derived_enc, derived_dec;
+  std::vector<void*>* alloc_into = &owned;
+  bool dirty_enc = true, dirty_dec = true;
 
   // encoder
   __nv_bfloat16* patch_w = nullptr;

@@ -217,12 +217,22 @@ class B200Sam(CallersMixin, nn.Module):
         return self._ensure(device, sync=False)
 
     def _sync_weights(self) -> None:
+        """Upload the tensors whose (storage, version, dtype) changed since the last call and re-finalise.  Only the
+        changed tensors travel, and the library rebuilds the derived buffers of the touched group (encoder /
+        decoders) in place of the old ones, so validate() between training epochs of the mask decoders
+        (train_ds.py:236-244,625-758) costs a few MB of copies and no extra memory."""
         tensors = self._tensors()
         sig = tuple((t.data_ptr(), t._version, t.dtype) for _, t in tensors)
         if sig == self._sig:
             return
+        old = self._sig if (self._sig is not None and len(self._sig) == len(sig)) else (None,) * len(sig)
         lib, h = _lib.load(), self._handle
-        for name, t in tensors:
+        # load_weight / finalize run on the legacy stream: everything queued on the caller's stream (producers of
+        # the parameter values, kernels still reading the previous weights) must be complete first
+        torch.cuda.current_stream(tensors[0][1].device).synchronize()
+        for (name, t), s_new, s_old in zip(tensors, sig, old):
+            if s_new == s_old:
+                continue
             src = t.detach()
             if src.dtype not in _DTYPES:
                 src = src.float()
@@ -312,8 +322,23 @@ class B200Sam(CallersMixin, nn.Module):
         _lib.check(rc, h, "decode")
         return out
 
+    def _no_autograd(self, what: str, *tensors: Optional[torch.Tensor], params=()) -> None:
+        """The library has no backward pass (SURVEY 8f row 4 is out of scope): outputs carry no grad_fn.  LISA's
+        training forward (LISA.py:284-325 with train_mask_decoder=True, :84-90) would silently get constant mask
+        losses, so refuse instead of returning detached tensors into a graph that expects gradients."""
+        if not torch.is_grad_enabled():
+            return
+        needs = [t for t in tensors if t is not None and t.requires_grad]
+        if needs or any(p.requires_grad for p in params):
+            raise NotImplementedError(
+                f"{what}: called with autograd enabled on inputs/parameters that require grad, but libb200sam is "
+                "inference-only (no backward).  Wrap evaluation in torch.no_grad() (as LISA.evaluate / "
+                "train_ds.validate do), or run the training forward through the reference PyTorch decoders.")
+
     def _decode_one_side(self, side: str, image_embeddings: torch.Tensor, sparse: torch.Tensor,
                          dense: Optional[torch.Tensor]):
+        dec = self.mask_decoder_left if side == "left" else self.mask_decoder_right
+        self._no_autograd(f"mask_decoder_{side}", image_embeddings, sparse, params=dec.parameters())
         if image_embeddings.dim() != 4 or tuple(image_embeddings.shape) != (1, OUT_CH, GRID, GRID):
             raise ValueError(f"image_embeddings must be (1,{OUT_CH},{GRID},{GRID}) per call (LISA.py:306,505), got "
                              f"{tuple(image_embeddings.shape)}")
@@ -352,6 +377,7 @@ class B200Sam(CallersMixin, nn.Module):
         """Sam.postprocess_masks (sam.py:155-189): returns fp32 (N,C,H,W)."""
         if masks.dim() != 4 or tuple(masks.shape[-2:]) != (256, 256):
             raise ValueError(f"masks must be (N,C,256,256), got {tuple(masks.shape)}")
+        self._no_autograd("postprocess_masks", masks)
         n, c = masks.shape[:2]
         low = masks.to(torch.float32).contiguous().reshape(n * c, 256, 256)
         logits, _ = self._postprocess_raw(low, input_size, original_size, True, False, 0.0)

@@ -41,6 +41,15 @@ CASES = {
 }
 
 
+# "lite" cases: frames [first, first + n) of a config, outputs only (low-res logits as fp16, packed full-res mask
+# bits, both heads, strided full-res samples) - no per-block taps, so eight ViT-H frames stay a few MB each
+LITE_CASES = {
+    #  name             arch    first n_frames n_prompts resize        original
+    "vit_h_cfg2_rest": ("vit_h", 2, 6, 3, (576, 1024), (1080, 1920)),   # frames 2..7 of configs[1]
+    "vit_l_lite": ("vit_l", 0, 1, 3, (576, 1024), (1080, 1920)),        # build_sam_vit_l, never a headline config
+}
+
+
 def build_reference(arch: synth.Arch):
     import segment_anything as sa
     from segment_anything.build_sam import _build_sam
@@ -54,15 +63,20 @@ def build_reference(arch: synth.Arch):
 
 
 def run_case(name: str):
-    arch_name, n_frames, n_prompts, resize, original = CASES[name]
+    lite = name in LITE_CASES
+    if lite:
+        arch_name, first, n_frames, n_prompts, resize, original = LITE_CASES[name]
+    else:
+        arch_name, n_frames, n_prompts, resize, original = CASES[name]
+        first = 0
     arch = synth.ARCHS[arch_name]
     torch.set_num_threads(os.cpu_count())
     sam = build_reference(arch)
-    frames = synth.make_frames(0, n_frames, valid_rows=resize[0])
+    frames = synth.make_frames(first, n_frames, valid_rows=resize[0])
     out = {}
     taps = []
-    hooks = [blk.register_forward_hook(lambda m, i, o: taps.append(o.detach().clone()))
-             for blk in sam.image_encoder.blocks]
+    hooks = [] if lite else [blk.register_forward_hook(lambda m, i, o: taps.append(o.detach().clone()))
+                             for blk in sam.image_encoder.blocks]
     t0 = time.time()
     with torch.no_grad():
         # LISA.get_visual_embs runs B=1 per call (LISA.py:157-168)
@@ -70,7 +84,7 @@ def run_case(name: str):
         for h in hooks:
             h.remove()
         pos = torch.tensor(TAP_POS)
-        for bi in range(arch.depth):
+        for bi in range(0 if lite else arch.depth):
             rows = torch.cat([taps[f * arch.depth + bi] for f in range(n_frames)], 0)
             out[f"tap_block{bi}"] = rows[:, pos][:, :, pos].numpy()          # (B,6,6,D)
         out["emb_slice"] = emb[:, ::16].numpy()                              # 16 of 256 channels
@@ -78,7 +92,7 @@ def run_case(name: str):
         out["emb_mean"] = emb.mean(dim=(1, 2, 3)).double().numpy()
         out["dense_pe_slice"] = sam.prompt_encoder.get_dense_pe()[0, ::32].numpy()
         for i in range(n_frames):
-            seg = synth.make_seg_embeds(i, n_prompts)
+            seg = synth.make_seg_embeds(first + i, n_prompts)
             sparse, dense = sam.prompt_encoder(points=None, boxes=None, masks=None,
                                                text_embeds=seg.unsqueeze(1))
             ml, il, tax = sam.mask_decoder_left(
@@ -96,8 +110,8 @@ def run_case(name: str):
                 full[side] = res[1]
             pl = sam.postprocess_masks(ml, input_size=resize, original_size=original)[:, 0]
             pr = sam.postprocess_masks(mr, input_size=resize, original_size=original)[:, 0]
-            out[f"f{i}_lowres_left"] = ml[:, 0].numpy().astype(np.float16 if arch_name == "vit_h" else np.float32)
-            out[f"f{i}_lowres_right"] = mr[:, 0].numpy().astype(np.float16 if arch_name == "vit_h" else np.float32)
+            out[f"f{i}_lowres_left"] = ml[:, 0].numpy().astype(np.float16 if arch_name in ("vit_h", "vit_l") else np.float32)
+            out[f"f{i}_lowres_right"] = mr[:, 0].numpy().astype(np.float16 if arch_name in ("vit_h", "vit_l") else np.float32)
             out[f"f{i}_lowres_left_absmax"] = ml[:, 0].abs().amax(dim=(1, 2)).numpy()
             out[f"f{i}_lowres_right_absmax"] = mr[:, 0].abs().amax(dim=(1, 2)).numpy()
             out[f"f{i}_iou_left"] = full["left"].numpy()
@@ -110,12 +124,12 @@ def run_case(name: str):
             out[f"f{i}_full_right_samples"] = pr[:, ::37, ::41].numpy()
             out[f"f{i}_full_left_absmax"] = pl.abs().amax(dim=(1, 2)).numpy()
             out[f"f{i}_full_right_absmax"] = pr.abs().amax(dim=(1, 2)).numpy()
-    out["meta"] = np.array([n_frames, n_prompts, resize[0], resize[1], original[0], original[1]])
+    out["meta"] = np.array([n_frames, n_prompts, resize[0], resize[1], original[0], original[1], first])
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), name + ".npz")
     np.savez_compressed(path, **out)
     print(f"{name}: {time.time() - t0:.1f}s -> {path} ({os.path.getsize(path) / 1e6:.2f} MB)")
 
 
 if __name__ == "__main__":
-    for c in (sys.argv[1:] or list(CASES)):
+    for c in (sys.argv[1:] or list(CASES) + list(LITE_CASES)):
         run_case(c)
