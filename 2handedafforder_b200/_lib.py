@@ -28,6 +28,9 @@ SYMBOLS = [
     ("b200sam_encode", _I, [_P, _P, _I, _I, _P, _I, _P]),
     ("b200sam_decode", _I, [_P, _P, _I, _I, _P, C.POINTER(_I), _P, _P, _P, _P, _P, _P]),
     ("b200sam_postprocess", _I, [_P, _P, _I, _I, _I, _I, _I, _P, _P, _F, _P]),
+    ("b200sam_postprocess_bits", _I, [_P, _P, _I, _I, _I, _I, _I, _P, _F, _P]),
+    ("b200sam_postprocess_pair", _I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _F, _P, _P, _P, _P, _P, _P]),
+    ("b200sam_checksum64", _I, [_P, _P, _I, _L, _L, _P, _P]),
     ("b200sam_dense_pe", _I, [_P, _P, _P]),
     ("b200sam_preprocess", _I, [_P, _P, _I, _I, _I, _P, _I, C.POINTER(_I), _P]),
     ("b200sam_seg_project", _I, [_P, _P, _I, _I, _I, _I, _P, _I, _L, _P, _P, _P, _P, _I, _P, _I, _P, _P]),

@@ -437,6 +437,15 @@ int alloc_workspace(b200sam_t* h) {
     CU(dalloc(h, &g, B * kTokens * (size_t)h->heads * 256));
     h->gbuf = g;
   }
+  {
+    void* flag = nullptr;
+    CU(cudaHostAlloc(&flag, sizeof(int), cudaHostAllocMapped));
+    h->ovf_host = reinterpret_cast<volatile int*>(flag);
+    *h->ovf_host = 0;
+    void* dflag = nullptr;
+    CU(cudaHostGetDevicePointer(&dflag, flag, 0));
+    h->ovf_dev = reinterpret_cast<int*>(dflag);
+  }
   const size_t hid_cols = 4 * D > 9 * 256 ? 4 * D : 9 * 256;
   CU(dalloc(h, &h->hid, B * kTokens * hid_cols));
   CU(dalloc(h, &h->emb_tok, B * kTokens * 256));
@@ -506,6 +515,12 @@ int create_common(b200sam_t** out, int dim, int depth, int heads, const int* gid
 int check_ready(b200sam_t* h) {
   if (!h) return B200SAM_ERR_INVALID;
   if (!h->finalized) return fail(h, B200SAM_ERR_STATE, "weights not finalised: call b200sam_finalize_weights first");
+  if (h->ovf_host && *h->ovf_host) {
+    *h->ovf_host = 0;
+    return fail(h, B200SAM_ERR_STATE,
+                "an earlier b200sam_encode saturated the fp16 rel-pos projections q.Rh / q.Rw (|value| > 65504) in a "
+                "global-attention block: its embeddings are invalid (checkpoint outside the supported range)");
+  }
   return 0;
 }
 
@@ -548,6 +563,7 @@ extern "C" void b200sam_destroy(b200sam_t* h) {
     free_list(h->owned);
     free_list(h->derived_enc);
     free_list(h->derived_dec);
+    if (h->ovf_host) cudaFreeHost(const_cast<int*>(h->ovf_host));
     if (h->side_stream) cudaStreamDestroy(h->side_stream);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
@@ -738,7 +754,7 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
     }
     h->pc = b.global ? B200SAM_PC_ATTN_GLOBAL : B200SAM_PC_ATTN_WINDOW;
     KL(launch_attention(h->qkv, b.global ? B : B * kWinPerSide * kWinPerSide, b.global ? kGrid : kWin, heads, hd, b.relh,
-                        b.relw, b.relg, h->gbuf, h->attn_o, s, /*window_token_out=*/true));
+                        b.relw, b.relg, h->gbuf, h->attn_o, s, /*window_token_out=*/true, h->ovf_dev));
     if (b.global) ++h->launches;   // the batched bias-projection GEMM in front of the global kernel
     {
       // proj + residual: x = shortcut + attn(x)                                    (image_encoder.py:187-190)
@@ -999,8 +1015,61 @@ extern "C" int b200sam_postprocess(b200sam_t* h, const float* lowres, int n_mask
   DeviceGuard g(h->device);
   h->prof_stream = reinterpret_cast<cudaStream_t>(stream);
   h->pc = B200SAM_PC_POSTPROCESS;
-  KL(launch_postprocess(lowres, n_masks, in_h, in_w, out_h, out_w, logits_out, mask_out, threshold,
+  KL(launch_postprocess(lowres, n_masks, in_h, in_w, out_h, out_w, logits_out, mask_out, nullptr, threshold,
                         reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int b200sam_postprocess_bits(b200sam_t* h, const float* lowres, int n_masks, int in_h, int in_w, int out_h,
+                                        int out_w, uint8_t* bits_out, float threshold, void* stream) {
+  if (!h) return B200SAM_ERR_INVALID;
+  if (n_masks < 0 || in_h < 1 || in_w < 1 || in_h > kImg || in_w > kImg || out_h < 1 || out_w < 1)
+    return fail(h, B200SAM_ERR_INVALID, "bad postprocess sizes n=%d in=(%d,%d) out=(%d,%d)", n_masks, in_h, in_w, out_h,
+                out_w);
+  if (n_masks == 0) return 0;
+  if (!lowres || !bits_out) return fail(h, B200SAM_ERR_INVALID, "lowres / bits_out is NULL");
+  DeviceGuard g(h->device);
+  h->prof_stream = reinterpret_cast<cudaStream_t>(stream);
+  h->pc = B200SAM_PC_POSTPROCESS;
+  KL(launch_postprocess(lowres, n_masks, in_h, in_w, out_h, out_w, nullptr, nullptr, bits_out, threshold,
+                        reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int b200sam_postprocess_pair(b200sam_t* h, const float* lowres_left, const float* lowres_right, int P,
+                                        int in_h, int in_w, int out_h, int out_w, uint8_t* bits_left,
+                                        uint8_t* bits_right, float threshold, const float* taxonomy,
+                                        const uint8_t* gt, const int* gt_index, int64_t* counts_out,
+                                        uint8_t* pred_bits_out, void* stream) {
+  if (!h) return B200SAM_ERR_INVALID;
+  if (P < 0 || in_h < 1 || in_w < 1 || in_h > kImg || in_w > kImg || out_h < 1 || out_w < 1)
+    return fail(h, B200SAM_ERR_INVALID, "bad postprocess sizes P=%d in=(%d,%d) out=(%d,%d)", P, in_h, in_w, out_h, out_w);
+  if (P == 0) return 0;
+  if (!lowres_left || !lowres_right) return fail(h, B200SAM_ERR_INVALID, "lowres is NULL");
+  if (gt && (!taxonomy || !counts_out))
+    return fail(h, B200SAM_ERR_INVALID, "evaluation against gt needs taxonomy and counts_out");
+  if (!gt && !bits_left && !bits_right) return fail(h, B200SAM_ERR_INVALID, "nothing to compute: no output given");
+  DeviceGuard g(h->device);
+  h->prof_stream = reinterpret_cast<cudaStream_t>(stream);
+  h->pc = B200SAM_PC_POSTPROCESS;
+  KL(launch_postprocess_pair(lowres_left, lowres_right, P, in_h, in_w, out_h, out_w, bits_left, bits_right, threshold,
+                             taxonomy, gt, gt_index, counts_out, pred_bits_out, reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int b200sam_checksum64(b200sam_t* h, const void* data, int n_items, int64_t bytes, int64_t stride,
+                                  uint64_t* out, void* stream) {
+  if (!h) return B200SAM_ERR_INVALID;
+  if (n_items < 0 || n_items > 65535 || bytes < 0 || stride < bytes)
+    return fail(h, B200SAM_ERR_INVALID, "bad checksum sizes n=%d bytes=%lld stride=%lld", n_items, (long long)bytes,
+                (long long)stride);
+  if (n_items == 0) return 0;
+  if (!data || !out) return fail(h, B200SAM_ERR_INVALID, "NULL argument");
+  DeviceGuard g(h->device);
+  h->prof_stream = reinterpret_cast<cudaStream_t>(stream);
+  h->pc = B200SAM_PC_METRICS;
+  KL(launch_checksum64(reinterpret_cast<const uint8_t*>(data), n_items, bytes, stride, out,
+                       reinterpret_cast<cudaStream_t>(stream)));
   return 0;
 }
 

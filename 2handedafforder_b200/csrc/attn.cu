@@ -13,7 +13,8 @@ cudaError_t attention_init() { return cudaSuccess; }
 
 cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int heads, int hd,
                              const __nv_bfloat16* relh, const __nv_bfloat16* relw, const __nv_bfloat16* relg,
-                             void* gbuf, __nv_bfloat16* out, cudaStream_t s, bool window_token_out) {
+                             void* gbuf, __nv_bfloat16* out, cudaStream_t s, bool window_token_out,
+                             int* f16_overflow) {
   if (nbatch <= 0) return cudaSuccess;
   if (hd != 64 && hd != 80) return cudaErrorInvalidValue;
   if (S == kWin) {
@@ -35,6 +36,7 @@ cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int he
     // kernel adds them to q.k on the tensor core (S += Gw E) before scaling by hd^-1/2
     e.rowmap = RM_RELW_SHIFT;
     e.relw_scale = sqrtf((float)hd);
+    e.f16_overflow = f16_overflow;   // fp16 range check of the projections (see GemmEpi)
     cudaError_t err = gemm_tc(false, GM_F16, qkv, 3 * heads * hd, relg, 128, nbatch * kTokens, 256, 128, e, s);
     if (err != cudaSuccess) return err;
     return launch_attention_global_tc(qkv, nbatch, heads, hd, reinterpret_cast<const __half*>(gbuf), out, s);

@@ -131,6 +131,14 @@ __device__ __forceinline__ void store_bf16x32(__nv_bfloat16* o, const float (&v)
   }
 }
 
+// fp16 stores of the rel-pos projections saturate instead of producing inf (an inf bias would turn a whole softmax row
+// into NaN); the caller is told through a host-mapped flag, so an out-of-range checkpoint fails loudly, not silently.
+constexpr float kF16Max = 65504.f;
+__device__ __forceinline__ float sat_f16(float x, bool& hit) {
+  hit |= fabsf(x) > kF16Max;
+  return fminf(fmaxf(x, -kF16Max), kF16Max);
+}
+
 // One output row (row of the 128-row tile owned by this thread), columns [n0, n0 + BN).
 // `src.load` is warp-collective for the TMEM source: every lane must call it the same number of times.
 struct NoWait {
@@ -170,6 +178,10 @@ __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, l
     for (int c = c_lo; c < c_hi; ++c) {
       src.load(c, v);
       if (row_in) {
+        bool hit = false;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = sat_f16(v[j], hit);
+        if (hit && e.f16_overflow) *e.f16_overflow = 1;
         uint4* o4 = reinterpret_cast<uint4*>(o + c * 32);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -420,6 +432,11 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
         if (has_add) add4(x, cur[i]);
         if (st) *reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + orow[i] * (long)e.ld_out + col) = x;
       } else if constexpr (MODE == GM_F16) {
+        const float ws = (e.rowmap == RM_RELW_SHIFT && col >= 128) ? e.relw_scale : 1.f;
+        bool hit = false;
+        x.x = sat_f16(x.x * ws, hit), x.y = sat_f16(x.y * ws, hit);
+        x.z = sat_f16(x.z * ws, hit), x.w = sat_f16(x.w * ws, hit);
+        if (hit && st && e.f16_overflow) *e.f16_overflow = 1;
         __half2 h0 = __floats2half2_rn(x.x, x.y), h1 = __floats2half2_rn(x.z, x.w);
         uint2 t;
         t.x = *reinterpret_cast<uint32_t*>(&h0);
@@ -428,8 +445,8 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
         if (e.rowmap == RM_RELW_SHIFT && col >= 128) {
           // per-row shift: source column 128 + j goes to 128 + (j - 63 + qx) when that lands in [0, 64)
           const int kx0 = (int)col - 191 + (orow[i] & 63);
-          const __half hv[4] = {__float2half_rn(x.x * e.relw_scale), __float2half_rn(x.y * e.relw_scale),
-                                __float2half_rn(x.z * e.relw_scale), __float2half_rn(x.w * e.relw_scale)};
+          const __half hv[4] = {__float2half_rn(x.x), __float2half_rn(x.y), __float2half_rn(x.z),
+                                __float2half_rn(x.w)};   // already scaled by relw_scale and saturated above
 #pragma unroll
           for (int q = 0; q < 4; ++q)
             if (st && (unsigned)(kx0 + q) < 64u) orp[128 + kx0 + q] = hv[q];

@@ -35,6 +35,7 @@ struct GemmEpi {
   int ld_out = 0;
   int rowmap = RM_IDENT;
   float relw_scale = 1.f;      // RM_RELW_SHIFT: factor applied (in fp32) to the shifted w columns before the fp16 store
+  int* f16_overflow = nullptr; // GM_F16: set to 1 (host-mapped flag) when a value had to be saturated to +-65504
   const float* ln_g = nullptr;
   const float* ln_b = nullptr;
   float ln_eps = 0.f;

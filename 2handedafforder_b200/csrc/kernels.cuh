@@ -34,7 +34,8 @@ cudaError_t launch_relpos_pack_g(const float* rel_h, const float* rel_w, int hd,
 // >= hd zero (launch_relpos_pack_g), and gbuf = (nbatch*4096, heads*256) fp16 scratch for the bias projections.
 cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int heads, int hd,
                              const __nv_bfloat16* relh, const __nv_bfloat16* relw, const __nv_bfloat16* relg,
-                             void* gbuf, __nv_bfloat16* out, cudaStream_t s, bool window_token_out = false);
+                             void* gbuf, __nv_bfloat16* out, cudaStream_t s, bool window_token_out = false,
+                             int* f16_overflow = nullptr);
 cudaError_t attention_init();
 // ---- attn_tc.cu (tcgen05): windowed attention; rel = (64, hd) bf16 [rel_pos_h padded to 32 rows; rel_pos_w padded]
 cudaError_t launch_attention_global_tc(const __nv_bfloat16* qkv, int nbatch, int heads, int hd, const __half* G,
@@ -48,7 +49,17 @@ struct DecSideWeights;   // device pointers of one mask decoder (api.cu owns it)
 struct DecoderWorkspace;
 
 // ---- postprocess.cu
+// one side: any of logits (n,H,W) f32 / mask (n,H,W) u8 / bits (n,H,ceil(W/8)) packed (numpy.packbits order) may be null
 cudaError_t launch_postprocess(const float* lowres, int n, int in_h, int in_w, int out_h, int out_w, float* logits,
-                               uint8_t* mask, float thr, cudaStream_t s);
+                               uint8_t* mask, uint8_t* bits, float thr, cudaStream_t s);
+// both sides of n prompts in one pass -> packed bits; with gt != null also the taxonomy-gated evaluation counts
+// (n,3) {intersection, union, area} (zeroed here) and the packed gated prediction
+cudaError_t launch_postprocess_pair(const float* low_left, const float* low_right, int n, int in_h, int in_w, int out_h,
+                                    int out_w, uint8_t* bits_left, uint8_t* bits_right, float thr,
+                                    const float* taxonomy, const uint8_t* gt, const int* gt_index, int64_t* counts,
+                                    uint8_t* pred_bits, cudaStream_t s);
+// out[i] = position-sensitive 64-bit checksum of data[i*stride, i*stride + bytes) (zeroed here)
+cudaError_t launch_checksum64(const uint8_t* data, int n_items, long bytes, long stride, uint64_t* out,
+                              cudaStream_t s);
 
 }  // namespace bsam

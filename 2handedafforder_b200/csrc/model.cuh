@@ -130,6 +130,10 @@ struct b200sam {
   int n_pad_rows = 0;
   __nv_bfloat16* attn_o = nullptr;   // (B*4900, D)
   void* gbuf = nullptr;              // (B*4096, heads*256) fp16 rel-pos projections of the global blocks
+  // host-mapped flag the G GEMM epilogue raises when a projection left the fp16 range and was saturated: checked at
+  // the next API call, which then fails (an out-of-range checkpoint must not produce quietly wrong masks)
+  volatile int* ovf_host = nullptr;
+  int* ovf_dev = nullptr;
   __nv_bfloat16* hid = nullptr;      // (B*4096, 4D) MLP hidden; also im2col scratch
   float* emb_tok = nullptr;          // (B*4096, 256) fp32 image embedding, token-major
   // decoder workspace

@@ -292,17 +292,24 @@ class B200Sam(CallersMixin, nn.Module):
                 "(mask prompts are not on the LISA path)")
 
     def _decode_raw(self, emb: Optional[torch.Tensor], n_frames: int, seg: torch.Tensor, offsets: Sequence[int],
-                    left: bool, right: bool, device: torch.device) -> Dict[str, torch.Tensor]:
+                    left: bool, right: bool, device: torch.device,
+                    heads_out: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+        """heads_out: optional (3, cap >= P, 4) f32 buffer; taxonomy / iou_left / iou_right are then written straight
+        into heads_out[0 / 1 / 2, :P] (e.g. the send slot of clip.segment_clip) instead of fresh tensors."""
         P = int(offsets[-1])
         f32 = dict(dtype=torch.float32, device=device)
         out: Dict[str, torch.Tensor] = {}
+        if heads_out is not None:
+            if (heads_out.dim() != 3 or heads_out.shape[0] != 3 or heads_out.shape[1] < P or heads_out.shape[2] != 4
+                    or heads_out.dtype != torch.float32 or not heads_out.is_contiguous() or heads_out.device != device):
+                raise ValueError("heads_out must be a contiguous (3, >=P, 4) float32 tensor on the frames' device")
         if left:
             out["lowres_left"] = torch.empty((P, 256, 256), **f32)
-            out["iou_left"] = torch.empty((P, 4), **f32)
-            out["taxonomy"] = torch.empty((P, 4), **f32)
+            out["iou_left"] = heads_out[1, :P] if heads_out is not None else torch.empty((P, 4), **f32)
+            out["taxonomy"] = heads_out[0, :P] if heads_out is not None else torch.empty((P, 4), **f32)
         if right:
             out["lowres_right"] = torch.empty((P, 256, 256), **f32)
-            out["iou_right"] = torch.empty((P, 4), **f32)
+            out["iou_right"] = heads_out[2, :P] if heads_out is not None else torch.empty((P, 4), **f32)
         if P == 0:
             return out
         h = self._ensure(device, batch=n_frames, prompts=P)
@@ -322,14 +329,16 @@ class B200Sam(CallersMixin, nn.Module):
         _lib.check(rc, h, "decode")
         return out
 
-    def _no_autograd(self, what: str, *tensors: Optional[torch.Tensor], params=()) -> None:
+    def _no_autograd(self, what: str, *tensors: Optional[torch.Tensor], module: Optional[nn.Module] = None) -> None:
         """The library has no backward pass (SURVEY 8f row 4 is out of scope): outputs carry no grad_fn.  LISA's
-        training forward (LISA.py:284-325 with train_mask_decoder=True, :84-90) would silently get constant mask
-        losses, so refuse instead of returning detached tensors into a graph that expects gradients."""
+        training forward (LISA.py:284-325 with train_mask_decoder=True; :84-90 puts both decoders in train() mode with
+        requires_grad parameters, and the [SEG] embeddings come out of the trainable text_hidden_fcs) would silently
+        get constant mask losses, so refuse instead of returning detached tensors into a graph that expects
+        gradients.  Plain inference - eval() mode, inputs without grad - is unaffected even outside no_grad()."""
         if not torch.is_grad_enabled():
             return
         needs = [t for t in tensors if t is not None and t.requires_grad]
-        if needs or any(p.requires_grad for p in params):
+        if needs or (module is not None and module.training and any(p.requires_grad for p in module.parameters())):
             raise NotImplementedError(
                 f"{what}: called with autograd enabled on inputs/parameters that require grad, but libb200sam is "
                 "inference-only (no backward).  Wrap evaluation in torch.no_grad() (as LISA.evaluate / "
@@ -338,7 +347,7 @@ class B200Sam(CallersMixin, nn.Module):
     def _decode_one_side(self, side: str, image_embeddings: torch.Tensor, sparse: torch.Tensor,
                          dense: Optional[torch.Tensor]):
         dec = self.mask_decoder_left if side == "left" else self.mask_decoder_right
-        self._no_autograd(f"mask_decoder_{side}", image_embeddings, sparse, params=dec.parameters())
+        self._no_autograd(f"mask_decoder_{side}", image_embeddings, sparse, module=dec)
         if image_embeddings.dim() != 4 or tuple(image_embeddings.shape) != (1, OUT_CH, GRID, GRID):
             raise ValueError(f"image_embeddings must be (1,{OUT_CH},{GRID},{GRID}) per call (LISA.py:306,505), got "
                              f"{tuple(image_embeddings.shape)}")
@@ -382,6 +391,99 @@ class B200Sam(CallersMixin, nn.Module):
         low = masks.to(torch.float32).contiguous().reshape(n * c, 256, 256)
         logits, _ = self._postprocess_raw(low, input_size, original_size, True, False, 0.0)
         return logits.reshape(n, c, int(original_size[0]), int(original_size[1]))
+
+    # ------------------------------------------------------------------ 1-bit wire format
+    @staticmethod
+    def bits_row_bytes(width: int) -> int:
+        return (int(width) + 7) // 8
+
+    @staticmethod
+    def unpack_bits(bits: torch.Tensor, width: int) -> torch.Tensor:
+        """(..., H, ceil(W/8)) packed u8 -> (..., H, W) u8 {0,1}; numpy.packbits(axis=-1) bit order.  A host/device
+        convenience for consumers of the wire format (tests, file writers); not used on the hot path."""
+        shifts = torch.arange(7, -1, -1, device=bits.device, dtype=torch.uint8)
+        full = (bits.unsqueeze(-1) >> shifts) & 1
+        return full.reshape(*bits.shape[:-1], bits.shape[-1] * 8)[..., :width].contiguous()
+
+    def checksum64(self, data: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Per-item 64-bit checksum (b200sam_checksum64) of a contiguous (n_items, ...) u8 tensor -> (n_items,) int64
+        (the bit pattern of the unsigned sum)."""
+        if data.dtype != torch.uint8 or not data.is_contiguous() or data.dim() < 1:
+            raise ValueError("checksum64 needs a contiguous uint8 tensor (n_items, ...)")
+        n = data.shape[0]
+        nbytes = data[0].numel() if n else 0
+        if out is None:
+            out = torch.empty((n,), dtype=torch.int64, device=data.device)
+        elif out.dtype != torch.int64 or out.numel() < n or not out.is_contiguous():
+            raise ValueError("out must be a contiguous int64 tensor with one element per item")
+        if n == 0:
+            return out
+        h = self._ensure_handle_only(data.device)
+        with torch.cuda.device(data.device):
+            rc = _lib.load().b200sam_checksum64(h, _ptr(data), n, nbytes, nbytes, _ptr(out), _stream_ptr())
+        _lib.check(rc, h, "checksum64")
+        return out
+
+    @torch.no_grad()
+    def segment_bits(self, frames: torch.Tensor, seg_embeds: Sequence[torch.Tensor], resize, original,
+                     threshold: float = 0.0, bits_out: Optional[torch.Tensor] = None,
+                     heads_out: Optional[torch.Tensor] = None, gt: Optional[torch.Tensor] = None,
+                     gt_index: Optional[torch.Tensor] = None) -> Dict[str, object]:
+        """`segment` for a batch that shares one (resize, original) size - a video clip - with the masks in the 1-bit
+        wire format and no staging copies: both decoders' masks are resampled and thresholded in ONE pass
+        (b200sam_postprocess_pair) straight into `bits_out` (2, cap >= P, H, ceil(W/8)) u8 [0 = left, 1 = right] and
+        the heads into `heads_out` (3, cap, 4) f32 [taxonomy, iou_left, iou_right] - clip.segment_clip passes views of
+        its NCCL send slot.  With `gt` ((G,H,W) u8) the evaluation of train_ds.py:662-709,761-796 is fused behind the
+        threshold: `counts` (P,3) int64 {intersection, union, area} and `pred_bits` (P,H,ceil(W/8)) come back too, and
+        no u8 plane is ever written.  Returns bits_left / bits_right (P,H,Wb) views, taxonomy, iou_left, iou_right,
+        offsets."""
+        B = frames.shape[0]
+        if len(seg_embeds) != B:
+            raise ValueError("seg_embeds must have one entry per frame")  # LISA.py:193
+        offsets = [0]
+        for e in seg_embeds:
+            if e.dim() != 2 or e.shape[1] != OUT_CH:
+                raise ValueError(f"seg_embeds entries must be (N,{OUT_CH})")
+            offsets.append(offsets[-1] + e.shape[0])
+        P = offsets[-1]
+        dev = frames.device
+        H, W = int(original[0]), int(original[1])
+        Wb = self.bits_row_bytes(W)
+        if bits_out is None:
+            bits_out = torch.empty((2, P, H, Wb), dtype=torch.uint8, device=dev)
+        elif (bits_out.dim() != 4 or bits_out.shape[0] != 2 or bits_out.shape[1] < P
+              or tuple(bits_out.shape[2:]) != (H, Wb) or bits_out.dtype != torch.uint8
+              or not bits_out.is_contiguous() or bits_out.device != dev):
+            raise ValueError(f"bits_out must be a contiguous (2, >={P}, {H}, {Wb}) uint8 tensor on {dev}")
+        self._ensure(dev, batch=B, prompts=P)
+        self._encode(frames, want_output=False)
+        seg = torch.cat([e.to(device=dev, dtype=torch.float32) for e in seg_embeds], 0) if B else \
+            torch.empty((0, OUT_CH), device=dev)
+        res = self._decode_raw(None, B, seg, offsets, True, True, dev, heads_out=heads_out)
+        out: Dict[str, object] = {"taxonomy": res["taxonomy"], "iou_left": res["iou_left"],
+                                  "iou_right": res["iou_right"], "offsets": offsets,
+                                  "lowres_left": res["lowres_left"], "lowres_right": res["lowres_right"],
+                                  "bits_left": bits_out[0, :P], "bits_right": bits_out[1, :P]}
+        counts = pred = None
+        if gt is not None:
+            if gt.dtype != torch.uint8 or gt.dim() != 3 or tuple(gt.shape[1:]) != (H, W) or not gt.is_contiguous():
+                raise ValueError(f"gt must be a contiguous (G,{H},{W}) uint8 tensor")
+            if gt_index is not None:
+                gt_index = gt_index.to(device=dev, dtype=torch.int32).contiguous()
+            elif gt.shape[0] < P:
+                raise ValueError("gt has fewer masks than prompts and no gt_index was given")
+            counts = torch.empty((P, 3), dtype=torch.int64, device=dev)
+            pred = torch.empty((P, H, Wb), dtype=torch.uint8, device=dev)
+            out["counts"], out["pred_bits"] = counts, pred
+        if P:
+            h = self._handle
+            with torch.cuda.device(dev):
+                rc = _lib.load().b200sam_postprocess_pair(
+                    h, _ptr(res["lowres_left"]), _ptr(res["lowres_right"]), P, int(resize[0]), int(resize[1]), H, W,
+                    _ptr(out["bits_left"]), _ptr(out["bits_right"]), float(threshold), _ptr(res["taxonomy"]),
+                    _ptr(gt), _ptr(gt_index), _ptr(counts), _ptr(pred), _stream_ptr())
+            _lib.check(rc, h, "postprocess_pair")
+        return out
 
     # ------------------------------------------------------------------ fused fast path
     @torch.no_grad()

@@ -168,12 +168,12 @@ def build_model(torch, max_batch: int, max_prompts: int):
 
 # ----------------------------------------------------------------------------------------------- CPU arm
 
-def cpu_reference_frames_per_s(torch, sd, n_prompts: int, steps: int, warmup: int):
-    """The oracle port (oracle/sam_oracle.py, fp32, all host threads) on ONE ViT-H frame x n_prompts per step:
+def cpu_reference_frames_per_s(torch, sd, n_prompts: int, steps: int, warmup: int, arch_name: str = "vit_h"):
+    """The oracle port (oracle/sam_oracle.py, fp32, all host threads) on ONE frame x n_prompts per step:
     encode + both decoders + postprocess + threshold.  Returns (frames/s, seconds per step list, threads)."""
     from oracle import sam_oracle as O
     from oracle import synth
-    arch = synth.ARCHS["vit_h"]
+    arch = synth.ARCHS[arch_name]
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
     times = []
@@ -189,6 +189,21 @@ def cpu_reference_frames_per_s(torch, sd, n_prompts: int, steps: int, warmup: in
             if it >= warmup:
                 times.append(dt)
     return len(times) / sum(times), times, threads
+
+
+def cpu_baseline_block(torch, sd_vit_h, n_prompts: int) -> dict:
+    """the CPU path timed with 1 warm-up + median of 3 on (a) the headline workload's model,
+    ViT-H 1 frame x n_prompts, and (b) BASELINE config 1 exactly (ViT-B, 1 frame, 2 prompts).  `value` is (a)."""
+    from oracle import synth
+    _, t_h, threads = cpu_reference_frames_per_s(torch, sd_vit_h, n_prompts, 3, 1, "vit_h")
+    sd_b = synth.make_state_dict(synth.ARCHS["vit_b"], seed=0)
+    _, t_b, _ = cpu_reference_frames_per_s(torch, sd_b, 2, 3, 1, "vit_b")
+    med_h, med_b = statistics.median(t_h), statistics.median(t_b)
+    return {"value": 1.0 / med_h, "unit": "frames/s", "cores": threads, "kind": "port",
+            "sample": f"1 ViT-H frame x {n_prompts} prompts, fp32 oracle port, 1 warm-up + median of 3 "
+                      f"({med_h:.2f} s per frame)",
+            "config1_vit_b": {"value": 1.0 / med_b, "unit": "frames/s", "seconds_per_frame": med_b,
+                              "sample": "BASELINE configs[0]: ViT-B, 1 frame x 2 prompts, fp32, 1 warm-up + median of 3"}}
 
 
 def run_reference_arm(args):
@@ -218,7 +233,8 @@ def run_reference_arm(args):
 
 def workload_config(args, frames_per_step: int) -> dict:
     return {"workload": "configs[1]: SAM ViT-H bf16, batch of synthetic 1024^2 frames x 3 [SEG] prompts "
-                        "(left+right decoders, taxonomy), postprocess to 1080x1920 + threshold",
+                        "(left+right decoders, taxonomy), postprocess to 1080x1920 + threshold, masks in the 1-bit "
+                        "wire format (numpy.packbits order)",
             "frames_per_step_per_gpu": frames_per_step, "prompts_per_frame": args.prompts,
             "resize": list(RESIZE), "original_size": list(ORIGINAL), "parallelism": f"frames sharded x{args.gpus}",
             "l2": "per-step working set (1.27 GB bf16 weights + >4 GB activations) >> 126 MB L2; no explicit flush"}
@@ -286,6 +302,42 @@ def measure_callers(torch, sam, dev, last_out, B, NP, iters=20):
     return res
 
 
+def measure_latency_b1(torch, sam, frame, seg, iters: int = 10):
+    """One frame x its prompts through the drop-in exactly as LISAForCausalLM.evaluate drives the reference modules
+    (LISA.py:162 image_encoder, :498-503 prompt_encoder, :505-530 both decoders, :511-527 postprocess_masks), then the
+    callers' threshold and the copy of the masks to the host (chat.py:231, inference.py:276-301).  CUDA-event time of
+    the device work and wall time including the host read-back, median over `iters` after 2 warm-ups."""
+    ev_ms, wall_ms = [], []
+    with torch.no_grad():
+        for it in range(iters + 2):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            emb = sam.image_encoder(frame)
+            sparse, dense = sam.prompt_encoder(points=None, boxes=None, masks=None, text_embeds=seg.unsqueeze(1))
+            sparse = sparse.to(seg.dtype)
+            pe = sam.prompt_encoder.get_dense_pe()
+            low_l, iou_l, tax = sam.mask_decoder_left(image_embeddings=emb[0].unsqueeze(0), image_pe=pe,
+                                                      sparse_prompt_embeddings=sparse,
+                                                      dense_prompt_embeddings=dense, multimask_output=False)
+            pl = sam.postprocess_masks(low_l, input_size=RESIZE, original_size=ORIGINAL)
+            low_r, iou_r = sam.mask_decoder_right(image_embeddings=emb[0].unsqueeze(0), image_pe=pe,
+                                                  sparse_prompt_embeddings=sparse, dense_prompt_embeddings=dense,
+                                                  multimask_output=False)
+            pr = sam.postprocess_masks(low_r, input_size=RESIZE, original_size=ORIGINAL)
+            ml, mr = pl[:, 0] > 0, pr[:, 0] > 0
+            e1.record()
+            _ = ml.cpu(), mr.cpu(), tax.cpu()
+            wall = (time.perf_counter() - t0) * 1e3
+            if it >= 2:
+                ev_ms.append(e0.elapsed_time(e1))
+                wall_ms.append(wall)
+    return {"device_ms": statistics.median(ev_ms), "wall_ms_incl_host_masks": statistics.median(wall_ms),
+            "what": f"1 ViT-H frame x {seg.shape[0]} prompts via image_encoder / prompt_encoder / mask_decoder_left / "
+                    "mask_decoder_right / postprocess_masks (fp32 logits) as LISA.evaluate calls them, bool masks to host"}
+
+
 def read_profile(lib, handle):
     ms = (C.c_float * len(PC_NAMES))()
     cnt = (C.c_int64 * len(PC_NAMES))()
@@ -326,23 +378,34 @@ def run_gpu_arm(args):
     H, W = ORIGINAL
     clip = importlib.import_module(PKG + ".clip")
 
-    def step(fr, sg):
-        return sam.segment(fr, sg, resize, original, threshold=0.0, return_logits=False)
+    lay = clip.SlotLayout(B, NP, ORIGINAL)
+    slot_dev = torch.zeros((lay.nbytes,), dtype=torch.uint8, device=dev)     # N = 1: the message the kernels write
+    slot_bits, slot_heads, _, _ = lay.views(slot_dev)
 
-    def run_steps(k, load, sink=None, prefetch=False):
-        """k steps.  N = 1: k segment() calls.  N > 1: the product clip path - a clip of world*B*k frames sharded
-        over the ranks, one micro-batch of B frames per rank per step, u8 masks + heads gathered to rank 0 over
-        NCCL asynchronously behind the next micro-batch."""
+    def step(fr, sg):
+        # masks leave the device in the 1-bit wire format (b200sam_postprocess_pair): same information as the u8
+        # masks of segment(), an eighth of the bytes
+        return sam.segment_bits(fr, sg, RESIZE, ORIGINAL, threshold=0.0, bits_out=slot_bits, heads_out=slot_heads)
+
+    clip_stats = {"masks_checked": 0, "checksum_mismatches": 0, "frames": 0}
+
+    def run_steps(k, load, batch_sink=None, prefetch=False):
+        """k steps.  N = 1: k segment_bits() calls.  N > 1: the product clip path - a clip of world*B*k frames sharded
+        over the ranks, one micro-batch of B frames per rank per step, packed masks + heads + checksums gathered to
+        rank 0 over NCCL asynchronously behind the next micro-batch and streamed to pinned host memory
+        (SURVEY.md 8e)."""
         if world == 1:
             out = None
             for _ in range(k):
                 out = step(*load(0, B))
-                if sink is not None:
-                    sink(out)
             return out
-        return clip.segment_clip(sam.segment, load, world * B * k, RESIZE, ORIGINAL, micro_batch=B,
-                                 max_prompts_per_frame=NP, threshold=0.0, device=dev, sink=sink, keep=False,
-                                 prefetch=prefetch)
+        res = clip.segment_clip(sam.segment_bits, load, world * B * k, RESIZE, ORIGINAL, micro_batch=B,
+                                max_prompts_per_frame=NP, threshold=0.0, device=dev, batch_sink=batch_sink,
+                                keep=False, prefetch=prefetch, checksum_fn=sam.checksum64)
+        clip_stats["masks_checked"] += res.masks_checked
+        clip_stats["checksum_mismatches"] += res.checksum_mismatches
+        clip_stats["frames"] += res.frames_done
+        return res
 
     def resident(lo, hi):
         return frames, segs
@@ -364,7 +427,7 @@ def run_gpu_arm(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
-    out = run_steps(args.steps, resident)
+    run_steps(args.steps, resident)
     ev1.record()
     barrier()
     ms_total = ev0.elapsed_time(ev1)
@@ -376,50 +439,40 @@ def run_gpu_arm(args):
     ms_total = float(t.item())
     fps = world * B * args.steps / (ms_total * 1e-3)
 
-    # ---- timed region 2: end to end from pinned host buffers (H2D frames + prompts, D2H masks + heads)
-    host_masks = torch.empty((2, P, H, W), dtype=torch.uint8).pin_memory()
-    host_heads = torch.empty((3, P, 4), dtype=torch.float32).pin_memory()
+    # ---- timed region 2: end to end from pinned host buffers (H2D frames + prompts, D2H packed masks + heads)
     h2d = host_frames.numel() * host_frames.element_size() + host_seg.numel() * 4
-    d2h = host_masks.numel() + host_heads.numel() * 4
+    d2h = lay.nbytes
 
     def from_host(lo, hi):
         fr = host_frames.to(dev, non_blocking=True)
         sg_all = host_seg.to(dev, non_blocking=True)
         return fr, [sg_all[i * NP:(i + 1) * NP] for i in range(B)]
 
-    def to_host_1(o):               # N = 1: the caller consumes the masks on the host after every step
-        host_masks[0].copy_(o["masks_left_packed"], non_blocking=True)
-        host_masks[1].copy_(o["masks_right_packed"], non_blocking=True)
-        host_heads[0].copy_(o["taxonomy"], non_blocking=True)
-        host_heads[1].copy_(o["iou_left"], non_blocking=True)
-        host_heads[2].copy_(o["iou_right"], non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+    first_block = {}
 
-    def to_host_n(f, ml, mr, tx, il, ir):   # N > 1, rank 0: every gathered frame goes to pinned host memory
-        a = (f % B) * NP
-        host_masks[0, a:a + NP].copy_(ml, non_blocking=True)
-        host_masks[1, a:a + NP].copy_(mr, non_blocking=True)
-        host_heads[0, a:a + NP].copy_(tx, non_blocking=True)
-        host_heads[1, a:a + NP].copy_(il, non_blocking=True)
-        host_heads[2, a:a + NP].copy_(ir, non_blocking=True)
+    def host_sink(src, lo, cnt, bits, heads):
+        """N > 1, rank 0 (consumer thread): the gathered round already sits in pinned host memory; keep the first
+        block of the last rank for the cross-GPU identity check below."""
+        if src == world - 1 and "bits" not in first_block and lo == clip.shard_range(world * B * args.steps, src, world)[0]:
+            first_block["bits"], first_block["heads"], first_block["cnt"] = bits.clone(), heads.clone(), list(cnt)
 
     # N = 1: the public host-to-host API (clip.HostPipeline): every step uploads ITS frames + prompts from pinned host
-    # memory and downloads ITS masks + heads, with the copies of neighbouring steps overlapping the kernels.
-    # N > 1: segment_clip with host loads and a host sink on rank 0.
-    pipe = clip.HostPipeline(sam.segment, B, NP, RESIZE, ORIGINAL, dev) if world == 1 else None
+    # memory and downloads ITS message (packed masks + heads), the copies of neighbouring steps overlapping the kernels.
+    # N > 1: segment_clip with host loads (prefetched on an upload stream) and the host-side consumer on rank 0.
+    pipe = clip.HostPipeline(sam.segment_bits, B, NP, RESIZE, ORIGINAL, dev) if world == 1 else None
 
-    def e2e_run(k):
+    def e2e_run(k, sink=None):
         if world == 1:
             for _ in range(k):
                 pipe.submit(host_frames, host_seg)
             pipe.flush()                         # the caller consumes the masks on the host
         else:
-            run_steps(k, from_host, to_host_n, prefetch=True)
+            run_steps(k, from_host, sink, prefetch=True)
 
     e2e_run(2)
     barrier()
     t0 = time.perf_counter()
-    e2e_run(args.steps)
+    e2e_run(args.steps, host_sink)
     barrier()
     e2e_s = time.perf_counter() - t0
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -427,13 +480,39 @@ def run_gpu_arm(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_fps = world * B * args.steps / float(t.item())
 
+    # ---- what rank 0 received is what the producers computed, and what a single GPU computes (untimed)
+    gather_verified = None
+    if world > 1 and rank == 0:
+        src = world - 1
+        fr = make_frames(torch, src * B, B).to(torch.bfloat16).to(dev)
+        sg = [make_seg(torch, src * B + i, NP).to(dev) for i in range(B)]
+        own = sam.segment_bits(fr, sg, RESIZE, ORIGINAL, threshold=0.0)
+        same = ("bits" in first_block and first_block["cnt"] == [NP] * B
+                and torch.equal(first_block["bits"][0], own["bits_left"].cpu())
+                and torch.equal(first_block["bits"][1], own["bits_right"].cpu())
+                and torch.equal(first_block["heads"][0], own["taxonomy"].cpu())
+                and torch.equal(first_block["heads"][1], own["iou_left"].cpu())
+                and torch.equal(first_block["heads"][2], own["iou_right"].cpu()))
+        gather_verified = {
+            "ok": bool(same and clip_stats["checksum_mismatches"] == 0 and clip_stats["masks_checked"] > 0),
+            "frames_gathered": clip_stats["frames"], "masks_checksummed": clip_stats["masks_checked"],
+            "checksum_mismatches": clip_stats["checksum_mismatches"],
+            "cross_gpu": {"frames": B, "source_rank": src, "bit_identical_to_rank0_recompute": bool(same)},
+            "how": "b200sam_checksum64 of every (side, prompt) mask on the producing rank vs. on the bytes the NCCL "
+                   "gather delivered; plus rank 0 recomputes the last rank's first micro-batch on its own GPU"}
+
+    # ---- B = 1 latency through the reference's own call sequence (LISA.evaluate, LISA.py:487-532)
+    latency = None
+    if rank == 0:
+        latency = measure_latency_b1(torch, sam, frames[:1], segs[0])
+
     # ---- per-launch CUDA events (b200sam_profile_*) over the same steps -> roofline of the dominant kernel
     kernels, roofline = {}, None
     if rank == 0:
         lib.b200sam_profile_enable(handle, 1)
         psteps = min(args.steps, 3)
         for _ in range(psteps):
-            sam.segment(frames, segs, resize, original, threshold=0.0)
+            step(frames, segs)
         torch.cuda.synchronize()
         prof = read_profile(lib, handle)
         lib.b200sam_profile_enable(handle, 0)
@@ -455,16 +534,22 @@ def run_gpu_arm(args):
                     "flops_per_launch": fl[dom] * B / kd["launches_per_step"],
                     "avg_launch_ms": kd["ms_per_step"] / kd["launches_per_step"],
                     "whole_step_tflops": fl["total"] * B / (ms_total / args.steps * 1e-3) / 1e12,
-                    "whole_step_frac": fl["total"] * B / (ms_total / args.steps * 1e-3) / 1e12 / peaks["bf16_sustained"]}
+                    "whole_step_frac": fl["total"] * B / (ms_total / args.steps * 1e-3) / 1e12 / peaks["bf16_sustained"],
+                    "whole_step_frac_of": {
+                        "measured_sustained": fl["total"] * B / (ms_total / args.steps * 1e-3) / 1e12 / peaks["bf16_sustained"],
+                        "measured_burst": fl["total"] * B / (ms_total / args.steps * 1e-3) / 1e12 / peaks["bf16_burst"],
+                        "nominal_2250": fl["total"] * B / (ms_total / args.steps * 1e-3) / 1e12 / 2250.0}}
 
-    aux = measure_callers(torch, sam, dev, out, B, NP) if (rank == 0 and world == 1) else None
+    aux = None
+    if rank == 0 and world == 1:
+        out_u8 = sam.segment(frames, segs, resize, original, threshold=0.0)
+        aux = measure_callers(torch, sam, dev, out_u8, B, NP)
+        del out_u8
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         sd = {k: v.detach().float().cpu() for k, v in sam.state_dict().items()}
-        cfps, times, threads = cpu_reference_frames_per_s(torch, sd, NP, 1, 0)
-        cpu = {"value": cfps, "unit": "frames/s", "cores": threads, "kind": "port",
-               "sample": f"1 ViT-H frame x {NP} prompts, fp32 oracle port, {times[0]:.1f} s"}
+        cpu = cpu_baseline_block(torch, sd, NP)
 
     if rank == 0:
         line = {
@@ -474,7 +559,7 @@ def run_gpu_arm(args):
             "config": workload_config(args, B),
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-            "kernels": kernels, "callers": aux,
+            "kernels": kernels, "callers": aux, "latency_b1_ms": latency, "gather_verified": gather_verified,
         }
         print(json.dumps(line))
     if world > 1:

@@ -77,6 +77,30 @@ int b200sam_decode(b200sam_t* h, const void* emb, int emb_dtype, int B, const fl
 int b200sam_postprocess(b200sam_t* h, const float* lowres, int n_masks, int in_h, int in_w, int out_h, int out_w,
                         float* logits_out, uint8_t* mask_out, float threshold, void* stream);
 
+/* Same resampling + threshold, written in the 1-bit wire format (1.56 MB instead of 12.4 MB per
+ * 1080p frame through NVLink and PCIe): bits_out (n, H, ceil(W/8)) u8, bit 7 of byte X/8 = pixel 8*(X/8) - the layout
+ * of numpy.packbits(mask, axis=-1); the pad bits of a row's last byte are 0.  bits_out may be any device address, e.g.
+ * a slice of the send buffer of the gather (clip.segment_clip writes there directly, no staging copy). */
+int b200sam_postprocess_bits(b200sam_t* h, const float* lowres, int n_masks, int in_h, int in_w, int out_h,
+                             int out_w, uint8_t* bits_out, float threshold, void* stream);
+
+/* Both decoders' masks of P prompts in ONE pass over the low-res logits: postprocess + threshold of the left and the
+ * right mask -> bits_left / bits_right (packed as above, either may be NULL) and, when gt != NULL, the evaluation of
+ * train_ds.py:662-709,761-796 fused behind the threshold - the taxonomy-gated prediction (argmax 0: left, 1: right,
+ * 2/3: left|right) against gt[gt_index[p]] ((G,H,W) u8, non-zero = set; gt_index NULL: gt[p]) reduced to
+ * counts_out (P,3) int64 {intersection, union, predicted area}, plus the packed gated prediction pred_bits_out
+ * (nullable).  No full-resolution u8 plane is written or re-read. */
+int b200sam_postprocess_pair(b200sam_t* h, const float* lowres_left, const float* lowres_right, int P, int in_h,
+                             int in_w, int out_h, int out_w, uint8_t* bits_left, uint8_t* bits_right, float threshold,
+                             const float* taxonomy, const uint8_t* gt, const int* gt_index, int64_t* counts_out,
+                             uint8_t* pred_bits_out, void* stream);
+
+/* out[i] = 64-bit position-sensitive checksum of the byte string data[i*stride, i*stride + bytes): the sum over its
+ * 8-byte little-endian words w_k (tail zero padded) of splitmix64_final(w_k ^ (k+1)*0x9E3779B97F4A7C15) mod 2^64.
+ * Shipped beside the packed masks by clip.segment_clip so that the gathering rank can verify what arrived. */
+int b200sam_checksum64(b200sam_t* h, const void* data, int n_items, int64_t bytes, int64_t stride, uint64_t* out,
+                       void* stream);
+
 /* ---- the callers either side of the branch ---- */
 
 /* ResizeLongestSide(1024).apply_image (segment_anything/utils/transforms.py:27-34: torchvision resize of a PIL image

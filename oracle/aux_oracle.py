@@ -78,3 +78,40 @@ def iou_iocm(pred255: np.ndarray, gt: np.ndarray) -> Tuple[float, float]:
     comparison_area = int(pred255.astype(np.int64).sum())          # = 255 * area (reference quirk, see header)
     iocm = inter / comparison_area if comparison_area != 0 else 0.0
     return iou, iocm
+
+
+# ---------------------------------------------------------------------------------------------- wire format
+
+def pack_bits(mask: np.ndarray) -> np.ndarray:
+    """(..., H, W) {0,1} -> (..., H, ceil(W/8)) u8: the 1-bit wire format of b200sam_postprocess_bits (bit 7 of byte
+    X/8 = pixel 8*(X/8), pad bits 0) - numpy.packbits along the row, which is also how the golden fixtures store masks."""
+    return np.packbits(mask.astype(bool), axis=-1)
+
+
+_MASK64 = (1 << 64) - 1
+
+
+def _mix64(z: int) -> int:
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & _MASK64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & _MASK64
+    return z ^ (z >> 31)
+
+
+def checksum64(data: np.ndarray) -> np.ndarray:
+    """include/b200sam.h b200sam_checksum64: per item of a (n, ...) u8 array, the sum over its 8-byte little-endian
+    words w_k (tail zero padded) of splitmix64_final(w_k ^ (k+1) * 0x9E3779B97F4A7C15) mod 2^64, returned as int64 bit
+    patterns.  Vectorised with numpy uint64 wrap-around arithmetic."""
+    d = np.ascontiguousarray(data).reshape(data.shape[0], -1).astype(np.uint8)
+    n, nb = d.shape
+    pad = (-nb) % 8
+    if pad:
+        d = np.concatenate([d, np.zeros((n, pad), np.uint8)], axis=1)
+    w = d.view("<u8")
+    k = (np.arange(1, w.shape[1] + 1, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15))
+    with np.errstate(over="ignore"):
+        z = w ^ k
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+        s = z.sum(axis=1, dtype=np.uint64)
+    return s.view(np.int64)

@@ -12,6 +12,12 @@ if ROOT not in sys.path:
 
 PKG = "2handedafforder_b200"
 
+# fp32 references computed with torch on the GPU must really be fp32 (SURVEY.md 8c hygiene note): cuDNN convolutions
+# default to TF32, and matmul precision is pinned explicitly rather than relying on the default.
+torch.backends.cuda.matmul.allow_tf32 = False
+torch.backends.cudnn.allow_tf32 = False
+torch.set_float32_matmul_precision("highest")
+
 
 def pkg():
     return importlib.import_module(PKG)

@@ -114,3 +114,76 @@ def test_postprocess_matches_interpolate(tiny, resize, original):
     _, mask = sam._postprocess_raw(low[:, 0].contiguous(), resize, original, False, True, 0.25)
     logits, _ = sam._postprocess_raw(low[:, 0].contiguous(), resize, original, True, False, 0.0)
     assert torch.equal(mask.bool(), logits > 0.25)
+
+
+def test_training_forward_is_refused_not_detached(tiny):
+    """LISA.model_forward with train_mask_decoder=True (LISA.py:84-90,284-325) needs gradients the library cannot give:
+    the facade raises instead of returning tensors without grad_fn; inference paths are unaffected."""
+    sam, _, _ = tiny
+    frames = synth.make_frames(0, 1).cuda()
+    with torch.no_grad():
+        emb = sam.image_encoder(frames)
+    seg = synth.make_seg_embeds(0, 2).cuda().requires_grad_(True)          # output of the trainable text_hidden_fcs
+    sparse, dense = sam.prompt_encoder(None, None, None, seg.unsqueeze(1))
+    assert sparse.requires_grad
+    with pytest.raises(NotImplementedError, match="inference-only"):
+        sam.mask_decoder_left(emb, sam.prompt_encoder.get_dense_pe(), sparse, dense, False)
+    with torch.no_grad():                                                   # LISA.evaluate / validate
+        low, iou, tax = sam.mask_decoder_left(emb, sam.prompt_encoder.get_dense_pe(), sparse, dense, False)
+    assert low.shape == (2, 1, 256, 256)
+    sam.mask_decoder_right.train()                                          # LISA.py:86-90
+    try:
+        with pytest.raises(NotImplementedError):
+            sam.mask_decoder_right(emb, sam.prompt_encoder.get_dense_pe(), sparse.detach(), dense, False)
+    finally:
+        sam.mask_decoder_right.eval()
+    sam.mask_decoder_right(emb, sam.prompt_encoder.get_dense_pe(), sparse.detach(), dense, False)   # eval: fine
+    with pytest.raises(NotImplementedError):
+        sam.postprocess_masks(low.clone().requires_grad_(True), (576, 1024), (64, 64))
+
+
+def test_weight_resync_keeps_memory_flat(tiny):
+    """validate() between training epochs of the mask decoders (train_ds.py:236-244,625-758): every parameter change
+    re-finalises the handle; the derived buffers must be replaced, not accumulated, and the outputs must follow."""
+    sam, _, _ = tiny
+    frames = synth.make_frames(1, 1).cuda()
+    seg = [synth.make_seg_embeds(1, 2).cuda()]
+    args = ([(576, 1024)], [(64, 96)])
+    p = sam.mask_decoder_left.iou_prediction_head.layers._modules["2"].bias
+    q = sam.image_encoder.blocks._modules["1"].attn.rel_pos_h
+    base = sam.segment(frames, seg, *args)
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    for it in range(20):
+        with torch.no_grad():
+            p.add_(0.5)
+            if it % 5 == 0:
+                q.mul_(1.0)                     # encoder group: version bump -> encoder packs rebuilt too
+        out = sam.segment(frames, seg, *args)
+    torch.cuda.synchronize()
+    free1 = torch.cuda.mem_get_info()[0]
+    assert abs(free0 - free1) < 64 << 20, f"free memory moved by {(free0 - free1) / 2**20:.1f} MiB over 20 re-syncs"
+    assert torch.allclose(out["iou_left"], base["iou_left"] + 10.0, atol=1e-4)
+    assert torch.equal(out["masks_left_packed"], base["masks_left_packed"])
+    with torch.no_grad():
+        p.sub_(10.0)
+
+
+def test_fp16_overflow_of_relpos_projection_is_reported(tiny):
+    """The global blocks keep q.Rh / q.Rw as fp16: values beyond 65504 are saturated (no inf/NaN in the output) and the
+    NEXT library call fails loudly; restoring the weights restores service."""
+    sam, _, _ = tiny
+    frames = synth.make_frames(2, 1).cuda()
+    good = sam.image_encoder(frames).clone()
+    rel = sam.image_encoder.blocks._modules["1"].attn.rel_pos_w          # tiny64: block 1 is the global one
+    keep = rel.detach().clone()
+    with torch.no_grad():
+        rel.fill_(3.0e4)
+    bad = sam.image_encoder(frames)
+    torch.cuda.synchronize()
+    assert torch.isfinite(bad.float()).all()
+    with pytest.raises(RuntimeError, match="saturated the fp16 rel-pos"):
+        sam.image_encoder(frames)
+    with torch.no_grad():
+        rel.copy_(keep)
+    assert torch.equal(sam.image_encoder(frames), good)

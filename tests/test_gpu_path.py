@@ -15,7 +15,7 @@ import torch
 from oracle import sam_oracle as O
 from oracle import synth
 from tests import gpu_util as G
-from tests.golden.make_golden import CASES, TAP_POS
+from tests.golden.make_golden import CASES, LITE_CASES, TAP_POS
 
 pytestmark = pytest.mark.gpu
 
@@ -45,6 +45,38 @@ def _taps(sam, frames, nblocks):
     return out
 
 
+def _check_frame(case, g, gi, out, bi, n_prompts):
+    """Frame `bi` of the batch result `out` against frame `gi` of golden fixture `g` (north_star pass criteria)."""
+    offs = out["offsets"]
+    sl = slice(offs[bi], offs[bi + 1])
+    assert offs[bi + 1] - offs[bi] == n_prompts
+    for side in ("left", "right"):
+        ref_low = torch.from_numpy(g[f"f{gi}_lowres_{side}"].astype(np.float32))
+        got_low = out[f"lowres_{side}"][sl].cpu()
+        logits = out[f"logits_{side}"][bi].cpu()
+        masks = out[f"masks_{side}"][bi].cpu()
+        assert torch.equal(masks.bool(), logits > 0)
+        bits = np.unpackbits(g[f"f{gi}_bits_{side}"], axis=-1)[..., : logits.shape[-1]].astype(bool)
+        samp = torch.from_numpy(g[f"f{gi}_full_{side}_samples"])
+        absmax = torch.from_numpy(g[f"f{gi}_full_{side}_absmax"])
+        for n in range(n_prompts):
+            e_low = O.logit_rel_err(got_low[n], ref_low[n])
+            e_full = float((logits[n, ::37, ::41] - samp[n]).abs().max() / absmax[n])
+            iou = O.mask_iou(logits[n], torch.from_numpy(bits[n]).float() - 0.5)
+            _report(case=case, frame=gi, side=side, prompt=n, lowres_err=e_low, full_err=e_full, iou=iou)
+            # the golden low-res logits of the ViT-H / ViT-L cases are stored as fp16 (5e-4 relative): inside the bound
+            assert e_low <= 2e-2, f"{case} f{gi} {side} p{n}: low-res logit error {e_low:.3e}"
+            assert e_full <= 2e-2, f"{case} f{gi} {side} p{n}: full-res logit error {e_full:.3e}"
+            assert iou >= 0.99, f"{case} f{gi} {side} p{n}: thresholded IoU {iou:.4f}"
+        iou_head = out[f"iou_{side}"][sl].cpu().numpy()
+        _report(case=case, frame=gi, side=side, iou_head_err=float(np.abs(iou_head - g[f"f{gi}_iou_{side}"]).max()))
+        assert np.array_equal(iou_head.argmax(-1), g[f"f{gi}_iou_{side}"].argmax(-1))
+    tax = out["taxonomy"][sl].cpu().numpy()
+    _report(case=case, frame=gi, tax_err=float(np.abs(tax - g[f"f{gi}_taxonomy"]).max()))
+    assert np.array_equal(tax.argmax(-1), g[f"f{gi}_taxonomy"].argmax(-1))
+    assert np.allclose(tax.sum(-1), 1.0, atol=1e-5)
+
+
 def _run_case(case, golden, tap_blocks, frame_dtype=torch.float32):
     arch_name, n_frames, n_prompts, resize, original = CASES[case]
     g = golden(case)
@@ -70,33 +102,8 @@ def _run_case(case, golden, tap_blocks, frame_dtype=torch.float32):
 
     out = sam.segment(frames, segs, [resize] * n_frames, [original] * n_frames, threshold=0.0, return_logits=True)
     torch.cuda.synchronize()
-    offs = out["offsets"]
     for i in range(n_frames):
-        sl = slice(offs[i], offs[i + 1])
-        for side in ("left", "right"):
-            ref_low = torch.from_numpy(g[f"f{i}_lowres_{side}"].astype(np.float32))
-            got_low = out[f"lowres_{side}"][sl].cpu()
-            logits = out[f"logits_{side}"][i].cpu()
-            masks = out[f"masks_{side}"][i].cpu()
-            assert torch.equal(masks.bool(), logits > 0)
-            bits = np.unpackbits(g[f"f{i}_bits_{side}"], axis=-1)[..., : logits.shape[-1]].astype(bool)
-            samp = torch.from_numpy(g[f"f{i}_full_{side}_samples"])
-            absmax = torch.from_numpy(g[f"f{i}_full_{side}_absmax"])
-            for n in range(n_prompts):
-                e_low = O.logit_rel_err(got_low[n], ref_low[n])
-                e_full = float((logits[n, ::37, ::41] - samp[n]).abs().max() / absmax[n])
-                iou = O.mask_iou(logits[n], torch.from_numpy(bits[n]).float() - 0.5)
-                _report(case=case, frame=i, side=side, prompt=n, lowres_err=e_low, full_err=e_full, iou=iou)
-                assert e_low <= 2e-2 + 2e-3, f"{case} f{i} {side} p{n}: low-res logit error {e_low:.3e}"
-                assert e_full <= 2e-2, f"{case} f{i} {side} p{n}: full-res logit error {e_full:.3e}"
-                assert iou >= 0.99, f"{case} f{i} {side} p{n}: thresholded IoU {iou:.4f}"
-            iou_head = out[f"iou_{side}"][sl].cpu().numpy()
-            _report(case=case, frame=i, side=side, iou_head_err=float(np.abs(iou_head - g[f"f{i}_iou_{side}"]).max()))
-            assert np.array_equal(iou_head.argmax(-1), g[f"f{i}_iou_{side}"].argmax(-1))
-        tax = out["taxonomy"][sl].cpu().numpy()
-        _report(case=case, frame=i, tax_err=float(np.abs(tax - g[f"f{i}_taxonomy"]).max()))
-        assert np.array_equal(tax.argmax(-1), g[f"f{i}_taxonomy"].argmax(-1))
-        assert np.allclose(tax.sum(-1), 1.0, atol=1e-5)
+        _check_frame(case, g, i, out, i, n_prompts)
     return sam, out
 
 
@@ -116,3 +123,41 @@ def test_path_vit_b_config1(golden):
 def test_path_vit_h_config2(golden):
     """Two frames of BASELINE.json configs[1] (ViT-H, 3 prompts per frame), bf16 frames as inference.py feeds them."""
     _run_case("vit_h_cfg2", golden, tap_blocks=[1, 8, 16, 32], frame_dtype=torch.bfloat16)
+
+
+def test_path_vit_h_all_eight_frames_of_config2(golden):
+    """All 8 frames of BASELINE.json configs[1] in ONE batch (the benchmark's shape) against the unmodified reference:
+    frame 0 from vit_h_cfg2.npz, frames 2..7 from vit_h_cfg2_rest.npz - and frame 1 carries NO [SEG] prompt
+    (LISA.evaluate with an image whose answer has no [SEG], chat.py:227), which must not disturb its neighbours
+    (frame 1 with its prompts is covered by test_path_vit_h_config2)."""
+    arch_name, first, n_rest, n_prompts, resize, original = LITE_CASES["vit_h_cfg2_rest"]
+    g0, g1 = golden("vit_h_cfg2"), golden("vit_h_cfg2_rest")
+    B = first + n_rest
+    sam, arch, sd = G.build_sam_from_synth(arch_name, max_batch=B, max_prompts=B * n_prompts)
+    frames = synth.make_frames(0, B, valid_rows=resize[0]).cuda().to(torch.bfloat16)
+    segs = [synth.make_seg_embeds(i, n_prompts).cuda() for i in range(B)]
+    segs[1] = segs[1][:0]
+    out = sam.segment(frames, segs, [resize] * B, [original] * B, threshold=0.0, return_logits=True)
+    torch.cuda.synchronize()
+    assert out["masks_left"][1].shape == (0, *original) and out["offsets"][2] == out["offsets"][1]
+    _check_frame("vit_h_cfg2_b8", g0, 0, out, 0, n_prompts)
+    for j in range(n_rest):
+        _check_frame("vit_h_cfg2_b8", g1, j, out, first + j, n_prompts)
+
+
+def test_path_vit_l(golden):
+    """build_sam_vit_l (dim 1024, 24 blocks, head dim 64, global blocks {5,11,17,23}): one frame x 3 prompts."""
+    arch_name, first, n_frames, n_prompts, resize, original = LITE_CASES["vit_l_lite"]
+    g = golden("vit_l_lite")
+    sam = G.pkg().build_sam_vit_l(max_batch=1, max_prompts=n_prompts)
+    sam.load_state_dict(synth.make_state_dict(synth.ARCHS[arch_name], seed=0), strict=True)
+    sam = sam.cuda()
+    frames = synth.make_frames(0, 1, valid_rows=resize[0]).cuda().to(torch.bfloat16)
+    emb = sam.image_encoder(frames)
+    err = O.logit_rel_err(emb[:, ::16].float().cpu(), torch.from_numpy(g["emb_slice"]))
+    _report(case="vit_l_lite", stage="emb", rel_err=err)
+    assert err < 3e-2
+    out = sam.segment(frames, [synth.make_seg_embeds(0, n_prompts).cuda()], [resize], [original], threshold=0.0,
+                      return_logits=True)
+    torch.cuda.synchronize()
+    _check_frame("vit_l_lite", g, 0, out, 0, n_prompts)

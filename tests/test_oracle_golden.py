@@ -11,17 +11,21 @@ import torch
 
 from oracle import sam_oracle as O
 from oracle import synth
-from tests.golden.make_golden import CASES, TAP_POS
+from tests.golden.make_golden import CASES, LITE_CASES, TAP_POS
 
 
 def _run_oracle(case):
-    arch_name, n_frames, n_prompts, resize, original = CASES[case]
+    if case in LITE_CASES:
+        arch_name, first, n_frames, n_prompts, resize, original = LITE_CASES[case]
+    else:
+        arch_name, n_frames, n_prompts, resize, original = CASES[case]
+        first = 0
     arch = synth.ARCHS[arch_name]
     w = synth.make_state_dict(arch, seed=0)
-    frames = synth.make_frames(0, n_frames, valid_rows=resize[0])
+    frames = synth.make_frames(first, n_frames, valid_rows=resize[0])
     taps = {}
     emb = O.encode(w, arch, frames, O.FP32, taps=taps)
-    segs = [synth.make_seg_embeds(i, n_prompts) for i in range(n_frames)]
+    segs = [synth.make_seg_embeds(first + i, n_prompts) for i in range(n_frames)]
     outs = O.segment(w, arch, frames, segs, [resize] * n_frames, [original] * n_frames, O.FP32, emb=emb)
     return arch, w, emb, taps, outs
 
@@ -30,7 +34,7 @@ def _check(case, golden, tol=2e-4):
     g = golden(case)
     arch, w, emb, taps, outs = _run_oracle(case)
     pos = torch.tensor(TAP_POS)
-    for bi in range(arch.depth):
+    for bi in range(0 if case in LITE_CASES else arch.depth):   # lite fixtures carry outputs only
         ref = torch.from_numpy(g[f"tap_block{bi}"])
         got = taps[f"block{bi}"][:, pos][:, :, pos]
         assert O.logit_rel_err(got, ref) < tol, f"block {bi}"
@@ -71,6 +75,11 @@ def test_oracle_vit_b_config1(golden):
 def test_oracle_vit_h_config2(golden):
     """Two frames of BASELINE.json configs[1] (ViT-H, 3 prompts)."""
     _check("vit_h_cfg2", golden)
+
+
+def test_oracle_vit_l_lite(golden):
+    """build_sam_vit_l, one frame x 3 prompts (outputs-only fixture)."""
+    _check("vit_l_lite", golden)
 
 
 def test_postprocess_matches_formula_edges():
