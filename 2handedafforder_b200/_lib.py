@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(PKG_DIR, "libb200sam.so")
 F32, BF16, F16 = 0, 1, 2
 VIT_B, VIT_L, VIT_H = 0, 1, 2
 
-# every symbol include/b200sam.h declares: (name, restype, argtypes)
+# every symbol include/b200sam.h and include/b200sam_debug.h declare: (name, restype, argtypes)
 _P, _I, _L, _F = C.c_void_p, C.c_int, C.c_int64, C.c_float
 SYMBOLS = [
     ("b200sam_create", _I, [C.POINTER(_P), _I, _I, _I, _I]),
@@ -44,6 +44,10 @@ SYMBOLS = [
     ("b200sam_op_gemm", _I, [_I, _I, _I, _P, _I, _P, _I, _I, _I, _I, _P, _P, _I, _I, _P, _P, _F, _P, _I, _I, _I, _P]),
     ("b200sam_op_layernorm", _I, [_P, _I, _I, _P, _P, _F, _P, _I, _P]),
     ("b200sam_op_attention", _I, [_P, _I, _I, _I, _I, _P, _P, _P, _P]),
+    # include/b200sam_debug.h (test / measurement hooks, not part of the drop-in surface)
+    ("b200sam_debug_set_variant", _I, [_I, _I]),
+    ("b200sam_debug_set_trace", _I, [_P]),
+    ("b200sam_debug_attention_bench", _I, [_P, _I, _I, _I, _I, _P, _P, _P, _I, C.POINTER(_F), _P]),
 ]
 
 _lib: Optional[C.CDLL] = None

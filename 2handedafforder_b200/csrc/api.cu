@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "../../include/b200sam.h"
+#include "../../include/b200sam_debug.h"
 #include "common.cuh"
 #include "decoder.cuh"
 #include "gemm_tc.cuh"
@@ -1268,5 +1269,60 @@ extern "C" int b200sam_op_attention(const void* qkv_bf16, int nbatch, int S, int
   cudaFree(relg);
   cudaFree(gbuf);
   if (err != cudaSuccess) fprintf(stderr, "b200sam_op_attention: %s\n", cudaGetErrorString(err));
+  return err == cudaSuccess ? 0 : B200SAM_ERR_CUDA;
+}
+
+// ------------------------------------------------------------------------------------------------ measurement hooks
+
+extern "C" int b200sam_debug_set_variant(int which, int value) {
+  if (which < 0 || which >= VK_COUNT) return B200SAM_ERR_INVALID;
+  set_kernel_variant(which, value);
+  return 0;
+}
+
+extern "C" int b200sam_debug_set_trace(void* dev_buffer) {
+  set_debug_trace_buffer(dev_buffer);
+  return 0;
+}
+
+extern "C" int b200sam_debug_attention_bench(const void* qkv_bf16, int nbatch, int S, int heads, int hd,
+                                             const float* rel_h, const float* rel_w, void* out_bf16, int iters,
+                                             float* host_ms_out, void* stream) {
+  if ((S != kWin && S != kGrid) || (hd != 64 && hd != 80) || heads <= 0 || nbatch <= 0 || iters <= 0 || !host_ms_out)
+    return B200SAM_ERR_INVALID;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || gemm_tc_init(dev) != cudaSuccess) return B200SAM_ERR_CUDA;
+  const int RP = S == kWin ? 32 : 128;
+  __nv_bfloat16 *tabs = nullptr, *relg = nullptr;
+  void* gbuf = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  cudaError_t err = cudaMalloc(reinterpret_cast<void**>(&tabs), (size_t)2 * RP * hd * 2);
+  if (err == cudaSuccess) err = launch_relpos_pack(rel_h, S, hd, tabs, s);
+  if (err == cudaSuccess) err = launch_relpos_pack(rel_w, S, hd, tabs + RP * hd, s);
+  if (err == cudaSuccess && S == kGrid) {
+    err = cudaMalloc(reinterpret_cast<void**>(&relg), 256 * 128 * 2);
+    if (err == cudaSuccess) err = cudaMalloc(&gbuf, (size_t)nbatch * kTokens * heads * 256 * 2 + 256);
+    if (err == cudaSuccess) err = launch_relpos_pack_g(rel_h, rel_w, hd, relg, s);
+  }
+  if (err == cudaSuccess) err = cudaEventCreate(&e0);
+  if (err == cudaSuccess) err = cudaEventCreate(&e1);
+  for (int it = -3; it < iters && err == cudaSuccess; ++it) {   // 3 warm-up launches
+    if (it == 0) err = cudaEventRecord(e0, s);
+    if (err == cudaSuccess)
+      err = launch_attention(reinterpret_cast<const __nv_bfloat16*>(qkv_bf16), nbatch, S, heads, hd, tabs,
+                             tabs + RP * hd, relg, gbuf, reinterpret_cast<__nv_bfloat16*>(out_bf16), s);
+  }
+  if (err == cudaSuccess) err = cudaEventRecord(e1, s);
+  if (err == cudaSuccess) err = cudaEventSynchronize(e1);
+  float ms = 0.f;
+  if (err == cudaSuccess) err = cudaEventElapsedTime(&ms, e0, e1);
+  *host_ms_out = ms / iters;
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
+  cudaFree(tabs);
+  cudaFree(relg);
+  cudaFree(gbuf);
+  if (err != cudaSuccess) fprintf(stderr, "b200sam_debug_attention_bench: %s\n", cudaGetErrorString(err));
   return err == cudaSuccess ? 0 : B200SAM_ERR_CUDA;
 }

@@ -11,6 +11,26 @@ namespace bsam {
 
 cudaError_t attention_init() { return cudaSuccess; }
 
+namespace {
+std::atomic<int> g_variant[VK_COUNT];   // zero-initialised: variant 0 everywhere, except the GEMM pair switch below
+std::atomic<bool> g_pair_set{false};
+std::atomic<void*> g_trace{nullptr};
+}  // namespace
+
+void* debug_trace_buffer() { return g_trace.load(); }
+void set_debug_trace_buffer(void* p) { g_trace.store(p); }
+
+int kernel_variant(int which) {
+  if (which < 0 || which >= VK_COUNT) return 0;
+  if (which == VK_GEMM_PAIR && !g_pair_set.load()) return 1;   // CTA-pair kernel is the default for the big GEMMs
+  return g_variant[which].load(std::memory_order_relaxed);
+}
+void set_kernel_variant(int which, int value) {
+  if (which < 0 || which >= VK_COUNT) return;
+  if (which == VK_GEMM_PAIR) g_pair_set.store(true);
+  g_variant[which].store(value, std::memory_order_relaxed);
+}
+
 cudaError_t launch_attention(const __nv_bfloat16* qkv, int nbatch, int S, int heads, int hd,
                              const __nv_bfloat16* relh, const __nv_bfloat16* relw, const __nv_bfloat16* relg,
                              void* gbuf, __nv_bfloat16* out, cudaStream_t s, bool window_token_out,

@@ -71,6 +71,19 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
 }
 
+// non-blocking probe of a phase (event-driven issue loops poll several barriers instead of blocking on one)
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n.reg .pred p;\n"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
@@ -83,6 +96,14 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* t
       ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c_inner),
       "r"(c_outer)
       : "memory");
+}
+
+// L2 prefetch of the box a later tma_load_2d will fetch (no shared memory, no barrier): turns the demand load of a
+// single-buffered operand into an L2 hit.
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* tm, int c_inner, int c_outer) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(reinterpret_cast<uint64_t>(tm)),
+               "r"(c_inner), "r"(c_outer)
+               : "memory");
 }
 
 // ---------------------------------------------------------------- tcgen05 / TMEM
@@ -98,6 +119,25 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// Same wait, with the destination registers of the outstanding tcgen05.ld tied to it as read-write operands: in a
+// software-pipelined loop (load chunk c+1, process chunk c, wait, process chunk c+1) nothing but this dependency keeps
+// the compiler from scheduling a use of the asynchronously written registers above the wait.
+__device__ __forceinline__ void tmem_wait_ld_dep(uint32_t (&r)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                 "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]),
+                 "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]),
+                 "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+               :
+               : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld_dep16(uint32_t (&r)[16]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                 "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+               :
+               : "memory");
+}
 
 // D[tmem] (+)= A[smem desc] * B[smem desc]; kind::f16 covers bf16/fp16 operands, kind::tf32 fp32 operands.
 template <bool kTf32>
@@ -363,6 +403,39 @@ __device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
   asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
   return r;
 }
+__device__ __forceinline__ void unpack2(uint64_t v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+// 2^x for two values at once WITHOUT the special-function unit: round-to-nearest range reduction with the 1.5 * 2^23
+// trick, a degree-3 minimax polynomial for 2^f on [-0.5, 0.5] (relative error 7.5e-5, far below the bf16 rounding of the
+// softmax probabilities it feeds) on packed fp32x2 FMAs, and the integer part added into the exponent field.  x <= 0 is
+// expected (softmax arguments after the maximum is subtracted); x is clamped at -125.  MUFU.EX2 costs 8 pipe cycles per
+// warp instruction on B200 (measured, scripts/ubench/mufu.cu) and is THE contended unit of the attention softmax:
+// evaluating a fraction of the exponentials here lets the FMA pipe share that load.
+__device__ __forceinline__ uint64_t ex2_poly2(uint64_t x2) {
+  float x0, x1;
+  unpack2(x2, x0, x1);
+  const uint64_t x = f32x2(fmaxf(x0, -125.f), fmaxf(x1, -125.f));
+  const uint64_t y = add2(x, f32x2(12582912.f, 12582912.f));
+  const uint64_t r = add2(y, f32x2(-12582912.f, -12582912.f));
+  const uint64_t f = fma2(r, f32x2(-1.f, -1.f), x);
+  uint64_t p = fma2(f, f32x2(0.05517153f, 0.05517153f), f32x2(0.24261111f, 0.24261111f));
+  p = fma2(p, f, f32x2(0.69326101f, 0.69326101f));
+  p = fma2(p, f, f32x2(0.99992807f, 0.99992807f));
+  float p0, p1, y0, y1;
+  unpack2(p, p0, p1);
+  unpack2(y, y0, y1);
+  return f32x2(__int_as_float(__float_as_int(p0) + (__float_as_int(y0) << 23)),
+               __int_as_float(__float_as_int(p1) + (__float_as_int(y1) << 23)));
+}
+__device__ __forceinline__ uint64_t ex2_mufu2(uint64_t x2) {
+  float x0, x1, e0, e1;
+  unpack2(x2, x0, x1);
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(x0));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(x1));
+  return f32x2(e0, e1);
+}
+
 // float4 += float4 as two packed adds (bit-identical to four scalar adds)
 __device__ __forceinline__ void add4(float4& x, const float4& y) {
   const uint64_t lo = add2(f32x2(x.x, x.y), f32x2(y.x, y.y)), hi = add2(f32x2(x.z, x.w), f32x2(y.z, y.w));
@@ -372,6 +445,22 @@ __device__ __forceinline__ void add4(float4& x, const float4& y) {
 // explicit shared-space 16-byte accesses (a generic pointer into dynamic smem compiles to generic LD/ST)
 __device__ __forceinline__ void sts128(uint32_t addr, float a, float b, float c, float d) {
   asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void sts128u(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 lds128u(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ float lds32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+  return v;
 }
 __device__ __forceinline__ float4 lds128(uint32_t addr) {
   float4 v;

@@ -27,6 +27,7 @@
 #include <mutex>
 
 #include "common.cuh"
+#include "kernels.cuh"
 
 namespace bsam {
 
@@ -749,8 +750,6 @@ __global__ void gemm_simt_debug_kernel(const void* A, int lda, const void* W, in
 std::atomic<PFN_cuTensorMapEncodeTiled_v12000> g_encode{nullptr};
 constexpr int kMaxDevices = 64;
 std::atomic<int> g_num_sms[kMaxDevices];
-bool g_pair_kernel = true;   // B200SAM_GEMM_PAIR=0 selects the single-CTA kernel (A/B measurements); read once
-std::once_flag g_env_once;
 
 cudaError_t make_tmap(CUtensorMap* tm, const void* ptr, bool f32, long rows, long cols, long ld, int box_rows) {
   const int esz = f32 ? 4 : 2;
@@ -827,9 +826,6 @@ cudaError_t gemm_tc_init(int device) {
     if (err != cudaSuccess) return err;
     g_num_sms[device].store(sms, std::memory_order_release);
   }
-  std::call_once(g_env_once, [] {
-    if (const char* v = getenv("B200SAM_GEMM_PAIR")) g_pair_kernel = atoi(v) != 0;
-  });
   return cudaSuccess;
 }
 
@@ -866,7 +862,7 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
   if (e.batch != 1 && (mode != GM_F16 || tf32 || dbg || e.batch < 1)) return cudaErrorInvalidValue;
   if ((mode == GM_LN || mode == GM_UPS1) && N != 256) return cudaErrorInvalidValue;
   if (mode == GM_UPS2 && N != 128) return cudaErrorInvalidValue;
-  if (!tf32 && !dbg && e.batch == 1 && M >= 1024 && N % 256 == 0 && g_pair_kernel) {
+  if (!tf32 && !dbg && e.batch == 1 && M >= 1024 && N % 256 == 0 && kernel_variant(VK_GEMM_PAIR) != 0) {
     switch (mode) {
       case GM_BIAS_BF16: return launch2<GM_BIAS_BF16>(A, lda, W, ldw, M, N, K, e, s);
       case GM_BIAS_GELU_BF16: return launch2<GM_BIAS_GELU_BF16>(A, lda, W, ldw, M, N, K, e, s);

@@ -44,6 +44,14 @@ cudaError_t launch_attention_global_tc(const __nv_bfloat16* qkv, int nbatch, int
 cudaError_t launch_attention_window_tc(const __nv_bfloat16* qkv, int nwin, int heads, int hd, const __nv_bfloat16* rel,
                                        __nv_bfloat16* out, cudaStream_t s, bool token_out = false);
 
+// Kernel variant switches for same-box A/B measurements (include/b200sam_debug.h); 0 = the shipped default.
+enum VariantKind : int { VK_ATTN_WINDOW = 0, VK_ATTN_GLOBAL = 1, VK_GEMM_PAIR = 2, VK_COUNT = 3 };
+int kernel_variant(int which);
+void set_kernel_variant(int which, int value);
+// device buffer of at least 16 * 16 * 10 uint64 that the tracing kernel variants fill (null: tracing variants refuse)
+void* debug_trace_buffer();
+void set_debug_trace_buffer(void* dev_ptr);
+
 // ---- decoder.cu
 struct DecSideWeights;   // device pointers of one mask decoder (api.cu owns it)
 struct DecoderWorkspace;

@@ -139,9 +139,6 @@ int b200sam_dense_pe(b200sam_t* h, float* out, void* stream);
 /* Number of kernels this library has launched on behalf of handle h since creation (bench.py's gpu_launches). */
 int64_t b200sam_launch_count(const b200sam_t* h);
 
-/* Debug switch: 1 = evaluate every GEMM with the SIMT debug kernel instead of tcgen05 (bisecting only). */
-int b200sam_set_debug_simt_gemm(b200sam_t* h, int on);
-
 /* Kernel classes of the per-launch profile. */
 enum b200sam_profile_class {
   B200SAM_PC_ELEMENTWISE = 0,     /* im2col of the patches, layout transposes */
@@ -169,12 +166,6 @@ enum b200sam_profile_class {
  * the launch count of every class into the two HOST arrays (length n_classes >= B200SAM_PC_COUNT) and resets. */
 int b200sam_profile_enable(b200sam_t* h, int on);
 int b200sam_profile_read(b200sam_t* h, float* host_ms, int64_t* host_count, int n_classes);
-
-/* Debug: make b200sam_encode stop after `nblocks` transformer blocks (-1 = run everything, the default) and
- * copy the fp32 residual stream (B,64,64,D) out; used by the per-block parity tests against the reference's
- * forward-hook taps. */
-int b200sam_debug_stop_after_block(b200sam_t* h, int nblocks);
-int b200sam_debug_read_tokens(b200sam_t* h, float* out, int B, void* stream);
 
 /* ---- operator-level entry points (used by the per-op parity tests; same kernels the path uses) ---- */
 

@@ -10,7 +10,7 @@ mkdir -p $O
 SEL='tests/test_gpu_path.py::test_path_tiny64 tests/test_gpu_path.py::test_path_tiny80 tests/test_gpu_wire.py::test_segment_bits_matches_segment_and_fused_metrics'
 # the plain run must pass first (a faulting program under a tool can take the GPU down)
 timeout 600 python -m pytest $SEL -x -q > $O/${TAG}_sanitize_plain.log 2>&1 || { echo "plain run failed"; tail -5 $O/${TAG}_sanitize_plain.log; exit 1; }
-timeout 1500 compute-sanitizer --tool $TOOL --launch-timeout 300 --error-exitcode 3 \
+timeout 700 compute-sanitizer --tool $TOOL --launch-timeout 300 --error-exitcode 3 \
     python -m pytest $SEL -x -q -p no:cacheprovider > $O/${TAG}_sanitize_${TOOL}.log 2>&1
 RC=$?
 { echo "# compute-sanitizer --tool $TOOL  rc=$RC  ($(date -u +%Y-%m-%dT%H:%MZ))  tests: $SEL";

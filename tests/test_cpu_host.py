@@ -11,13 +11,16 @@ import torch
 from oracle import synth
 from tests import gpu_util as G
 
-HEADER = os.path.join(G.ROOT, "include", "b200sam.h")
+HEADERS = [os.path.join(G.ROOT, "include", n) for n in ("b200sam.h", "b200sam_debug.h")]
 
 
 def _declared_functions():
-    src = open(HEADER).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(b200sam_[a-z0-9_]+)\s*\(", src)))
+    out = set()
+    for path in HEADERS:
+        src = open(path).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        out |= set(re.findall(r"\b(b200sam_[a-z0-9_]+)\s*\(", src))
+    return sorted(out)
 
 
 def test_library_exports_every_declared_symbol():
@@ -28,7 +31,7 @@ def test_library_exports_every_declared_symbol():
     declared = _declared_functions()
     assert len(declared) >= 15
     for name in declared:
-        assert hasattr(lib, name), f"{name} declared in include/b200sam.h but not exported"
+        assert hasattr(lib, name), f"{name} declared in include/*.h but not exported"
     bound = {n for n, _, _ in libmod.SYMBOLS}
     assert bound == set(declared), f"ctypes binding and header disagree: {bound ^ set(declared)}"
     libmod.load()
