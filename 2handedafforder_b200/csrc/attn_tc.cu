@@ -364,7 +364,8 @@ attn_window_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
   if (warp == 2) tmem_dealloc(tmem, 512);
 }
 
-// ------------------------------------------------------------------------------------------------ variant 1
+// ------------------------------------------------------------------------------------------------ shipped kernel
+// (the kernel above is the round-1 version, kept as variant 9 for same-box A/B)
 // Same data path and TMEM / shared-memory layout; what changes is the scheduling of the two M tiles ("units"):
 //  * one MMA-issuing warp per unit, each blocking on its own unit's barriers, so tile 0 of the NEXT problem starts as
 //    soon as its own TMEM columns are drained instead of queueing behind tile 1's P.V in program order (a single
@@ -917,30 +918,34 @@ cudaError_t launch_window(const __nv_bfloat16* qkv, int nwin, int heads, const _
   const int nprob = nwin * heads;
   const int grid = nprob < gemm_num_sms() ? nprob : gemm_num_sms();
   const float scale = 1.0f / sqrtf((float)HD);
-  switch (kernel_variant(VK_ATTN_WINDOW)) {
-    case 0:
+  // Variants (include/b200sam_debug.h): 0 = shipped kernel (attn_window_tc_kernel_v1), 4 = same with the L2 prefetch of
+  // the single-buffered operands, 2 / 3 = with the phase trace (3: without the global stores), 9 = the round-1 kernel,
+  // kept for same-box A/B (scripts/bench_attn.py).
+  const int variant = kernel_variant(VK_ATTN_WINDOW);
+  switch (variant) {
+    case 9:
       attn_window_tc_kernel<HD><<<grid, kThreadsWin, C::kSmem, s>>>(tm128, tm32, tmR128, tmR32, out, nwin, heads, scale,
                                                                   token_out ? 1 : 0);
       break;
-    case 4:     // variant 1 without the L2 prefetch of the single-buffered operands (A/B of that choice)
-    case 1: {
+    case 4:
+    case 0: {
       static std::atomic<uint64_t> attr1{0};
       e = smem_opt_in(attn_window_tc_kernel_v1<HD, false>, C::kSmem + Win1Extra<HD>::value, attr1);
       if (e != cudaSuccess) return e;
       attn_window_tc_kernel_v1<HD, false><<<grid, kThreadsWin1, C::kSmem + Win1Extra<HD>::value, s>>>(
           tm128, tm32, tmR128, tmR32, tmQa128, tmQa32, tmQb128, tmQb32, out, nwin, heads, scale,
-          (token_out ? 1 : 0) | (kernel_variant(VK_ATTN_WINDOW) == 1 ? 4 : 0), nullptr);
+          (token_out ? 1 : 0) | (variant == 4 ? 4 : 0), nullptr);
       break;
     }
     case 3:     // variant 2 without the global stores of O (measurement only: how much of the chain is the store?)
-    case 2: {   // variant 1 with the phase trace of CTA 0 (b200sam_debug_set_trace)
+    case 2: {   // the shipped kernel with the phase trace of CTA 0 (b200sam_debug_set_trace)
       static std::atomic<uint64_t> attr2{0};
       if (!debug_trace_buffer()) return cudaErrorInvalidValue;
       e = smem_opt_in(attn_window_tc_kernel_v1<HD, true>, C::kSmem + Win1Extra<HD>::value, attr2);
       if (e != cudaSuccess) return e;
       attn_window_tc_kernel_v1<HD, true><<<grid, kThreadsWin1, C::kSmem + Win1Extra<HD>::value, s>>>(
           tm128, tm32, tmR128, tmR32, tmQa128, tmQa32, tmQb128, tmQb32, out, nwin, heads, scale,
-          (token_out ? 1 : 0) | (kernel_variant(VK_ATTN_WINDOW) == 3 ? 2 : 0) | 4,
+          (token_out ? 1 : 0) | (variant == 3 ? 2 : 0),
           reinterpret_cast<unsigned long long*>(debug_trace_buffer()));
       break;
     }

@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Same-box A/B of the attention kernel variants (include/b200sam_debug.h): times the windowed (S = 14) and global
 (S = 64) attention op at the shapes of one ViT-H encoder block for a batch of 8 frames, every variant on the same
-inputs in one process, and checks each variant's output against variant 0.
+inputs in one process, and checks each variant's output against the first one listed (window variants: 0 = shipped,
+9 = round-1 kernel, 4 = shipped + L2 prefetch).
 Usage: python scripts/bench_attn.py [--win 0,1] [--glb 0,1] [--iters 20] [--batch 8]"""
 import argparse
 import ctypes as C
@@ -48,7 +49,7 @@ def run(lib, S, nb, heads, hd, variants, iters, which):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--win", default="0,1")
+    ap.add_argument("--win", default="9,0")
     ap.add_argument("--glb", default="0")
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--batch", type=int, default=8)
