@@ -36,6 +36,7 @@ constexpr int kStagesK = 2;   // K tiles in flight (20 KB each)
 constexpr int kStagesV = 3;   // V tiles in flight (32 KB each)
 constexpr int kThreadsG = 384;
 constexpr int kOColG = 256;           // O_t at kOColG + t * 128
+constexpr int kGlobalPolyDefault = 0; // variant number that runs the MUFU-only softmax (flipped once the A/B is in)
 
 template <int HD>
 struct GlbCfg {
@@ -69,12 +70,21 @@ __device__ __forceinline__ float ex2_fast(float x) {
   return y;
 }
 
-template <int HD>
+// POLY: fp32x2 softmax arithmetic with two key pairs of every five on the FMA-pipe exp2 polynomial (ex2_poly2)
+// instead of MUFU.EX2 - the special-function unit (8 pipe cycles per warp instruction) is the co-limiter of this kernel.
+// TRACE: CTA 0 records clock64() at the phase boundaries of the first 16 key tiles of its first item
+// ([warp][tile j][tag], include/b200sam_debug.h); the shipped instantiation has TRACE = false.
+template <int HD, bool POLY, bool TRACE>
 __global__ void __launch_bounds__(kThreadsG, 1)
 attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tm32,
                       const __grid_constant__ CUtensorMap tmG,
                       const __half* __restrict__ G, __nv_bfloat16* __restrict__ out, int nbatch, int heads,
-                      float scale) {
+                      float scale, unsigned long long* __restrict__ trace) {
+  auto mark = [&](int w, int item_it, int j, int tag) {
+    if constexpr (TRACE) {
+      if (blockIdx.x == 0 && item_it == 1 && j < 16) trace[(w * 16 + j) * 10 + tag] = clock64();
+    }
+  };
   using C = GlbCfg<HD>;
   constexpr bool kHasRem = C::kRem > 0;
   extern __shared__ uint8_t smem_raw[];
@@ -89,7 +99,8 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
   uint64_t* s_full = v_empty + kStagesV;          // [2]
   uint64_t* p_full = s_full + 2;                  // [2]
   uint64_t* o_full = p_full + 2;                  // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 2);
+  uint64_t* p_half = o_full + 2;                  // [2] POLY variant: P of the first 64 keys of the tile is stored
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_half + 2);
 
   const int warp = (int)uniform_u32(threadIdx.x >> 5), lane = threadIdx.x & 31;
   const int nitems = nbatch * heads * kQBlocks;
@@ -113,6 +124,7 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
     for (int i = 0; i < 2; ++i) {
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], 4);
+      mbar_init(&p_half[i], 4);
       mbar_init(&o_full[i], 1);
     }
     mbar_fence_init();
@@ -226,13 +238,26 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
         mbar_wait(&v_full[sv], ((kc + j) / kStagesV) & 1);
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
+          const uint32_t dO = tm + kOColG + t * 128, aP = tm + t * 128;
+          const uint32_t bM = sVm + sv * C::kMain;
+          if (lane == 0) mark(1, it, j, 4 * t);
+          if constexpr (POLY) {
+            // P.V in two steps (O does not alias the scores here): the first four key groups start as soon as their P
+            // is stored, while the softmax warps still work on the second half of the tile
+            mbar_wait(&p_half[t], (t ? np1 : np0) & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int ks = 0; ks < kBKeys / 32; ++ks) {
+              const uint64_t db = umma_desc(bM + ks * 2048, 1024, lbo, 2);
+              if (leader) umma_ts_bf16(dO, aP + ks * 8, db, kHasRem ? idO128 : idO64, (j | ks) != 0);
+            }
+          }
           mbar_wait(&p_full[t], (t ? np1 : np0) & 1);
           if (t) ++np1; else ++np0;
           tc_fence_after();
-          const uint32_t dO = tm + kOColG + t * 128, aP = tm + t * 128;
-          const uint32_t bM = sVm + sv * C::kMain;
+          if (lane == 0) mark(1, it, j, 4 * t + 1);
 #pragma unroll
-          for (int ks = 0; ks < kBKeys / 16; ++ks) {
+          for (int ks = POLY ? kBKeys / 32 : 0; ks < kBKeys / 16; ++ks) {
             const uint64_t db = umma_desc(bM + ks * 2048, 1024, lbo, 2);
             if (leader) umma_ts_bf16(dO, aP + ks * 8, db, kHasRem ? idO128 : idO64, (j | ks) != 0);
           }
@@ -249,6 +274,7 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
           } else {
             if (leader) umma_commit(&o_full[t]);
           }
+          if (lane == 0) mark(1, it, j, 4 * t + 2);
         }
       }
     }
@@ -286,11 +312,13 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
         mbar_wait(&s_full[t], ns & 1);
         ++ns;
         tc_fence_after();
+        if (lane == 0) mark(warp, it, j, 0);
         // ---- the whole 128-key score row of this thread in registers (one TMEM round trip per tile)
         uint32_t v[128];
 #pragma unroll
         for (int c = 0; c < 4; ++c) tmem_ld_32x32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32 * c]));
         tmem_wait_ld();
+        if (lane == 0) mark(warp, it, j, 1);
         // maximum of the raw scores -> upper bound of the biased tile maximum
         float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
@@ -334,34 +362,69 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
           }
         }
         const float c0 = bh0 - m_used, c1 = bh1 - m_used;
+        if (lane == 0) mark(warp, it, j, 2);
         // ---- p = 2^(s*cs + bh - m) (s holds q.k + w-bias), row sum (4 partial chains), P (bf16 pairs) into the
         // first 64 columns of S_t
-        float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
+        float sum;
+        if constexpr (POLY) {
+          uint64_t acc2 = f32x2(0.f, 0.f);
+          const uint64_t cs2 = f32x2(cs, cs);
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          const float cc = c < 2 ? c0 : c1;
-          uint32_t u[16];
+          for (int c = 0; c < 4; ++c) {
+            const float cc = c < 2 ? c0 : c1;
+            const uint64_t cc2 = f32x2(cc, cc);
+            uint32_t u[16];
 #pragma unroll
-          for (int i = 0; i < 32; i += 4) {
-            const float p0 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i]), cs, cc));
-            const float p1 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 1]), cs, cc));
-            const float p2 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 2]), cs, cc));
-            const float p3 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 3]), cs, cc));
-            sum0 += p0;
-            sum1 += p1;
-            sum2 += p2;
-            sum3 += p3;
-            u[i >> 1] = pack_bf16(p0, p1);
-            u[(i >> 1) + 1] = pack_bf16(p2, p3);
+            for (int i = 0; i < 32; i += 2) {
+              const uint64_t tt = fma2(f32x2(__uint_as_float(v[32 * c + i]), __uint_as_float(v[32 * c + i + 1])), cs2, cc2);
+              const int pi = ((32 * c + i) >> 1) % 5;
+              const uint64_t e = (pi == 1 || pi == 3) ? ex2_poly2(tt) : ex2_mufu2(tt);
+              acc2 = add2(acc2, e);
+              float e0, e1;
+              unpack2(e, e0, e1);
+              u[i >> 1] = pack_bf16(e0, e1);
+            }
+            tmem_st_32x32_16(tS + c * 16, u);
+            if (c == 1) {                        // P of keys 0..63 is complete
+              tmem_wait_st();
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&p_half[t]);
+            }
           }
-          tmem_st_32x32_16(tS + c * 16, u);
+          float a0, a1;
+          unpack2(acc2, a0, a1);
+          sum = a0 + a1;
+        } else {
+        float sum0 = 0.f, sum1 = 0.f, sum2 = 0.f, sum3 = 0.f;
+  #pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const float cc = c < 2 ? c0 : c1;
+            uint32_t u[16];
+  #pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+              const float p0 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i]), cs, cc));
+              const float p1 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 1]), cs, cc));
+              const float p2 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 2]), cs, cc));
+              const float p3 = ex2_fast(fmaf(__uint_as_float(v[32 * c + i + 3]), cs, cc));
+              sum0 += p0;
+              sum1 += p1;
+              sum2 += p2;
+              sum3 += p3;
+              u[i >> 1] = pack_bf16(p0, p1);
+              u[(i >> 1) + 1] = pack_bf16(p2, p3);
+            }
+            tmem_st_32x32_16(tS + c * 16, u);
+          }
+          sum = (sum0 + sum1) + (sum2 + sum3);
         }
-        const float sum = (sum0 + sum1) + (sum2 + sum3);
         l += sum;
+        if (lane == 0) mark(warp, it, j, 3);
         tmem_wait_st();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[t]);
+        if (lane == 0) mark(warp, it, j, 4);
         bh0 = nb0 * kLog2e;
         bh1 = nb1 * kLog2e;
       }
@@ -417,8 +480,14 @@ template <int HD>
 cudaError_t launch_global(const __nv_bfloat16* qkv, int nbatch, int heads, const __half* G, __nv_bfloat16* out,
                           cudaStream_t s) {
   using C = GlbCfg<HD>;
-  static std::atomic<uint64_t> attr{0};
-  cudaError_t e = smem_opt_in(attn_global_tc_kernel<HD>, C::kSmem, attr);
+  static std::atomic<uint64_t> attr{0}, attr_p{0};
+  static std::atomic<uint64_t> attr_t{0};
+  // 0 = shipped, 1 = the other softmax arithmetic (A/B), 2 = variant-1 arithmetic with the phase trace
+  const int variant = kernel_variant(VK_ATTN_GLOBAL);
+  if (variant < 0 || variant > 2 || (variant == 2 && !debug_trace_buffer())) return cudaErrorInvalidValue;
+  cudaError_t e = variant == 2 ? smem_opt_in(attn_global_tc_kernel<HD, true, true>, C::kSmem, attr_t)
+                  : variant == kGlobalPolyDefault ? smem_opt_in(attn_global_tc_kernel<HD, false, false>, C::kSmem, attr)
+                                                  : smem_opt_in(attn_global_tc_kernel<HD, true, false>, C::kSmem, attr_p);
   if (e != cudaSuccess) return e;
   const long rows = (long)nbatch * kGT, cols = 3L * heads * HD;
   CUtensorMap tm128, tm32;
@@ -435,8 +504,16 @@ cudaError_t launch_global(const __nv_bfloat16* qkv, int nbatch, int heads, const
   if (e != cudaSuccess) return e;
   const int nitems = nbatch * heads * kQBlocks;
   const int grid = nitems < gemm_num_sms() ? nitems : gemm_num_sms();
-  attn_global_tc_kernel<HD><<<grid, kThreadsG, C::kSmem, s>>>(tm128, tm32, tmG, G, out, nbatch, heads,
-                                                            1.0f / sqrtf((float)HD));
+  const float scale = 1.0f / sqrtf((float)HD);
+  if (variant == 2)
+    attn_global_tc_kernel<HD, true, true><<<grid, kThreadsG, C::kSmem, s>>>(
+        tm128, tm32, tmG, G, out, nbatch, heads, scale, reinterpret_cast<unsigned long long*>(debug_trace_buffer()));
+  else if (variant == kGlobalPolyDefault)
+    attn_global_tc_kernel<HD, false, false><<<grid, kThreadsG, C::kSmem, s>>>(tm128, tm32, tmG, G, out, nbatch, heads,
+                                                                            scale, nullptr);
+  else
+    attn_global_tc_kernel<HD, true, false><<<grid, kThreadsG, C::kSmem, s>>>(tm128, tm32, tmG, G, out, nbatch, heads,
+                                                                           scale, nullptr);
   return cudaGetLastError();
 }
 
