@@ -254,6 +254,12 @@ __device__ __forceinline__ void tmem_ld_32x32_16(uint32_t taddr, uint32_t (&r)[1
       : "r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ void tmem_ld_32x32_8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
 // registers -> TMEM: thread i of the warp writes lane (base_lane + i), 16 consecutive 32-bit columns.
 __device__ __forceinline__ void tmem_st_32x32_16(uint32_t taddr, const uint32_t (&r)[16]) {
   asm volatile(
