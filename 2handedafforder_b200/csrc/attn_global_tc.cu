@@ -35,9 +35,7 @@ constexpr int kQBlocks = kGT / 256;   // 16 work items per (frame, head)
 constexpr int kStagesK = 2;   // K tiles in flight (20 KB each)
 constexpr int kStagesV = 3;   // V tiles in flight (32 KB each)
 constexpr int kThreadsG = 384;
-constexpr int kThreadsG2 = 640;       // split softmax: warps 4..19
 constexpr int kOColG = 256;           // O_t at kOColG + t * 128
-constexpr int kGlobalPolyDefault = 0; // variant number that runs the MUFU-only softmax (flipped once the A/B is in)
 
 template <int HD>
 struct GlbCfg {
@@ -57,8 +55,6 @@ struct GlbCfg {
   static constexpr int oQm = 0;                           // 2 tiles
   static constexpr int oGw = 2 * kMain;                   // 2 tiles (fp16)
   static constexpr int oE = oGw + 2 * kMain;              // 64 rows (n % 64) x 64 (kx) fp16, K-major, swizzle-128: 8 KB
-  static constexpr int oXch = oE + kMain / 2;             // 4 KB: row-maximum / row-sum hand-over between the two
-                                                          // threads of a query row (split softmax), see below
   static constexpr int oKm = oE + kMain;                  // kStagesK tiles
   static constexpr int oVm = oKm + kStagesK * kMain;      // kStagesV tiles
   static constexpr int oVr = oVm + kStagesV * kMain;      // kStagesV second boxes
@@ -78,12 +74,8 @@ __device__ __forceinline__ float ex2_fast(float x) {
 // instead of MUFU.EX2 - the special-function unit (8 pipe cycles per warp instruction) is the co-limiter of this kernel.
 // TRACE: CTA 0 records clock64() at the phase boundaries of the first 16 key tiles of its first item
 // ([warp][tile j][tag], include/b200sam_debug.h); the shipped instantiation has TRACE = false.
-// SPLIT: two threads per query row (16 softmax warps, 640 threads): thread half h of a row owns keys [64h, 64h + 64) of
-// every 128-key tile, so load / maximum / exponentials per thread halve and the per-tile chain softmax -> P.V + S gets
-// close to the tensor time of a tile.  The halves agree on the tile's reference maximum through shared memory and a
-// 64-thread named barrier (one per pair of warps) every tile - the lazy rescale needs both to take the same decision.
-template <int HD, bool POLY, bool TRACE, bool SPLIT>
-__global__ void __launch_bounds__(SPLIT ? kThreadsG2 : kThreadsG, 1)
+template <int HD, bool POLY, bool TRACE>
+__global__ void __launch_bounds__(kThreadsG, 1)
 attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tm32,
                       const __grid_constant__ CUtensorMap tmG,
                       const __half* __restrict__ G, __nv_bfloat16* __restrict__ out, int nbatch, int heads,
@@ -131,7 +123,7 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&s_full[i], 1);
-      mbar_init(&p_full[i], SPLIT ? 8 : 4);
+      mbar_init(&p_full[i], 4);
       mbar_init(&p_half[i], 4);
       mbar_init(&o_full[i], 1);
     }
@@ -252,7 +244,7 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
           const uint32_t dO = tm + kOColG + t * 128, aP = tm + t * 128;
           const uint32_t bM = sVm + sv * C::kMain;
           if (lane == 0) mark(1, it, j, 4 * t);
-          if constexpr (POLY && !SPLIT) {
+          if constexpr (POLY) {
             // P.V in two steps (O does not alias the scores here): the first four key groups start as soon as their P
             // is stored, while the softmax warps still work on the second half of the tile
             mbar_wait(&p_half[t], (t ? np1 : np0) & 1);
@@ -268,7 +260,7 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
           tc_fence_after();
           if (lane == 0) mark(1, it, j, 4 * t + 1);
 #pragma unroll
-          for (int ks = (POLY && !SPLIT) ? kBKeys / 32 : 0; ks < kBKeys / 16; ++ks) {
+          for (int ks = POLY ? kBKeys / 32 : 0; ks < kBKeys / 16; ++ks) {
             const uint64_t db = umma_desc(bM + ks * 2048, 1024, lbo, 2);
             if (leader) umma_ts_bf16(dO, aP + ks * 8, db, kHasRem ? idO128 : idO64, (j | ks) != 0);
           }
@@ -291,163 +283,6 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
     }
   } else if (warp < 4) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-  } else if constexpr (SPLIT) {
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
-    const int t = (warp - 4) >> 3, h = ((warp - 4) >> 2) & 1, q = warp & 3;
-    const int rl = q * 32 + lane;                       // row inside the M tile
-    const uint32_t tl = tmem + (uint32_t(q * 32) << 16);
-    const uint32_t tS = tl + t * 128, tO = tl + kOColG + t * 128;
-    constexpr float kLog2e = 1.4426950408889634f;
-    const float cs = scale * kLog2e;
-    const uint64_t cs2 = f32x2(cs, cs);
-    const long ldg = (long)heads * 256, ldo = (long)heads * HD;
-    // hand-over slots: [parity][tile][half][row]; the pair (warp, warp +- 4) meets at named barrier 1 + t*4 + q
-    float* xch = reinterpret_cast<float*>(smem + C::oXch);
-    const int bar_id = 1 + t * 4 + q;
-    auto pair_sync = [&]() { asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory"); };
-    uint32_t ns = 0, nx = 0;                             // score tiles consumed; hand-overs done (slot parity)
-    int it = 0;
-    for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
-      const int ir = nitems - 1 - item;
-      const int bhh = ir / kQBlocks, qb = ir - bhh * kQBlocks;
-      const int b = bhh / heads, head = bhh - b * heads;
-      const int qrow = qb * 256 + t * 128 + rl;          // token index inside the frame
-      const int qy = qrow >> 6;
-      const __half* gh = G + ((long)b * kGT + qrow) * ldg + head * 256 + qy + 63 - h;   // h-bias of key row 2j + h: gh[-2j]
-      float bh = __half2float(__ldg(gh)) * kLog2e;
-      float m_used = -INFINITY, l = 0.f;
-#pragma unroll 1
-      for (int j = 0; j < kNIter; ++j) {
-        const float nb = j + 1 < kNIter ? __half2float(__ldg(gh - 2 * (j + 1))) : 0.f;
-        mbar_wait(&s_full[t], ns & 1);
-        ++ns;
-        tc_fence_after();
-        if (lane == 0) mark(warp, it, j, 0);
-        uint32_t v[64];
-        tmem_ld_32x32(tS + h * 64, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-        tmem_ld_32x32(tS + h * 64 + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
-        tmem_wait_ld_dep(*reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-        tmem_wait_ld_dep(*reinterpret_cast<uint32_t(*)[32]>(&v[32]));
-        if (lane == 0) mark(warp, it, j, 1);
-        float mx0 = -INFINITY, mx1 = -INFINITY;
-#pragma unroll
-        for (int i = 0; i < 64; i += 4) {
-          mx0 = fmaxf(mx0, fmaxf(__uint_as_float(v[i]), __uint_as_float(v[i + 1])));
-          mx1 = fmaxf(mx1, fmaxf(__uint_as_float(v[i + 2]), __uint_as_float(v[i + 3])));
-        }
-        // the tile's reference maximum must be the same for both halves of the row: exchange
-        const float Mh = fmaxf(mx0, mx1) * cs + bh;
-        float* slot = xch + ((nx & 1) * 2 + t) * 256 + rl;
-        ++nx;
-        slot[h * 128] = Mh;
-        pair_sync();
-        const float Mt = fmaxf(Mh, slot[(h ^ 1) * 128]);
-        const bool grow = Mt > m_used + 8.f;
-        if (__any_sync(0xffffffffu, grow)) {
-          const float m_new = grow ? Mt : m_used;
-          const float f = ex2_fast(m_used - m_new);     // 0 on the first tile (m_used = -inf), 1 for unchanged rows
-          l *= f;
-          m_used = m_new;
-          if (j > 0) {
-            // each half rescales its share of the O columns: [32h, 32h + 32) and, head dim 80, 8 of the last 16
-            uint32_t o[32];
-            tmem_ld_32x32(tO + h * 32, o);
-            tmem_wait_ld_dep(o);
-            uint32_t a[16], bq[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              a[i] = __float_as_uint(__uint_as_float(o[i]) * f);
-              bq[i] = __float_as_uint(__uint_as_float(o[16 + i]) * f);
-            }
-            tmem_st_32x32_16(tO + h * 32, a);
-            tmem_st_32x32_16(tO + h * 32 + 16, bq);
-            if (kHasRem) {
-              uint32_t w8[8];
-              tmem_ld_32x32_8(tO + 128 - C::kRem + h * 8, w8);
-              tmem_wait_ld();
-#pragma unroll
-              for (int i = 0; i < 8; ++i) w8[i] = __float_as_uint(__uint_as_float(w8[i]) * f);
-              tmem_st_32x32_8(tO + 128 - C::kRem + h * 8, w8);
-            }
-          }
-        }
-        if (lane == 0) mark(warp, it, j, 2);
-        const float cc = bh - m_used;
-        const uint64_t cc2 = f32x2(cc, cc);
-        uint64_t acc2 = f32x2(0.f, 0.f);
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t u[16];
-#pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            const uint64_t tt = fma2(f32x2(__uint_as_float(v[32 * c + i]), __uint_as_float(v[32 * c + i + 1])), cs2, cc2);
-            const int pi = ((32 * c + i) >> 1) % 5;
-            const uint64_t e = (pi == 1 || pi == 3) ? ex2_poly2(tt) : ex2_mufu2(tt);
-            acc2 = add2(acc2, e);
-            float e0, e1;
-            unpack2(e, e0, e1);
-            u[i >> 1] = pack_bf16(e0, e1);
-          }
-          tmem_st_32x32_16(tS + h * 32 + c * 16, u);   // P of keys [64h, 64h + 64): columns [32h, 32h + 32)
-        }
-        float a0, a1;
-        unpack2(acc2, a0, a1);
-        l += a0 + a1;
-        if (lane == 0) mark(warp, it, j, 3);
-        tmem_wait_st();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&p_full[t]);
-        if (lane == 0) mark(warp, it, j, 4);
-        bh = nb * kLog2e;
-      }
-      // ---- epilogue: O / (l of both halves) -> bf16; half h stores head columns [HD/2 * h, HD/2 * (h + 1))
-      float* slot = xch + ((nx & 1) * 2 + t) * 256 + rl;
-      ++nx;
-      slot[h * 128] = l;
-      pair_sync();
-      const float inv = 1.f / (l + slot[(h ^ 1) * 128]);
-      mbar_wait(&o_full[t], it & 1);
-      tc_fence_after();
-      __nv_bfloat16* go = out + ((long)b * kGT + qrow) * ldo + head * HD + h * (HD / 2);
-      auto st8 = [&](const uint32_t* w, __nv_bfloat16* dst) {   // 8 fp32 accumulators -> 8 bf16 (16 bytes)
-        uint4 x;
-        x.x = pack_bf16(__uint_as_float(w[0]) * inv, __uint_as_float(w[1]) * inv);
-        x.y = pack_bf16(__uint_as_float(w[2]) * inv, __uint_as_float(w[3]) * inv);
-        x.z = pack_bf16(__uint_as_float(w[4]) * inv, __uint_as_float(w[5]) * inv);
-        x.w = pack_bf16(__uint_as_float(w[6]) * inv, __uint_as_float(w[7]) * inv);
-        *reinterpret_cast<uint4*>(dst) = x;
-      };
-      {
-        uint32_t o[32];
-        tmem_ld_32x32(tO + h * 32, o);     // head dim 64: exactly this half's columns [32h, 32h + 32)
-        tmem_wait_ld_dep(o);
-        if (!kHasRem) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) st8(&o[8 * i], go + 8 * i);
-        } else {
-          // head dim 80: half 0 owns head columns 0..39 = O columns 0..39, half 1 owns 40..79 = O columns 40..63 and
-          // 112..127 (the second V box lands head columns 64..79 there)
-          uint32_t w8[8], w16[16];
-          if (h == 0) {
-            tmem_ld_32x32_8(tO + 32, w8);
-            tmem_wait_ld();
-#pragma unroll
-            for (int i = 0; i < 4; ++i) st8(&o[8 * i], go + 8 * i);
-            st8(w8, go + 32);
-          } else {
-            tmem_ld_32x32_16(tO + 128 - C::kRem, w16);
-            tmem_wait_ld_dep16(w16);
-            // o holds O columns 32..63: head columns 40..63 are o[8..31]
-#pragma unroll
-            for (int i = 0; i < 3; ++i) st8(&o[8 + 8 * i], go + 8 * i);
-            st8(&w16[0], go + 24);
-            st8(&w16[8], go + 32);
-          }
-        }
-      }
-      tc_fence_before();   // orders these TMEM reads before the next item's p_full arrive -> PV(0) overwrite
-    }
   } else {
     asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     const int t = (warp - 4) >> 2, q = warp & 3;
@@ -648,18 +483,13 @@ template <int HD>
 cudaError_t launch_global(const __nv_bfloat16* qkv, int nbatch, int heads, const __half* G, __nv_bfloat16* out,
                           cudaStream_t s) {
   using C = GlbCfg<HD>;
-  static std::atomic<uint64_t> attr{0}, attr_p{0};
-  static std::atomic<uint64_t> attr_t{0};
-  // 0 = shipped, 1 = the other softmax arithmetic (A/B), 2 = variant-1 arithmetic with the phase trace
+  // 0 = shipped (fp32x2 + polynomial-exp2 softmax, P.V in two steps), 1 = the round-1 arithmetic (MUFU.EX2 only, A/B),
+  // 2 = shipped kernel with the phase trace (include/b200sam_debug.h)
   const int variant = kernel_variant(VK_ATTN_GLOBAL);
   if (variant < 0 || variant > 2 || (variant == 2 && !debug_trace_buffer())) return cudaErrorInvalidValue;
-  cudaError_t e = variant == 2 ? smem_opt_in(attn_global_tc_kernel<HD, true, true>, C::kSmem, attr_t)
-                  : variant == kGlobalPolyDefault ? smem_opt_in(attn_global_tc_kernel<HD, false, false>, C::kSmem, attr)
-                                                  : smem_opt_in(attn_global_tc_kernel<HD, true, false>, C::kSmem, attr_p);
-  if (e != cudaSuccess) return e;
   const long rows = (long)nbatch * kGT, cols = 3L * heads * HD;
   CUtensorMap tm128, tm32;
-  e = make_tmap_2d(&tm128, qkv, 2, rows, cols, cols, 64, 128, 128);
+  cudaError_t e = make_tmap_2d(&tm128, qkv, 2, rows, cols, cols, 64, 128, 128);
   if (e != cudaSuccess) return e;
   if (C::kRem) {
     e = make_tmap_2d(&tm32, qkv, 2, rows, cols, cols, 16, 128, 32);
@@ -673,15 +503,19 @@ cudaError_t launch_global(const __nv_bfloat16* qkv, int nbatch, int heads, const
   const int nitems = nbatch * heads * kQBlocks;
   const int grid = nitems < gemm_num_sms() ? nitems : gemm_num_sms();
   const float scale = 1.0f / sqrtf((float)HD);
-  if (variant == 2)
-    attn_global_tc_kernel<HD, true, true><<<grid, kThreadsG, C::kSmem, s>>>(
-        tm128, tm32, tmG, G, out, nbatch, heads, scale, reinterpret_cast<unsigned long long*>(debug_trace_buffer()));
-  else if (variant == kGlobalPolyDefault)
-    attn_global_tc_kernel<HD, false, false><<<grid, kThreadsG, C::kSmem, s>>>(tm128, tm32, tmG, G, out, nbatch, heads,
-                                                                            scale, nullptr);
-  else
-    attn_global_tc_kernel<HD, true, false><<<grid, kThreadsG, C::kSmem, s>>>(tm128, tm32, tmG, G, out, nbatch, heads,
-                                                                           scale, nullptr);
+  unsigned long long* tr = reinterpret_cast<unsigned long long*>(debug_trace_buffer());
+#define BSAM_LAUNCH_GLOBAL(POLY, TRACE, TRACEPTR)                                                                  \
+  do {                                                                                                             \
+    static std::atomic<uint64_t> attr{0};                                                                          \
+    e = smem_opt_in(attn_global_tc_kernel<HD, POLY, TRACE>, C::kSmem, attr);                                       \
+    if (e != cudaSuccess) return e;                                                                                \
+    attn_global_tc_kernel<HD, POLY, TRACE><<<grid, kThreadsG, C::kSmem, s>>>(tm128, tm32, tmG, G, out, nbatch,     \
+                                                                             heads, scale, TRACEPTR);              \
+  } while (0)
+  if (variant == 2) BSAM_LAUNCH_GLOBAL(true, true, tr);
+  else if (variant == 1) BSAM_LAUNCH_GLOBAL(false, false, nullptr);
+  else BSAM_LAUNCH_GLOBAL(true, false, nullptr);
+#undef BSAM_LAUNCH_GLOBAL
   return cudaGetLastError();
 }
 

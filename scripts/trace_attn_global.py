@@ -19,9 +19,11 @@ qkv = (torch.randn((rows, 3 * heads * hd), generator=g) * 1.5).to(torch.bfloat16
 rel_h = (torch.randn((2 * S - 1, hd), generator=g) * 0.3).cuda()
 rel_w = (torch.randn((2 * S - 1, hd), generator=g) * 0.3).cuda()
 out = torch.zeros((rows, heads * hd), dtype=torch.bfloat16, device="cuda")
-trace = torch.zeros((16, 16, 10), dtype=torch.int64, device="cuda")
+trace = torch.zeros((20, 16, 10), dtype=torch.int64, device="cuda")
 assert lib.b200sam_debug_set_trace(C.c_void_p(trace.data_ptr())) == 0
-assert lib.b200sam_debug_set_variant(1, 2) == 0
+import sys as _s
+V = int(_s.argv[1]) if len(_s.argv) > 1 else 2
+assert lib.b200sam_debug_set_variant(1, V) == 0
 ms = C.c_float()
 rc = lib.b200sam_debug_attention_bench(C.c_void_p(qkv.data_ptr()), nb, S, heads, hd, C.c_void_p(rel_h.data_ptr()),
                                        C.c_void_p(rel_w.data_ptr()), C.c_void_p(out.data_ptr()), 1, C.byref(ms),
