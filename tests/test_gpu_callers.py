@@ -189,3 +189,73 @@ def test_config4_chain_hidden_states_to_masks(sam):
                 assert O.mask_iou(got[n], ref[i][f"masks_{side}"][n]) >= 0.99
         lo, hi = offsets[i], offsets[i + 1]
         assert torch.equal(out["taxonomy"][lo:hi].cpu().argmax(-1), ref[i]["taxonomy"].argmax(-1))
+
+
+def test_config4_real_dimensions_lisa_evaluate_loop():
+    """BASELINE configs[3] at the dimensions of the real model: LLaVA-7B hidden size 4096, bf16 hidden states and
+    text_hidden_fcs weights, ViT-H visual_model, two images with 3 and 2 [SEG] tokens.  The per-image loop of
+    LISAForCausalLM.evaluate (LISA.py:457-532) is executed statement by statement around the drop-in's submodules
+    (image_encoder B=1 per image, prompt_encoder, mask_decoder_left / _right, postprocess_masks) on hidden states
+    projected by b200sam_seg_project, and compared with the same loop restated by the oracle chain
+    (aux_oracle.seg_project in fp32 numpy on the bf16-rounded inputs -> sam_oracle.segment, fp32).
+    Constructing LISAForCausalLM itself is not possible on the GPU box (the reference tree does not travel, and
+    evaluate() hard-codes .cuda(), LISA.py:461,478): this is SURVEY 8c's fallback harness."""
+    from oracle import sam_oracle as O
+    from oracle import synth
+    sam, arch, sd = G.build_sam_from_synth("vit_h", max_batch=1, max_prompts=3)
+    hdim, T, seg_idx = 4096, 40, 32003
+    fcs = _fcs(hdim, 21).to(torch.bfloat16)
+    g = torch.Generator().manual_seed(100)                     # SURVEY 8d: config 4 seed
+    ids = torch.randint(0, 32000, (2, T), generator=g)
+    ids[0, [5, 17, 33]] = seg_idx
+    ids[1, [8, 30]] = seg_idx
+    hidden = torch.randn((2, 255 + T - 1, hdim), generator=g).to(torch.bfloat16)
+    frames = synth.make_frames(0, 2).to(torch.bfloat16)
+    resize_list, original_size_list = [(576, 1024)] * 2, [(1080, 1920)] * 2
+    # ---- LISA.evaluate, drop-in side (LISA.py:457-485 -> seg_project; :487-532 verbatim below)
+    pred_embeddings, offsets = sam.seg_project(hidden.cuda(), ids.cuda(), seg_idx, fcs.cuda())
+    assert offsets == [0, 3, 5]
+    image_embeddings = torch.cat([sam.image_encoder(frames[i:i + 1].cuda()) for i in range(2)], 0)   # LISA.py:157-168
+    pred_left, pred_right, taxes = [], [], []
+    with torch.no_grad():
+        for i in range(len(pred_embeddings)):
+            sparse_embeddings, dense_embeddings = sam.prompt_encoder(
+                points=None, boxes=None, masks=None, text_embeds=pred_embeddings[i].unsqueeze(1))
+            sparse_embeddings = sparse_embeddings.to(pred_embeddings[i].dtype)
+            low_res_masks_left, iou_left, taxonomy = sam.mask_decoder_left(
+                image_embeddings=image_embeddings[i].unsqueeze(0), image_pe=sam.prompt_encoder.get_dense_pe(),
+                sparse_prompt_embeddings=sparse_embeddings, dense_prompt_embeddings=dense_embeddings,
+                multimask_output=False)
+            pred_mask_left = sam.postprocess_masks(low_res_masks_left, input_size=resize_list[i],
+                                                   original_size=original_size_list[i])
+            low_res_masks_right, iou_right = sam.mask_decoder_right(
+                image_embeddings=image_embeddings[i].unsqueeze(0), image_pe=sam.prompt_encoder.get_dense_pe(),
+                sparse_prompt_embeddings=sparse_embeddings, dense_prompt_embeddings=dense_embeddings,
+                multimask_output=False)
+            pred_mask_right = sam.postprocess_masks(low_res_masks_right, input_size=resize_list[i],
+                                                    original_size=original_size_list[i])
+            pred_left.append(pred_mask_left[:, 0])
+            pred_right.append(pred_mask_right[:, 0])
+            taxes.append(taxonomy)
+    torch.cuda.synchronize()
+    # ---- oracle side: the same chain in fp32 on the same (bf16-rounded) inputs
+    w = [t.detach().float().cpu().numpy() for t in (fcs[0][0].weight, fcs[0][0].bias, fcs[0][2].weight, fcs[0][2].bias)]
+    ref_embs, ref_off = A.seg_project(hidden.float().numpy(), ids.numpy(), seg_idx, *w)
+    assert list(ref_off) == offsets
+    ref = O.segment(sd, arch, frames.float(), [torch.from_numpy(e) for e in ref_embs], resize_list,
+                    original_size_list, O.FP32)
+    for i in range(2):
+        assert pred_left[i].dtype == torch.float32 and pred_left[i].shape == (offsets[i + 1] - offsets[i], 1080, 1920)
+        for name, got in (("left", pred_left[i]), ("right", pred_right[i])):
+            for n in range(got.shape[0]):
+                err = O.logit_rel_err(got[n].cpu(), ref[i][f"masks_{name}"][n])
+                iou = O.mask_iou(got[n].cpu(), ref[i][f"masks_{name}"][n])
+                assert err <= 2e-2 and iou >= 0.99, (i, name, n, err, iou)
+        assert torch.equal(taxes[i].cpu().argmax(-1), ref[i]["taxonomy"].argmax(-1))
+    # the fused fast path agrees with the module-by-module loop (it keeps the image embedding in fp32 inside the handle
+    # instead of handing a bf16 tensor from image_encoder to the decoders, so the bits differ at bf16 level)
+    out = sam.segment(frames[:1].cuda(), [pred_embeddings[0]], resize_list[:1], original_size_list[:1],
+                      threshold=0.0, return_logits=True)
+    for n in range(3):
+        assert O.logit_rel_err(out["logits_left"][0][n].cpu(), pred_left[0][n].cpu()) <= 1e-2
+        assert O.mask_iou(out["logits_right"][0][n].cpu(), pred_right[0][n].cpu()) >= 0.99
