@@ -564,6 +564,11 @@ extern "C" void b200sam_destroy(b200sam_t* h) {
     free_list(h->owned);
     free_list(h->derived_enc);
     free_list(h->derived_dec);
+    for (auto& kv : h->enc_graphs)
+      if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    if (h->graph_stream) cudaStreamDestroy(h->graph_stream);
+    if (h->ev_g0) cudaEventDestroy(h->ev_g0);
+    if (h->ev_g1) cudaEventDestroy(h->ev_g1);
     if (h->ovf_host) cudaFreeHost(const_cast<int*>(h->ovf_host));
     if (h->side_stream) cudaStreamDestroy(h->side_stream);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
@@ -698,6 +703,9 @@ extern "C" int b200sam_finalize_weights(b200sam_t* h) {
     h->dirty_dec = false;
   }
   CU(cudaDeviceSynchronize());
+  for (auto& kv : h->enc_graphs)       // captured launches hold pointers into the buffers rebuilt above
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  h->enc_graphs.clear();
   h->prof_on = prof_was;
   h->finalized = true;
   h->have_emb = false;
@@ -706,23 +714,15 @@ extern "C" int b200sam_finalize_weights(b200sam_t* h) {
 
 // ------------------------------------------------------------------------------------------------ encode
 
-extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype, int B, void* emb_out, int emb_dtype,
-                              void* stream) {
-  if (int r = check_ready(h)) return r;
-  if (B < 0 || B > h->max_batch) return fail(h, B200SAM_ERR_INVALID, "batch %d exceeds max_batch %d", B, h->max_batch);
-  if (B == 0) return 0;
-  if (!frames) return fail(h, B200SAM_ERR_INVALID, "frames is NULL");
-  if (frames_dtype < 0 || frames_dtype > 2 || (emb_out && (emb_dtype < 0 || emb_dtype > 2)))
-    return fail(h, B200SAM_ERR_INVALID, "unsupported dtype");
-  DeviceGuard g(h->device);
-  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  h->prof_stream = s;
+namespace {
+
+// Everything of ImageEncoderViT.forward that reads and writes only the handle's own buffers: patch GEMM, the
+// transformer blocks, the neck.  No caller pointer appears in any launch, which is what makes the sequence
+// capturable into a CUDA graph (b200sam_encode).  Returns 1 when a debug stop cut the sequence short.
+int encode_body(b200sam_t* h, int B, cudaStream_t s) {
   const int D = h->dim, heads = h->heads, hd = h->hd;
   const long T = (long)B * kTokens;
-
-  // PatchEmbed + pos_embed (image_encoder.py:111-113): im2col index map, GEMM, bias + pos_embed in the epilogue
-  h->pc = B200SAM_PC_ELEMENTWISE;
-  KL(launch_im2col_patch(frames, frames_dtype, B, h->hid, s));
+  // PatchEmbed GEMM (bias + pos_embed in the epilogue) on the im2col rows b200sam_encode left in `hid`
   {
     GemmEpi e;
     e.bias = h->patch_b;
@@ -790,7 +790,7 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
       if (int r = run_gemm(h, false, GM_F32, h->hid, 4 * D, b.lin2_w, 4 * D, T, D, 4 * D, e, s)) return r;
     }
   }
-  if (nblocks != h->depth) return 0;   // debug: residual stream after `nblocks` blocks is left in X
+  if (nblocks != h->depth) return 1;   // debug: residual stream after `nblocks` blocks is left in X
   // neck (image_encoder.py:92-108): conv1x1 -> LayerNorm2d -> conv3x3 -> LayerNorm2d, token-major
   h->pc = B200SAM_PC_NECK;
   KL(launch_cast_f32_bf16(h->X, h->ln_plain, T * D, s));
@@ -813,6 +813,85 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
     e.ln_b = h->neck3b;
     e.ln_eps = 1e-6f;
     if (int r = run_gemm(h, false, GM_LN, h->hid, 9 * 256, h->neck2_w, 9 * 256, T, 256, 9 * 256, e, s)) return r;
+  }
+  return 0;
+}
+
+// The ~300 launches of encode_body replayed as one CUDA graph per batch size: at B = 1 - the
+// reference's real call pattern, LISA.py:160-166 - the kernels are short enough for launch overhead and the two
+// cuTensorMapEncodeTiled calls per GEMM to show.  The first call of a batch size runs eagerly (it also sets the
+// kernels' shared-memory attributes), the second is captured on the caller's stream, later ones replay.  Profiling,
+// debug switches and a caller who is capturing the stream himself use the plain launch sequence.
+int encode_body_graphed(b200sam_t* h, int B, cudaStream_t s) {
+  const int sig = kernel_variant(VK_ATTN_WINDOW) * 10000 + kernel_variant(VK_ATTN_GLOBAL) * 100 + kernel_variant(VK_GEMM_PAIR);
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  const bool plain = h->prof_on || h->debug_simt || h->debug_stop_block >= 0 || !h->use_graphs ||
+                     cudaStreamIsCapturing(s, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone;
+  if (plain) return encode_body(h, B, s);
+  EncGraph& g = h->enc_graphs[B];
+  if (g.exec && g.sig != sig) {
+    cudaGraphExecDestroy(g.exec);
+    g = EncGraph();
+  }
+  if (!g.exec && g.calls++ == 0) return encode_body(h, B, s);
+  // The caller's stream may be the legacy default stream (PyTorch's default), which can be neither captured nor
+  // graph-launched into without serialising the device: capture and replay happen on a stream of the handle, ordered
+  // behind / in front of the caller's stream by two events.
+  if (!h->graph_stream) {
+    CU(cudaStreamCreateWithFlags(&h->graph_stream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&h->ev_g0, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&h->ev_g1, cudaEventDisableTiming));
+  }
+  cudaStream_t gs = h->graph_stream;
+  CU(cudaEventRecord(h->ev_g0, s));
+  CU(cudaStreamWaitEvent(gs, h->ev_g0, 0));
+  if (!g.exec) {
+    const int64_t before = h->launches;
+    CU(cudaStreamBeginCapture(gs, cudaStreamCaptureModeThreadLocal));
+    const int r = encode_body(h, B, gs);
+    cudaGraph_t graph = nullptr;
+    cudaError_t ce = cudaStreamEndCapture(gs, &graph);
+    if (r == 0 && ce == cudaSuccess && graph) ce = cudaGraphInstantiate(&g.exec, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    const int64_t captured = h->launches - before;
+    h->launches = before;
+    if (r != 0 || ce != cudaSuccess || !g.exec) {
+      g.exec = nullptr;
+      cudaGetLastError();
+      h->use_graphs = false;          // same kernels, launched one by one from now on
+      return r < 0 ? r : encode_body(h, B, s);
+    }
+    g.sig = sig;
+    g.n_launches = captured;
+  }
+  CU(cudaGraphLaunch(g.exec, gs));
+  h->launches += g.n_launches;
+  CU(cudaEventRecord(h->ev_g1, gs));
+  CU(cudaStreamWaitEvent(s, h->ev_g1, 0));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype, int B, void* emb_out, int emb_dtype,
+                              void* stream) {
+  if (int r = check_ready(h)) return r;
+  if (B < 0 || B > h->max_batch) return fail(h, B200SAM_ERR_INVALID, "batch %d exceeds max_batch %d", B, h->max_batch);
+  if (B == 0) return 0;
+  if (!frames) return fail(h, B200SAM_ERR_INVALID, "frames is NULL");
+  if (frames_dtype < 0 || frames_dtype > 2 || (emb_out && (emb_dtype < 0 || emb_dtype > 2)))
+    return fail(h, B200SAM_ERR_INVALID, "unsupported dtype");
+  DeviceGuard g(h->device);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  h->prof_stream = s;
+
+  // PatchEmbed (image_encoder.py:111-113): the im2col index map reads the caller's frames
+  h->pc = B200SAM_PC_ELEMENTWISE;
+  KL(launch_im2col_patch(frames, frames_dtype, B, h->hid, s));
+  {
+    const int r = encode_body_graphed(h, B, s);
+    if (r < 0) return r;
+    if (r > 0) return 0;               // debug stop: no embedding
   }
   h->pc = B200SAM_PC_ELEMENTWISE;
   if (emb_out) KL(launch_tokens_to_nchw(h->emb_tok, B, emb_out, emb_dtype, s));

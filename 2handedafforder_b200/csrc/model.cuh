@@ -79,6 +79,14 @@ struct DecWorkspace {
   float* hyper = nullptr;            // (P, 32) mask-0 hypernetwork output
 };
 
+// encode_body captured for one batch size (api.cu)
+struct EncGraph {
+  cudaGraphExec_t exec = nullptr;
+  int sig = 0;                       // kernel-variant signature the capture was made with
+  int calls = 0;
+  int64_t n_launches = 0;            // kernels inside the graph (b200sam_launch_count keeps counting them)
+};
+
 }  // namespace bsam
 
 struct b200sam {
@@ -97,6 +105,10 @@ struct b200sam {
   std::vector<int> prof_cls;
   int debug_stop_block = -1;         // >= 0: encode() stops after that many blocks (bisecting only)
   bool finalized = false;
+  bool use_graphs = true;
+  std::map<int, bsam::EncGraph> enc_graphs;   // by batch size
+  cudaStream_t graph_stream = nullptr;        // where the encoder graphs are captured and replayed
+  cudaEvent_t ev_g0 = nullptr, ev_g1 = nullptr;
   bool have_emb = false;
   int emb_batch = 0;
 
