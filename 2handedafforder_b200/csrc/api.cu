@@ -449,6 +449,10 @@ int alloc_workspace(b200sam_t* h) {
   }
   const size_t hid_cols = 4 * D > 9 * 256 ? 4 * D : 9 * 256;
   CU(dalloc(h, &h->hid, B * kTokens * hid_cols));
+  // neck.1 output in the zero-ringed (B, 66, 66, 256) layout the 3x3 convolution reads through a 4-D tensor map; the
+  // ring is zeroed here once and never written again
+  CU(dalloc(h, &h->zpad, B * 66 * 66 * 256, /*zero=*/true));
+  CU(cudaDeviceSynchronize());
   CU(dalloc(h, &h->emb_tok, B * kTokens * 256));
   CU(dalloc(h, &h->emb_in, B * kTokens * 256));
   if (P > 0) {
@@ -716,24 +720,39 @@ extern "C" int b200sam_finalize_weights(b200sam_t* h) {
 
 namespace {
 
-// Everything of ImageEncoderViT.forward that reads and writes only the handle's own buffers: patch GEMM, the
+// PatchEmbed (image_encoder.py:111-113, 395-426) + absolute position embedding (:115-116) as one GEMM with bias and
+// pos_embed in the epilogue.  bf16 frames are read by the GEMM's own TMA loads through a 5-D tensor map (AM_PATCH16,
+// no im2col copy); fp32 / fp16 frames, widths that are not a multiple of 256 and the SIMT bisect path go through the
+// im2col index map, which also casts to bf16.  Reads the caller's frames, so it stays outside the CUDA graph.
+int encode_patch(b200sam_t* h, const void* frames, int frames_dtype, int B, cudaStream_t s) {
+  const int D = h->dim;
+  const long T = (long)B * kTokens;
+  GemmEpi e;
+  e.bias = h->patch_b;
+  e.addend = h->pos;
+  e.ld_add = D;
+  e.add_mod = kTokens;
+  e.out = h->X;
+  e.ld_out = D;
+  const bool implicit = frames_dtype == DT_BF16 && D % 256 == 0 && !h->debug_simt &&
+                        kernel_variant(VK_IMPLICIT_CONV) == 0 && (reinterpret_cast<uintptr_t>(frames) & 15) == 0;
+  if (implicit) {
+    e.a_mode = AM_PATCH16;
+    h->pc = B200SAM_PC_GEMM_PATCH;
+    return run_gemm(h, false, GM_F32, frames, 768, h->patch_w, 768, T, D, 768, e, s);
+  }
+  h->pc = B200SAM_PC_ELEMENTWISE;
+  KL(launch_im2col_patch(frames, frames_dtype, B, h->hid, s));
+  h->pc = B200SAM_PC_GEMM_PATCH;
+  return run_gemm(h, false, GM_F32, h->hid, 768, h->patch_w, 768, T, D, 768, e, s);
+}
+
+// Everything of ImageEncoderViT.forward that reads and writes only the handle's own buffers: the
 // transformer blocks, the neck.  No caller pointer appears in any launch, which is what makes the sequence
 // capturable into a CUDA graph (b200sam_encode).  Returns 1 when a debug stop cut the sequence short.
 int encode_body(b200sam_t* h, int B, cudaStream_t s) {
   const int D = h->dim, heads = h->heads, hd = h->hd;
   const long T = (long)B * kTokens;
-  // PatchEmbed GEMM (bias + pos_embed in the epilogue) on the im2col rows b200sam_encode left in `hid`
-  {
-    GemmEpi e;
-    e.bias = h->patch_b;
-    e.addend = h->pos;
-    e.ld_add = D;
-    e.add_mod = kTokens;
-    e.out = h->X;
-    e.ld_out = D;
-    h->pc = B200SAM_PC_GEMM_PATCH;
-    if (int r = run_gemm(h, false, GM_F32, h->hid, 768, h->patch_w, 768, T, D, 768, e, s)) return r;
-  }
   const int nblocks = (h->debug_stop_block >= 0 && h->debug_stop_block < h->depth) ? h->debug_stop_block : h->depth;
   for (int i = 0; i < nblocks; ++i) {
     const EncBlock& b = h->blk[i];
@@ -794,9 +813,13 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
   // neck (image_encoder.py:92-108): conv1x1 -> LayerNorm2d -> conv3x3 -> LayerNorm2d, token-major
   h->pc = B200SAM_PC_NECK;
   KL(launch_cast_f32_bf16(h->X, h->ln_plain, T * D, s));
-  __nv_bfloat16* z = h->attn_o;   // (T, 256) bf16 scratch
+  // neck.2 Conv2d 3x3: the GEMM gathers its A tiles from the zero-ringed neck.1 output (AM_CONV3); the SIMT bisect
+  // path and variant 1 materialise the (T, 9*256) im2col rows instead
+  const bool implicit3 = !h->debug_simt && kernel_variant(VK_IMPLICIT_CONV) == 0;
+  __nv_bfloat16* z = implicit3 ? h->zpad : h->attn_o;   // (B, 66, 66, 256) / (T, 256) bf16
   {
     GemmEpi e;
+    e.rowmap = implicit3 ? RM_TOKEN_TO_PAD66 : RM_IDENT;
     e.out2 = z;
     e.ld_out = 256;
     e.ln_g = h->neck1g;
@@ -804,15 +827,17 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
     e.ln_eps = 1e-6f;
     if (int r = run_gemm(h, false, GM_LN, h->ln_plain, D, h->neck0_w, D, T, 256, D, e, s)) return r;
   }
-  KL(launch_im2col_3x3(z, B, h->hid, s));
+  if (!implicit3) KL(launch_im2col_3x3(z, B, h->hid, s));
   {
     GemmEpi e;
+    e.a_mode = implicit3 ? AM_CONV3 : AM_PLAIN;
     e.out = h->emb_tok;
     e.ld_out = 256;
     e.ln_g = h->neck3g;
     e.ln_b = h->neck3b;
     e.ln_eps = 1e-6f;
-    if (int r = run_gemm(h, false, GM_LN, h->hid, 9 * 256, h->neck2_w, 9 * 256, T, 256, 9 * 256, e, s)) return r;
+    if (int r = run_gemm(h, false, GM_LN, implicit3 ? z : h->hid, 9 * 256, h->neck2_w, 9 * 256, T, 256, 9 * 256, e, s))
+      return r;
   }
   return 0;
 }
@@ -823,7 +848,8 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
 // kernels' shared-memory attributes), the second is captured on the caller's stream, later ones replay.  Profiling,
 // debug switches and a caller who is capturing the stream himself use the plain launch sequence.
 int encode_body_graphed(b200sam_t* h, int B, cudaStream_t s) {
-  const int sig = kernel_variant(VK_ATTN_WINDOW) * 10000 + kernel_variant(VK_ATTN_GLOBAL) * 100 + kernel_variant(VK_GEMM_PAIR);
+  const int sig = kernel_variant(VK_ATTN_WINDOW) * 10000 + kernel_variant(VK_ATTN_GLOBAL) * 100 +
+                  kernel_variant(VK_GEMM_PAIR) * 10 + kernel_variant(VK_IMPLICIT_CONV);
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
   const bool plain = h->prof_on || h->debug_simt || h->debug_stop_block >= 0 || !h->use_graphs ||
                      cudaStreamIsCapturing(s, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone;
@@ -885,9 +911,7 @@ extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   h->prof_stream = s;
 
-  // PatchEmbed (image_encoder.py:111-113): the im2col index map reads the caller's frames
-  h->pc = B200SAM_PC_ELEMENTWISE;
-  KL(launch_im2col_patch(frames, frames_dtype, B, h->hid, s));
+  if (int r = encode_patch(h, frames, frames_dtype, B, s)) return r;
   {
     const int r = encode_body_graphed(h, B, s);
     if (r < 0) return r;

@@ -98,6 +98,17 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* t
       : "memory");
 }
 
+// 4-D tiled load (coordinates innermost first): the 3x3 neck convolution reads its A tiles straight from the
+// zero-padded (B, 66, 66, 256) activation, one (64 channels, 64 x, 2 y) box per tap (gemm_tc.cu, AM_CONV3).
+__device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1,
+                                            int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2),
+      "r"(c3)
+      : "memory");
+}
+
 // L2 prefetch of the box a later tma_load_2d will fetch (no shared memory, no barrier): turns the demand load of a
 // single-buffered operand into an L2 hit.
 __device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* tm, int c_inner, int c_outer) {
@@ -224,6 +235,16 @@ __device__ __forceinline__ void tma_load_2d_2cta(void* smem_dst, const CUtensorM
       "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], "
       "[%2];" ::"r"(smem_u32(smem_dst)),
       "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c_inner), "r"(c_outer)
+      : "memory");
+}
+// 5-D tiled load issued by either CTA of a pair (transaction bytes credited to the leader's mbarrier): the patch
+// embedding reads (16 kx, 64 px, 1 ky, 2 py, 1 channel) boxes of the caller's NCHW frames (gemm_tc.cu, AM_PATCH16).
+__device__ __forceinline__ void tma_load_5d_2cta(void* smem_dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1,
+                                                 int c2, int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], "
+      "[%1, {%3, %4, %5, %6, %7}], [%2];" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
       : "memory");
 }
 // D[tmem, both CTAs] (+)= A * B with M = 256 split over the pair (bf16 operands); issued by the leader only.

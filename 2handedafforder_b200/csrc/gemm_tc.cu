@@ -281,8 +281,15 @@ __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, l
         for (int j = 0; j < 32; ++j)
           v[j] = (v[j] - mean) * rstd * __ldg(e.ln_g + c * 32 + j) + __ldg(e.ln_b + c * 32 + j);
         if (e.out) store_f32x32(reinterpret_cast<float*>(e.out) + row * (long)e.ld_out + c * 32, v);
-        if (e.out2)
-          store_bf16x32(reinterpret_cast<__nv_bfloat16*>(e.out2) + row * (long)e.ld_out + c * 32, v);
+        if (e.out2) {
+          long r2 = row;
+          if (e.rowmap == RM_TOKEN_TO_PAD66) {
+            const long b = row / kTokens;
+            const int t = (int)(row - b * kTokens);
+            r2 = b * (66 * 66) + (t / kGrid + 1) * 66 + (t % kGrid) + 1;
+          }
+          store_bf16x32(reinterpret_cast<__nv_bfloat16*>(e.out2) + r2 * (long)e.ld_out + c * 32, v);
+        }
       }
     }
   } else if constexpr (MODE == GM_UPS1) {
@@ -530,7 +537,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           uint8_t* sA = smem + stage * Cfg::kStageBytes;
           uint8_t* sB = sA + kBM * 128;
           mbar_expect_tx(&full[stage], Cfg::kStageBytes);
-          tma_load_2d(sA, &tmA, &full[stage], a_col0 + kb * kBK, m_blk * kBM);
+          if (!kTf32 && e.a_mode == AM_CONV3) {
+            // 128 tokens = image rows y0, y0+1 of frame b; k block kb = tap (dy, dx), channels c0 .. c0+63.  The box
+            // (64 c, 64 x, 2 y) of the zero-ringed activation lands as 128 rows x 128 bytes, i.e. the K-major SW128 tile
+            const int tap = kb >> 2, c0 = (kb & 3) * 64;
+            tma_load_4d(sA, &tmA, &full[stage], c0, tap % 3, (m_blk & 31) * 2 + tap / 3, m_blk >> 5);
+          } else {
+            tma_load_2d(sA, &tmA, &full[stage], a_col0 + kb * kBK, m_blk * kBM);
+          }
           tma_load_2d(sB, &tmB, &full[stage], kb * kBK, n_blk * BN);
           if (++stage == kStages) {
             stage = 0;
@@ -668,7 +682,17 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           uint8_t* sA = smem + stage * kStageBytes2;
           uint8_t* sB = sA + kBM * 128;
           if (rank == 0) mbar_expect_tx(&full[stage], 2 * kStageBytes2);
-          tma_load_2d_2cta(sA, &tmA, &full[stage], kb * 64, m_blk * 256 + (int)rank * 128);
+          if (e.a_mode == AM_PATCH16) {
+            // this CTA's 128 patches = patch rows py0, py0+1 of frame b; k block kb = channel c, kernel rows ky0..ky0+3.
+            // One box per kernel row: (16 kx, 64 px, 1 ky, 2 py) = 128 rows x 32 bytes, the K-major SW32 tile of one
+            // K = 16 MMA step (4 KB each, 4 per stage).
+            const int p0 = m_blk * 256 + (int)rank * 128;
+            const int bc = (p0 >> 12) * 3 + (kb >> 2), py0 = (p0 & 4095) >> 6, ky0 = (kb & 3) * 4;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) tma_load_5d_2cta(sA + j * 4096, &tmA, &full[stage], 0, 0, ky0 + j, py0, bc);
+          } else {
+            tma_load_2d_2cta(sA, &tmA, &full[stage], kb * 64, m_blk * 256 + (int)rank * 128);
+          }
           tma_load_2d_2cta(sB, &tmB, &full[stage], kb * 64, n_blk * BN + (int)rank * 128);
           if (++stage == kStages2) {
             stage = 0;
@@ -693,10 +717,17 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           tc_fence_after();
           const uint32_t a0 = smem_u32(smem + stage * kStageBytes2);
           const uint32_t b0 = a0 + kBM * 128;
+          if (e.a_mode == AM_PATCH16) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            umma_ss_2cta(d_tmem, umma_desc_sw128(a0 + k * 32), umma_desc_sw128(b0 + k * 32), kIdesc,
-                         (kb | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < 4; ++k)    // A: one 128 x 32 B SW32 sub-tile per K step (8-row groups 256 B apart)
+              umma_ss_2cta(d_tmem, umma_desc(a0 + k * 4096, 256, 0, 6), umma_desc_sw128(b0 + k * 32), kIdesc,
+                           (kb | k) != 0 ? 1u : 0u);
+          } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              umma_ss_2cta(d_tmem, umma_desc_sw128(a0 + k * 32), umma_desc_sw128(b0 + k * 32), kIdesc,
+                           (kb | k) != 0 ? 1u : 0u);
+          }
           umma_commit_2cta(&empty[stage], 3);      // frees the slot in both CTAs
           if (++stage == kStages2) {
             stage = 0;
@@ -765,6 +796,32 @@ cudaError_t make_tmap(CUtensorMap* tm, const void* ptr, bool f32, long rows, lon
   return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
+// bf16 frames (B, 3, 1024, 1024) as (kx, px, ky, py, b*3+c): strides ascending, box = one kernel row of two patch rows
+cudaError_t make_tmap_patch16(CUtensorMap* tm, const void* frames, long B) {
+  cuuint64_t dims[5] = {16, 64, 16, 64, (cuuint64_t)(3 * B)};
+  cuuint64_t strides[4] = {32, 2048, 32768, 2097152};
+  cuuint32_t box[5] = {16, 64, 1, 2, 1};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  if (reinterpret_cast<uintptr_t>(frames) & 15) return cudaErrorInvalidValue;
+  CUresult r = g_encode.load()(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(frames), dims, strides, box,
+                               estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
+// bf16 zero-ringed activation (B, 66, 66, 256) as (c, x, y, b); box = 64 channels of 64 x 2 positions
+cudaError_t make_tmap_conv3(CUtensorMap* tm, const void* z, long B) {
+  cuuint64_t dims[4] = {256, 66, 66, (cuuint64_t)B};
+  cuuint64_t strides[3] = {512, 512 * 66, 512 * 66 * 66};
+  cuuint32_t box[4] = {64, 64, 2, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  if (reinterpret_cast<uintptr_t>(z) & 15) return cudaErrorInvalidValue;
+  CUresult r = g_encode.load()(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(z), dims, strides, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
 template <bool kTf32, int MODE, int BN>
 cudaError_t launch(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const GemmEpi& e,
                    cudaStream_t stream, bool debug_simt) {
@@ -778,7 +835,14 @@ cudaError_t launch(const void* A, int lda, const void* W, int ldw, int M, int N,
   cudaError_t err = smem_opt_in(gemm_tc_kernel<kTf32, MODE, BN>, TileCfg<BN>::kSmemBytes, attr_set);
   if (err != cudaSuccess) return err;
   CUtensorMap tmA, tmB;
-  err = make_tmap(&tmA, A, kTf32, M, e.batch > 1 ? lda : K, lda, kBM);
+  if (e.a_mode == AM_CONV3) {
+    if (kTf32 || M % (2 * kGrid) != 0 || M % kTokens != 0 || K != 9 * 256 || e.batch != 1) return cudaErrorInvalidValue;
+    err = make_tmap_conv3(&tmA, A, M / kTokens);
+  } else if (e.a_mode != AM_PLAIN) {
+    return cudaErrorInvalidValue;
+  } else {
+    err = make_tmap(&tmA, A, kTf32, M, e.batch > 1 ? lda : K, lda, kBM);
+  }
   if (err != cudaSuccess) return err;
   err = make_tmap(&tmB, W, kTf32, N, K, ldw, BN);
   if (err != cudaSuccess) return err;
@@ -796,7 +860,14 @@ cudaError_t launch2(const void* A, int lda, const void* W, int ldw, int M, int N
   cudaError_t err = smem_opt_in(gemm_tc2_kernel<MODE>, kSmemBytes2, attr_set);
   if (err != cudaSuccess) return err;
   CUtensorMap tmA, tmB;
-  err = make_tmap(&tmA, A, false, M, K, lda, 128);
+  if (e.a_mode == AM_PATCH16) {
+    if (M % kTokens != 0 || K != 3 * kPatch * kPatch) return cudaErrorInvalidValue;
+    err = make_tmap_patch16(&tmA, A, M / kTokens);
+  } else if (e.a_mode != AM_PLAIN) {
+    return cudaErrorInvalidValue;
+  } else {
+    err = make_tmap(&tmA, A, false, M, K, lda, 128);
+  }
   if (err != cudaSuccess) return err;
   err = make_tmap(&tmB, W, false, N, K, ldw, 128);
   if (err != cudaSuccess) return err;
@@ -861,8 +932,11 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
   if (N % 32 != 0 || K % 8 != 0) return cudaErrorInvalidValue;
   if (e.batch != 1 && (mode != GM_F16 || tf32 || dbg || e.batch < 1)) return cudaErrorInvalidValue;
   if ((mode == GM_LN || mode == GM_UPS1) && N != 256) return cudaErrorInvalidValue;
+  if (e.a_mode != AM_PLAIN && (dbg || tf32)) return cudaErrorInvalidValue;   // the SIMT bisect path reads a plain A
+  if (e.a_mode == AM_PATCH16 && !(e.batch == 1 && M >= 1024 && N % 256 == 0 && mode == GM_F32)) return cudaErrorInvalidValue;
   if (mode == GM_UPS2 && N != 128) return cudaErrorInvalidValue;
-  if (!tf32 && !dbg && e.batch == 1 && M >= 1024 && N % 256 == 0 && kernel_variant(VK_GEMM_PAIR) != 0) {
+  if (!tf32 && !dbg && e.batch == 1 && M >= 1024 && N % 256 == 0 && e.a_mode != AM_CONV3 &&
+      (kernel_variant(VK_GEMM_PAIR) != 0 || e.a_mode == AM_PATCH16)) {
     switch (mode) {
       case GM_BIAS_BF16: return launch2<GM_BIAS_BF16>(A, lda, W, ldw, M, N, K, e, s);
       case GM_BIAS_GELU_BF16: return launch2<GM_BIAS_GELU_BF16>(A, lda, W, ldw, M, N, K, e, s);

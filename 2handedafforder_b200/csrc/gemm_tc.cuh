@@ -22,7 +22,20 @@ enum RowMap : int {
   RM_WINDOW_TO_TOKEN = 1,  // input rows are in 14x14-window order (25 windows x 196 per frame, pad rows skipped)
   RM_RELW_SHIFT = 3,       // fp16 mode, global rel-pos projections: columns >= 128 of token row r hold q.Rw[126-j];
                            // they are stored shifted by qx = r % 64 so that out[128 + kx] = q.Rw[qx - kx + 63], kx < 64
+  RM_TOKEN_TO_PAD66 = 4,   // GM_LN: the bf16 copy (out2) of token row b*4096 + y*64 + x goes to row b*4356 + (y+1)*66 + x+1
+                           // (the zero-ringed layout AM_CONV3 reads); the fp32 output, if any, stays in token order
   RM_TOKEN_TO_WINDOW = 2,  // bf16 modes: input rows in token order (B*4096), output rows scattered into 14x14-window order (B*4900)
+};
+
+// How the A operand is addressed.  The two convolutions of the encoder are GEMMs whose A tiles are gathered by the TMA
+// engine from the activation itself (no im2col copy): multi-dimensional tensor maps turn a (patch, k) / (token, tap, c)
+// tile into one or four box loads.
+enum AMode : int {
+  AM_PLAIN = 0,    // A is a row-major (M, K) matrix
+  AM_PATCH16 = 1,  // PatchEmbed Conv2d(k16, s16) (image_encoder.py:395-426): A = bf16 frames (B, 3, 1024, 1024), row =
+                   // b*4096 + py*64 + px, k = c*256 + ky*16 + kx; M % 256 == 0, K == 768; CTA-pair kernel only
+  AM_CONV3 = 2,    // neck Conv2d 3x3 pad 1 (image_encoder.py:100-106): A = bf16 (B, 66, 66, 256) zero-ringed activation,
+                   // row = b*4096 + y*64 + x, k = (dy*3 + dx)*256 + c; M % 128 == 0, K == 2304; single-CTA kernel only
 };
 
 struct GemmEpi {
@@ -34,6 +47,7 @@ struct GemmEpi {
   void* out2 = nullptr;           // GM_LN: optional bf16 copy
   int ld_out = 0;
   int rowmap = RM_IDENT;
+  int a_mode = AM_PLAIN;
   float relw_scale = 1.f;      // RM_RELW_SHIFT: factor applied (in fp32) to the shifted w columns before the fp16 store
   int* f16_overflow = nullptr; // GM_F16: set to 1 (host-mapped flag) when a value had to be saturated to +-65504
   const float* ln_g = nullptr;

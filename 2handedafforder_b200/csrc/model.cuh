@@ -146,6 +146,7 @@ struct b200sam {
   // the next API call, which then fails (an out-of-range checkpoint must not produce quietly wrong masks)
   volatile int* ovf_host = nullptr;
   int* ovf_dev = nullptr;
+  __nv_bfloat16* zpad = nullptr;     // (B, 66, 66, 256) neck.1 output with a zero ring (3x3 convolution operand)
   __nv_bfloat16* hid = nullptr;      // (B*4096, 4D) MLP hidden; also im2col scratch
   float* emb_tok = nullptr;          // (B*4096, 256) fp32 image embedding, token-major
   // decoder workspace

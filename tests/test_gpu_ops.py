@@ -9,6 +9,7 @@ import math
 import pytest
 import torch
 
+from oracle import synth
 from tests import gpu_util as G
 
 pytestmark = pytest.mark.gpu
@@ -186,3 +187,28 @@ def test_attention_relpos_checkpoint_like_magnitudes(S, nb, heads, hd):
     # near one-hot softmax rows: compare on an absolute scale (|v| ~ 1)
     assert float((out.float() - ref).abs().max()) < 6e-2
     assert float((out.float() - ref).abs().mean() / ref.abs().mean()) < 1e-2
+
+
+@pytest.mark.parametrize("arch_name,batch", [("tiny64", 1), ("tiny64", 3), ("tiny80", 2)])
+def test_tma_gathered_convolutions_equal_the_im2col_path(arch_name, batch):
+    """PatchEmbed Conv2d(k16,s16) and the neck's Conv2d 3x3 (image_encoder.py:395-426, 100-106) read their A tiles
+    through multi-dimensional TMA tensor maps (gemm_tc.cuh AM_PATCH16 / AM_CONV3).  Same K order, same tiles, same
+    accumulation order as the im2col copy + plain GEMM (debug variant 3 = 1), so the embeddings are bit-identical.
+    tiny80 (width 320, not a multiple of 256) takes the im2col patch path but the gathered 3x3; fp32 frames take
+    im2col for the patch embedding by design (the index map is also the cast)."""
+    sam, arch, sd = G.build_sam_from_synth(arch_name, max_batch=batch, max_prompts=1)
+    frames = synth.make_frames(3, batch).cuda()
+    try:
+        for dt in (torch.bfloat16, torch.float32):
+            x = frames.to(dt)
+            assert G.lib().b200sam_debug_set_variant(3, 1) == 0
+            want = sam.get_visual_embs(x)
+            assert G.lib().b200sam_debug_set_variant(3, 0) == 0
+            got = sam.get_visual_embs(x)
+            got2 = sam.get_visual_embs(x)           # second / third call: the CUDA-graph replay of the body
+            got3 = sam.get_visual_embs(x)
+            torch.cuda.synchronize()
+            assert torch.isfinite(want.float()).all() and want.float().abs().max() > 0
+            assert torch.equal(got, want) and torch.equal(got2, want) and torch.equal(got3, want)
+    finally:
+        G.lib().b200sam_debug_set_variant(3, 0)
