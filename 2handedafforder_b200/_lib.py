@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(PKG_DIR, "libb200sam.so")
 F32, BF16, F16 = 0, 1, 2
 VIT_B, VIT_L, VIT_H = 0, 1, 2
 
-# every symbol include/b200sam.h and include/b200sam_debug.h declare: (name, restype, argtypes)
+# every symbol include/b200sam.h, include/b200sam_train.h and include/b200sam_debug.h declare: (name, restype, argtypes)
 _P, _I, _L, _F = C.c_void_p, C.c_int, C.c_int64, C.c_float
 SYMBOLS = [
     ("b200sam_create", _I, [C.POINTER(_P), _I, _I, _I, _I]),
@@ -44,6 +44,23 @@ SYMBOLS = [
     ("b200sam_op_gemm", _I, [_I, _I, _I, _P, _I, _P, _I, _I, _I, _I, _P, _P, _I, _I, _P, _P, _F, _P, _I, _I, _I, _P]),
     ("b200sam_op_layernorm", _I, [_P, _I, _I, _P, _P, _F, _P, _I, _P]),
     ("b200sam_op_attention", _I, [_P, _I, _I, _I, _I, _P, _P, _P, _P]),
+    # include/b200sam_train.h (fp32 forward / backward primitives of the decoder training graph)
+    ("b200sam_train_gemm", _I, [_P, _P, C.POINTER(_L), _P, C.POINTER(_L), _P, C.POINTER(_L), _P, _I, _I, _I, _I, _I, _I,
+                                _F, _F, _I, _P]),
+    ("b200sam_train_layernorm_fwd", _I, [_P, _P, _P, _P, _L, _I, _F, _P, _P, _P, _P]),
+    ("b200sam_train_layernorm_bwd", _I, [_P, _P, _P, _P, _P, _P, _L, _I, _P, _P, _P, _P]),
+    ("b200sam_train_softmax_fwd", _I, [_P, _P, _L, _I, _P, _P]),
+    ("b200sam_train_softmax_bwd", _I, [_P, _P, _P, _L, _I, _P, _P]),
+    ("b200sam_train_act_fwd", _I, [_P, _I, _P, _L, _P, _P]),
+    ("b200sam_train_act_bwd", _I, [_P, _I, _P, _P, _L, _P, _P]),
+    ("b200sam_train_add_bcast", _I, [_P, _P, _P, _L, _I, _L, _P, _P]),
+    ("b200sam_train_colsum", _I, [_P, _P, _L, _I, _P, _P]),
+    ("b200sam_train_pixel_shuffle", _I, [_P, _P, _L, _I, _I, _I, _I, _P, _P]),
+    ("b200sam_train_src_tokens", _I, [_P, _P, _I, _I, _P, _P, _I, _P, _P]),
+    ("b200sam_train_resize_fwd", _I, [_P, _P, _L, _I, _I, _L, _L, _I, _I, _P, _P]),
+    ("b200sam_train_resize_bwd", _I, [_P, _P, _L, _I, _I, _L, _L, _I, _I, _P, _P]),
+    ("b200sam_train_mask_loss_fwd", _I, [_P, _P, _P, _P, _I, _L, _P, _P]),
+    ("b200sam_train_mask_loss_bwd", _I, [_P, _P, _P, _P, _P, _P, _P, _I, _L, _F, _F, _P, _P]),
     # include/b200sam_debug.h (test / measurement hooks, not part of the drop-in surface)
     ("b200sam_debug_set_variant", _I, [_I, _I]),
     ("b200sam_debug_set_trace", _I, [_P]),

@@ -160,6 +160,8 @@ class B200Sam(CallersMixin, nn.Module):
         self._sig = None
         self._frozen = False
         self._pe_cache: Optional[torch.Tensor] = None
+        self._pe_tok_cache: Optional[Tuple[torch.Tensor, torch.Tensor]] = None
+        self._pe_key: Optional[Tuple[int, int, str]] = None
         self.eval()
 
     # ------------------------------------------------------------------ handle / weights
@@ -242,7 +244,6 @@ class B200Sam(CallersMixin, nn.Module):
                        h, f"load_weight({name})")
         _lib.check(lib.b200sam_finalize_weights(h), h, "finalize_weights")
         self._sig = sig
-        self._pe_cache = None
 
     def freeze_weights(self, frozen: bool = True) -> None:
         """Skip the per-call parameter-change check (inference servers / benchmarks)."""
@@ -257,6 +258,7 @@ class B200Sam(CallersMixin, nn.Module):
             raise ValueError(f"frames must be (B,3,{IMG_SIZE},{IMG_SIZE}), got {tuple(x.shape)}")
         if x.dtype not in _DTYPES:
             raise TypeError(f"unsupported frame dtype {x.dtype}")
+        self._no_autograd("image_encoder", x)      # frozen in the reference (LISA.py:81-83): no backward pass
         h = self._ensure(x.device, batch=x.shape[0])
         x = x.contiguous()
         out = torch.empty((x.shape[0], OUT_CH, GRID, GRID), dtype=x.dtype, device=x.device) if want_output else None
@@ -274,12 +276,18 @@ class B200Sam(CallersMixin, nn.Module):
     # ------------------------------------------------------------------ prompt encoder / decoder
     def _dense_pe(self) -> torch.Tensor:
         dev = self.device
+        # the PE depends on one never-trained buffer only: as long as that buffer is unchanged the cached tensor is
+        # returned without the weight-change check of _ensure (LISA's training loop asks for it once per image while
+        # the decoder parameters change every step)
+        g = self.prompt_encoder.pe_layer.positional_encoding_gaussian_matrix
+        key = (g.data_ptr(), g._version, str(dev))
+        if self._pe_cache is not None and self._pe_key == key:
+            return self._pe_cache
         h = self._ensure(dev)
-        if self._pe_cache is None:
-            out = torch.empty((1, OUT_CH, GRID, GRID), dtype=torch.float32, device=dev)
-            with torch.cuda.device(dev):
-                _lib.check(_lib.load().b200sam_dense_pe(h, _ptr(out), _stream_ptr()), h, "dense_pe")
-            self._pe_cache = out
+        out = torch.empty((1, OUT_CH, GRID, GRID), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.load().b200sam_dense_pe(h, _ptr(out), _stream_ptr()), h, "dense_pe")
+        self._pe_cache, self._pe_key = out, key
         return self._pe_cache
 
     def _check_dense(self, dense: Optional[torch.Tensor]) -> None:
@@ -299,6 +307,7 @@ class B200Sam(CallersMixin, nn.Module):
         P = int(offsets[-1])
         f32 = dict(dtype=torch.float32, device=device)
         out: Dict[str, torch.Tensor] = {}
+        self._no_autograd("the fused inference decode (segment / segment_bits / eval-mode decoders)", emb, seg)
         if heads_out is not None:
             if (heads_out.dim() != 3 or heads_out.shape[0] != 3 or heads_out.shape[1] < P or heads_out.shape[2] != 4
                     or heads_out.dtype != torch.float32 or not heads_out.is_contiguous() or heads_out.device != device):
@@ -329,25 +338,79 @@ class B200Sam(CallersMixin, nn.Module):
         _lib.check(rc, h, "decode")
         return out
 
-    def _no_autograd(self, what: str, *tensors: Optional[torch.Tensor], module: Optional[nn.Module] = None) -> None:
-        """The library has no backward pass (SURVEY 8f row 4 is out of scope): outputs carry no grad_fn.  LISA's
-        training forward (LISA.py:284-325 with train_mask_decoder=True; :84-90 puts both decoders in train() mode with
-        requires_grad parameters, and the [SEG] embeddings come out of the trainable text_hidden_fcs) would silently
-        get constant mask losses, so refuse instead of returning detached tensors into a graph that expects
-        gradients.  Plain inference - eval() mode, inputs without grad - is unaffected even outside no_grad()."""
+    def _wants_grad(self, *tensors: Optional[torch.Tensor], module: Optional[nn.Module] = None) -> bool:
+        """True when the call is part of a training forward: autograd is on and an input requires grad, or the
+        decoder is in train() mode with requires_grad parameters (LISA.py:84-90 does exactly that).  Plain inference -
+        eval() mode, inputs without grad - stays on the fused inference kernels even outside no_grad()."""
         if not torch.is_grad_enabled():
-            return
-        needs = [t for t in tensors if t is not None and t.requires_grad]
-        if needs or (module is not None and module.training and any(p.requires_grad for p in module.parameters())):
+            return False
+        if any(t is not None and t.requires_grad for t in tensors):
+            return True
+        return module is not None and module.training and any(p.requires_grad for p in module.parameters())
+
+    def _no_autograd(self, what: str, *tensors: Optional[torch.Tensor], module: Optional[nn.Module] = None) -> None:
+        """Entry points without a backward pass (the frozen encoder, the fused segment() fast path) refuse inputs that
+        require grad instead of returning detached tensors into a graph that expects gradients."""
+        if self._wants_grad(*tensors, module=module):
             raise NotImplementedError(
-                f"{what}: called with autograd enabled on inputs/parameters that require grad, but libb200sam is "
-                "inference-only (no backward).  Wrap evaluation in torch.no_grad() (as LISA.evaluate / "
-                "train_ds.validate do), or run the training forward through the reference PyTorch decoders.")
+                f"{what}: called with autograd enabled on inputs/parameters that require grad, but this entry point "
+                "has no backward pass.  The trainable part of the SAM branch (both mask decoders, postprocess_masks, "
+                "the mask losses) has one: use mask_decoder_left / mask_decoder_right / postprocess_masks or "
+                "train_decode(); wrap everything else in torch.no_grad() as LISA.get_visual_embs does.")
+
+    # ------------------------------------------------------------------ training forward / backward (SURVEY 8f-4)
+    def train_ops(self, device: Optional[torch.device] = None):
+        """The training module (2handedafforder_b200/train.py) bound to this model's library handle."""
+        from . import train as T
+        T.bind_handle(self._ensure_handle_only(device if device is not None else self.device))
+        return T
+
+    def _key_pe_tokens(self) -> torch.Tensor:
+        """Dense positional encoding in token order (4096, 256) fp32 (transformer.py:84: image_pe.flatten(2).permute)."""
+        pe = self._dense_pe()
+        if self._pe_tok_cache is None or self._pe_tok_cache[0] is not pe:
+            with torch.no_grad():
+                self._pe_tok_cache = (pe, pe.flatten(2).permute(0, 2, 1)[0].contiguous())
+        return self._pe_tok_cache[1]
+
+    def _decode_train(self, side: str, image_embeddings: torch.Tensor, frame_of_prompt: Optional[torch.Tensor],
+                      sparse: torch.Tensor):
+        if image_embeddings.requires_grad:
+            raise NotImplementedError("image_embeddings require grad, but the image encoder is frozen in the reference "
+                                      "(LISA.py:81-83) and has no backward pass here")
+        dec = self.mask_decoder_left if side == "left" else self.mask_decoder_right
+        T = self.train_ops(image_embeddings.device)
+        key_pe = self._key_pe_tokens()
+        dense_vec = self.prompt_encoder.no_mask_embed.weight.detach().reshape(-1).float()
+        with torch.cuda.device(image_embeddings.device):
+            return T.decoder_forward(dec, image_embeddings.contiguous(), frame_of_prompt, sparse, dense_vec, key_pe)
+
+    def train_decode(self, image_embeddings: torch.Tensor, seg_embeds: Sequence[torch.Tensor]) -> Dict[str, object]:
+        """Both decoders for every prompt of every frame in ONE pass per side, under autograd (the reference loops
+        per image, LISA.py:284-325).  image_embeddings: (F, 256, 64, 64) from get_visual_embs (no grad); seg_embeds:
+        F tensors (N_i, 256), e.g. text_hidden_fcs outputs that require grad.
+        Returns low_res_left / low_res_right (P, 1, 256, 256), iou_left / iou_right (P, 1), taxonomy (P, 4), offsets."""
+        if image_embeddings.dim() != 4 or tuple(image_embeddings.shape[1:]) != (OUT_CH, GRID, GRID):
+            raise ValueError(f"image_embeddings must be (F,{OUT_CH},{GRID},{GRID}), got {tuple(image_embeddings.shape)}")
+        if len(seg_embeds) != image_embeddings.shape[0]:
+            raise ValueError("one seg_embeds tensor per frame is required")
+        dev = image_embeddings.device
+        counts = [int(s.shape[0]) for s in seg_embeds]
+        offsets = [0]
+        for c in counts:
+            offsets.append(offsets[-1] + c)
+        P = offsets[-1]
+        sparse = torch.cat([s.reshape(-1, OUT_CH) for s in seg_embeds], 0).reshape(P, 1, OUT_CH)
+        fop = torch.tensor([i for i, c in enumerate(counts) for _ in range(c)], dtype=torch.int32, device=dev)
+        ml, il, tax = self._decode_train("left", image_embeddings, fop, sparse)
+        mr, ir, _ = self._decode_train("right", image_embeddings, fop, sparse)
+        return {"low_res_left": ml, "low_res_right": mr, "iou_left": il, "iou_right": ir, "taxonomy": tax,
+                "offsets": offsets}
 
     def _decode_one_side(self, side: str, image_embeddings: torch.Tensor, sparse: torch.Tensor,
                          dense: Optional[torch.Tensor]):
         dec = self.mask_decoder_left if side == "left" else self.mask_decoder_right
-        self._no_autograd(f"mask_decoder_{side}", image_embeddings, sparse, module=dec)
+        train = self._wants_grad(sparse, module=dec)
         if image_embeddings.dim() != 4 or tuple(image_embeddings.shape) != (1, OUT_CH, GRID, GRID):
             raise ValueError(f"image_embeddings must be (1,{OUT_CH},{GRID},{GRID}) per call (LISA.py:306,505), got "
                              f"{tuple(image_embeddings.shape)}")
@@ -355,6 +418,9 @@ class B200Sam(CallersMixin, nn.Module):
             raise ValueError("sparse_prompt_embeddings must be (N,1,256): exactly one [SEG] embedding per prompt")
         self._check_dense(dense)
         n = sparse.shape[0]
+        if train:      # LISA.model_forward with train_mask_decoder (LISA.py:84-90,296-321): fp32 kernels with a backward
+            masks, iou, tax = self._decode_train(side, image_embeddings, None, sparse)
+            return (masks, iou, tax) if side == "left" else (masks, iou)
         res = self._decode_raw(image_embeddings, 1, sparse.reshape(n, OUT_CH), [0, n], side == "left", side == "right",
                                image_embeddings.device)
         masks = res[f"lowres_{side}"].reshape(n, 1, 256, 256)
@@ -386,7 +452,10 @@ class B200Sam(CallersMixin, nn.Module):
         """Sam.postprocess_masks (sam.py:155-189): returns fp32 (N,C,H,W)."""
         if masks.dim() != 4 or tuple(masks.shape[-2:]) != (256, 256):
             raise ValueError(f"masks must be (N,C,256,256), got {tuple(masks.shape)}")
-        self._no_autograd("postprocess_masks", masks)
+        if self._wants_grad(masks):     # LISA.py:304-321 in the training forward
+            T = self.train_ops(masks.device)
+            with torch.cuda.device(masks.device):
+                return T.postprocess_masks(masks.float(), input_size, original_size, IMG_SIZE)
         n, c = masks.shape[:2]
         low = masks.to(torch.float32).contiguous().reshape(n * c, 256, 256)
         logits, _ = self._postprocess_raw(low, input_size, original_size, True, False, 0.0)

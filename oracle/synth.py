@@ -206,3 +206,31 @@ def synth_image(H, W, seed):
     base = 127 + 100 * np.sin(xx / 17.0 + seed) * np.cos(yy / 11.0)
     img = base[..., None] + rng.normal(0, 40, (H, W, 3))
     return np.clip(img, 0, 255).astype(np.uint8)
+
+
+# --------------------------------------------------------------------------- training case
+TRAIN_CASE = {
+    # two frames with 2 and 1 [SEG] prompts, different aspect ratios, small label resolutions
+    "prompts": (2, 1),
+    "resize": ((576, 1024), (1024, 683)),
+    "original": ((135, 240), (150, 100)),
+    "taxonomies": ((0.0, 0.0, 1.0, 0.0), (1.0, 0.0, 0.0, 0.0)),   # frame 0: bimanual, frame 1: left hand only
+}
+
+
+def make_train_inputs(seed: int = 7):
+    """Image embeddings (F,256,64,64) (stand-ins for the frozen encoder's output), ground-truth masks per frame and
+    side, one-hot taxonomies.  The [SEG] embeddings are make_seg_embeds(i, n)."""
+    g = torch.Generator().manual_seed(seed)
+    n_frames = len(TRAIN_CASE["prompts"])
+    emb = 0.5 * torch.randn(n_frames, OUT_CH, GRID, GRID, generator=g)
+    gt_left, gt_right = [], []
+    for i, (n, (h, w)) in enumerate(zip(TRAIN_CASE["prompts"], TRAIN_CASE["original"])):
+        yy = torch.arange(h, dtype=torch.float32)[:, None] / h
+        xx = torch.arange(w, dtype=torch.float32)[None, :] / w
+        c = torch.rand(n, 2, 2, generator=g)
+        gt_left.append((((yy - c[:, 0, 0, None, None]) ** 2 + (xx - c[:, 0, 1, None, None]) ** 2) < 0.06).float())
+        gt_right.append((((yy - c[:, 1, 0, None, None]) ** 2 + (xx - c[:, 1, 1, None, None]) ** 2) < 0.04).float())
+    tax = torch.tensor(TRAIN_CASE["taxonomies"], dtype=torch.float32)
+    segs = [make_seg_embeds(i, n) for i, n in enumerate(TRAIN_CASE["prompts"])]
+    return emb, segs, gt_left, gt_right, tax

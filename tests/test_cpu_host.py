@@ -11,7 +11,7 @@ import torch
 from oracle import synth
 from tests import gpu_util as G
 
-HEADERS = [os.path.join(G.ROOT, "include", n) for n in ("b200sam.h", "b200sam_debug.h")]
+HEADERS = [os.path.join(G.ROOT, "include", n) for n in ("b200sam.h", "b200sam_debug.h", "b200sam_train.h")]
 
 
 def _declared_functions():

@@ -116,9 +116,11 @@ def test_postprocess_matches_interpolate(tiny, resize, original):
     assert torch.equal(mask.bool(), logits > 0.25)
 
 
-def test_training_forward_is_refused_not_detached(tiny):
-    """LISA.model_forward with train_mask_decoder=True (LISA.py:84-90,284-325) needs gradients the library cannot give:
-    the facade raises instead of returning tensors without grad_fn; inference paths are unaffected."""
+def test_training_forward_gets_a_graph_and_frozen_parts_refuse(tiny):
+    """LISA.model_forward with train_mask_decoder=True (LISA.py:84-90,284-325): the decoders and postprocess_masks
+    return tensors WITH grad_fn (the fp32 training kernels, tests/test_gpu_train.py checks the numbers); the frozen
+    encoder and the fused inference fast path refuse grad-requiring inputs instead of returning detached tensors;
+    inference calls are unaffected."""
     sam, _, _ = tiny
     frames = synth.make_frames(0, 1).cuda()
     with torch.no_grad():
@@ -126,20 +128,29 @@ def test_training_forward_is_refused_not_detached(tiny):
     seg = synth.make_seg_embeds(0, 2).cuda().requires_grad_(True)          # output of the trainable text_hidden_fcs
     sparse, dense = sam.prompt_encoder(None, None, None, seg.unsqueeze(1))
     assert sparse.requires_grad
-    with pytest.raises(NotImplementedError, match="inference-only"):
-        sam.mask_decoder_left(emb, sam.prompt_encoder.get_dense_pe(), sparse, dense, False)
+    low_t, iou_t, tax_t = sam.mask_decoder_left(emb, sam.prompt_encoder.get_dense_pe(), sparse, dense, False)
+    assert low_t.grad_fn is not None and tax_t.grad_fn is not None and low_t.shape == (2, 1, 256, 256)
     with torch.no_grad():                                                   # LISA.evaluate / validate
         low, iou, tax = sam.mask_decoder_left(emb, sam.prompt_encoder.get_dense_pe(), sparse, dense, False)
-    assert low.shape == (2, 1, 256, 256)
+    assert low.shape == (2, 1, 256, 256) and low.grad_fn is None
+    # same weights, fp32 training kernels vs the TF32 inference kernels
+    assert G.rel_err(low_t.detach(), low) < 2e-2
+    up = sam.postprocess_masks(low.clone().requires_grad_(True), (576, 1024), (64, 64))
+    assert up.grad_fn is not None
+    with pytest.raises(NotImplementedError, match="no backward"):
+        sam.image_encoder(frames.clone().requires_grad_(True))
+    out = sam.segment(frames, [seg], [(576, 1024)], [(64, 64)])            # the fused fast path is @torch.no_grad()
+    assert out["taxonomy"].grad_fn is None
     sam.mask_decoder_right.train()                                          # LISA.py:86-90
     try:
-        with pytest.raises(NotImplementedError):
-            sam.mask_decoder_right(emb, sam.prompt_encoder.get_dense_pe(), sparse.detach(), dense, False)
+        for p in sam.mask_decoder_right.parameters():
+            p.requires_grad = True
+        low_r, _ = sam.mask_decoder_right(emb, sam.prompt_encoder.get_dense_pe(), sparse.detach(), dense, False)
+        assert low_r.grad_fn is not None
     finally:
         sam.mask_decoder_right.eval()
-    sam.mask_decoder_right(emb, sam.prompt_encoder.get_dense_pe(), sparse.detach(), dense, False)   # eval: fine
-    with pytest.raises(NotImplementedError):
-        sam.postprocess_masks(low.clone().requires_grad_(True), (576, 1024), (64, 64))
+    low_e, _ = sam.mask_decoder_right(emb, sam.prompt_encoder.get_dense_pe(), sparse.detach(), dense, False)   # eval
+    assert low_e.grad_fn is None
 
 
 def test_weight_resync_keeps_memory_flat(tiny):

@@ -1,0 +1,342 @@
+"""Training forward / backward of the two mask decoders on the GPU: every primitive of
+include/b200sam_train.h against the same torch op (forward and autograd backward, fp32 with TF32 off), then the whole
+SAM branch of a training step - the call sequence of LISA.model_forward (2Haff/model/LISA.py:284-325) through the
+facade in train() mode, postprocess_masks under autograd, the mask losses of LISA.py:16-59,346-420 - against
+oracle/train_oracle.py (pinned to the unmodified reference by tests/golden/train_tiny.npz): losses, outputs, the gradient
+of the [SEG] embeddings and of EVERY decoder parameter.
+
+Tolerance (floating point, stated here): fp32 kernels vs an fp32 CPU reference differ by summation order only, so
+max |got - ref| <= 2e-4 * max |ref| + 1e-7 per tensor (the observed error is ~1e-5 relative)."""
+import math
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import synth
+from oracle import train_oracle as TO
+from tests import gpu_util as G
+
+pytestmark = pytest.mark.gpu
+
+TOL = 2e-4
+
+
+def _close(got, ref, what, tol=TOL, floor=1e-7):
+    got, ref = got.detach().float().cpu(), ref.detach().float().cpu()
+    assert got.shape == ref.shape, (what, got.shape, ref.shape)
+    err = float((got - ref).abs().max())
+    lim = tol * float(ref.abs().max()) + floor
+    assert err <= lim, f"{what}: max err {err:.3e} > {lim:.3e}"
+
+
+@pytest.fixture(scope="module")
+def tiny():
+    sam, arch, sd = G.build_sam_from_synth("tiny64", max_batch=2, max_prompts=4)
+    T = sam.train_ops(torch.device("cuda", 0))
+    return sam, sd, T
+
+
+def _rand(*shape, seed=0, grad=True):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(*shape, generator=g).cuda().requires_grad_(grad)
+
+
+@pytest.mark.parametrize("rows,K,N,relu,w_kn", [(6, 256, 128, False, False), (3 * 4096, 256, 128, False, False),
+                                                (18, 256, 2048, True, False), (2 * 4096, 256, 256, False, True),
+                                                (5, 1024, 4, False, False), (8192, 64, 128, False, True)])
+def test_linear_forward_backward(tiny, rows, K, N, relu, w_kn):
+    _, _, T = tiny
+    x = _rand(rows, K, seed=1)
+    w = _rand(*((K, N) if w_kn else (N, K)), seed=2)
+    w.data.mul_(1.0 / math.sqrt(K))
+    b = _rand(N, seed=3)
+    dy = _rand(rows, N, seed=4, grad=False)
+    y = T.linear(x, w, b, relu=relu, w_kn=w_kn)
+    y.backward(dy)
+    xr, wr, br = (t.detach().clone().requires_grad_(True) for t in (x, w, b))
+    yr = xr @ wr + br if w_kn else F.linear(xr, wr, br)
+    yr = torch.relu(yr) if relu else yr
+    yr.backward(dy)
+    _close(y, yr, "y")
+    _close(x.grad, xr.grad, "dx")
+    _close(w.grad, wr.grad, "dw")     # rows = 12288: the split-K path with atomics
+    _close(b.grad, br.grad, "db")
+
+
+def test_linear_on_strided_rows(tiny):
+    _, _, T = tiny
+    hs = _rand(5, 6, 256, seed=5)
+    w, b = _rand(32, 256, seed=6), _rand(32, seed=7)
+    y = T.linear(hs[:, 2, :], w, b)
+    y.sum().backward()
+    hr = hs.detach().clone().requires_grad_(True)
+    F.linear(hr[:, 2, :], w.detach(), b.detach()).sum().backward()
+    _close(hs.grad, hr.grad, "d hs")
+
+
+@pytest.mark.parametrize("P,Tq,Tk", [(3, 6, 6), (3, 6, 4096), (2, 4096, 6)])
+def test_attention_products_with_head_strides(tiny, P, Tq, Tk):
+    """q @ k^T / sqrt(d), softmax, @ v with the heads as stride patterns (transformer.py:222-233)."""
+    _, _, T = tiny
+    H, d = 8, 16
+    q, k, v = _rand(P, Tq, H * d, seed=1), _rand(P, Tk, H * d, seed=2), _rand(P, Tk, H * d, seed=3)
+    dy = _rand(P, Tq, H * d, seed=4, grad=False)
+
+    def run(q, k, v, mm, sm):
+        qh = q.view(P, Tq, H, d).permute(0, 2, 1, 3)
+        kt = k.view(P, Tk, H, d).permute(0, 2, 3, 1)
+        vh = v.view(P, Tk, H, d).permute(0, 2, 1, 3)
+        return mm(sm(mm(qh, kt, 1.0 / math.sqrt(d), None)), vh, 1.0, (0, 2, 1, 3)).permute(0, 2, 1, 3).reshape(P, Tq, H * d)
+
+    out = run(q, k, v, lambda a, b, al, oo: T.matmul4(a, b, al, oo or (0, 1, 2, 3)), T.softmax)
+    assert out.is_contiguous() or out.reshape(-1).data_ptr() == out.data_ptr()
+    out.backward(dy)
+    qr, kr, vr = (t.detach().clone().requires_grad_(True) for t in (q, k, v))
+    ref = run(qr, kr, vr, lambda a, b, al, oo: (a @ b) * al, lambda s: torch.softmax(s, -1))
+    ref.backward(dy)
+    _close(out, ref, "out")
+    for a, b, n in ((q, qr, "dq"), (k, kr, "dk"), (v, vr, "dv")):
+        _close(a.grad, b.grad, n)
+
+
+@pytest.mark.parametrize("rows,C,eps", [(18, 256, 1e-5), (3 * 4096, 256, 1e-5), (2 * 128 * 128, 64, 1e-6)])
+def test_layernorm_forward_backward(tiny, rows, C, eps):
+    _, _, T = tiny
+    x, g, b = _rand(rows, C, seed=1), _rand(C, seed=2), _rand(C, seed=3)
+    dy = _rand(rows, C, seed=4, grad=False)
+    y = T.layernorm(x, g, b, eps)
+    y.backward(dy)
+    xr, gr, br = (t.detach().clone().requires_grad_(True) for t in (x, g, b))
+    yr = F.layer_norm(xr, (C,), gr, br, eps)
+    yr.backward(dy)
+    _close(y, yr, "y")
+    _close(x.grad, xr.grad, "dx")
+    _close(g.grad, gr.grad, "dgamma")
+    _close(b.grad, br.grad, "dbeta")
+
+
+def test_gelu_add_fork_pixel_shuffle(tiny):
+    _, _, T = tiny
+    x = _rand(2, 64, 64, 16 * 4, seed=1)
+    dy = _rand(2, 128, 128, 16, seed=2, grad=False)
+    a, b = T.fork(x, 2)
+    y = T.gelu(T.PixelShuffleFn.apply(T.add(a, b), 2, 64, 64, 16))
+    y.backward(dy)
+    xr = x.detach().clone().requires_grad_(True)
+    z = (xr + xr).view(2, 64, 64, 16, 2, 2).permute(0, 1, 4, 2, 5, 3).reshape(2, 128, 128, 16)
+    yr = F.gelu(z)
+    yr.backward(dy)
+    _close(y, yr, "y")
+    _close(x.grad, xr.grad, "dx")
+    # positional add with a broadcast period (keys + key_pe)
+    k, pe = _rand(3, 4096, 256, seed=3), _rand(4096, 256, seed=4, grad=False)
+    o = T.add_bcast(k, pe, 4096)
+    o.sum().backward()
+    _close(o, k.detach() + pe, "keys + pe")
+    assert torch.equal(k.grad, torch.ones_like(k))
+
+
+def test_conv_transpose_as_linear_plus_shuffle(tiny):
+    """ConvTranspose2d(k=2, s=2) (mask_decoder.py:52-61) = Linear with the flat (C_in, C_out*4) weight + pixel shuffle."""
+    _, _, T = tiny
+    ci, co, n = 64, 32, 2
+    x = _rand(n, 32, 32, ci, seed=1)
+    w, b = _rand(ci, co, 2, 2, seed=2), _rand(co, seed=3)
+    dy = _rand(n, 64, 64, co, seed=4, grad=False)
+    y = T.PixelShuffleFn.apply(T.linear(x, w.view(ci, co * 4), b.repeat_interleave(4), w_kn=True), n, 32, 32, co)
+    y.backward(dy)
+    xr, wr, br = (t.detach().clone().requires_grad_(True) for t in (x, w, b))
+    yr = F.conv_transpose2d(xr.permute(0, 3, 1, 2), wr, br, stride=2).permute(0, 2, 3, 1)
+    yr.backward(dy)
+    _close(y, yr, "y")
+    _close(x.grad, xr.grad, "dx")
+    _close(w.grad, wr.grad, "dw")
+    _close(b.grad, br.grad, "db")
+
+
+@pytest.mark.parametrize("resize,original", [((576, 1024), (135, 240)), ((1024, 683), (300, 203)),
+                                             ((576, 1024), (1080, 1920))])
+def test_postprocess_masks_under_autograd(tiny, resize, original):
+    sam, _, T = tiny
+    low = _rand(3, 1, 256, 256, seed=1)
+    out = sam.postprocess_masks(low, resize, original)
+    assert out.requires_grad and out.shape == (3, 1, *original)
+    dy = _rand(3, 1, *original, seed=2, grad=False)
+    out.backward(dy)
+    lr = low.detach().clone().requires_grad_(True)
+    m = F.interpolate(lr, (1024, 1024), mode="bilinear", align_corners=False)[..., :resize[0], :resize[1]]
+    ref = F.interpolate(m, original, mode="bilinear", align_corners=False)
+    ref.backward(dy)
+    _close(out, ref, "postprocess")
+    _close(low.grad, lr.grad, "d low-res", tol=5e-4)     # fp32 atomics: order of up to ~60 terms per input pixel
+
+
+def test_mask_losses_forward_backward(tiny):
+    _, _, T = tiny
+    P, H, W = 3, 135, 243
+    x = _rand(P, H, W, seed=1)
+    x.data.mul_(4.0)
+    gt = (torch.rand(P, H, W, generator=torch.Generator().manual_seed(2)) > 0.7).float().cuda()
+    wgt = torch.tensor([1.0, 0.0, 2.0]).cuda()
+    bce, dice = T.mask_losses(x, gt, wgt)
+    (2.0 * bce.sum() + 0.5 * dice.sum() * 3).backward()
+    xr = x.detach().clone().requires_grad_(True)
+    z = wgt.view(-1, 1, 1) * xr
+    bce_r = torch.stack([TO.sigmoid_ce_loss(z[i:i + 1], gt[i:i + 1], 1) for i in range(P)])
+    dice_r = torch.stack([TO.dice_loss(z[i:i + 1], gt[i:i + 1], 1) for i in range(P)])
+    (2.0 * bce_r.sum() + 0.5 * dice_r.sum() * 3).backward()
+    _close(bce, bce_r, "bce", tol=2e-5)
+    _close(dice, dice_r, "dice", tol=2e-5)
+    _close(x.grad, xr.grad, "d logits")
+
+
+def _lisa_train_forward(sam, emb, segs, case):
+    """The SAM part of LISA.model_forward as written (LISA.py:284-325), on the facade."""
+    pl, pr, taxes, lows = [], [], [], []
+    for i, s in enumerate(segs):
+        sparse, dense = sam.prompt_encoder(points=None, boxes=None, masks=None, text_embeds=s.unsqueeze(1))
+        sparse = sparse.to(s.dtype)
+        ml, iou_l, tax = sam.mask_decoder_left(
+            image_embeddings=emb[i].unsqueeze(0), image_pe=sam.prompt_encoder.get_dense_pe(),
+            sparse_prompt_embeddings=sparse, dense_prompt_embeddings=dense, multimask_output=False)
+        mr, iou_r = sam.mask_decoder_right(
+            image_embeddings=emb[i].unsqueeze(0), image_pe=sam.prompt_encoder.get_dense_pe(),
+            sparse_prompt_embeddings=sparse, dense_prompt_embeddings=dense, multimask_output=False)
+        assert ml.shape == (s.shape[0], 1, 256, 256) and iou_l.shape == (s.shape[0], 1) and tax.shape == (s.shape[0], 4)
+        assert ml.grad_fn is not None and mr.grad_fn is not None and tax.grad_fn is not None
+        taxes.append(tax)
+        lows.append((ml, mr))
+        pl.append(sam.postprocess_masks(ml, input_size=case["resize"][i], original_size=case["original"][i])[:, 0])
+        pr.append(sam.postprocess_masks(mr, input_size=case["resize"][i], original_size=case["original"][i])[:, 0])
+    return pl, pr, taxes, lows
+
+
+def _lisa_losses(T, pl, pr, taxes, gt_left, gt_right, tax_gt):
+    """LISA.py:346-420 with the per-mask loss vectors of the library."""
+    wl = tax_gt[:, 0] + tax_gt[:, 2] + tax_gt[:, 3]
+    wr = tax_gt[:, 1] + tax_gt[:, 2] + tax_gt[:, 3]
+    bl = br = dl = dr = tce = 0.0
+    n = 0
+    for i in range(len(pl)):
+        k = pl[i].shape[0]
+        b, d = T.mask_losses(pl[i], gt_left[i], wl[i].expand(k))
+        bl, dl = bl + b.sum() / (k + 1e-8) * k, dl + d.sum() / (k + 1e-8) * k
+        b, d = T.mask_losses(pr[i], gt_right[i], wr[i].expand(k))
+        br, dr = br + b.sum() / (k + 1e-8) * k, dr + d.sum() / (k + 1e-8) * k
+        n += k
+        tce = tce + F.cross_entropy(taxes[i], tax_gt[i][None].expand(k, -1))
+    tce = tce / len(pl)
+    bce = 2.0 * bl / (n + 1e-8) + 2.0 * br / (n + 1e-8)
+    dice = 0.5 * dl / (n + 1e-8) + 0.5 * dr / (n + 1e-8)
+    return {"mask_bce_loss": bce, "mask_dice_loss": dice, "taxonomy_ce_loss": tce, "loss": bce + dice + tce}
+
+
+def test_training_step_matches_oracle_and_reference_golden(tiny, golden):
+    sam, sd, T = tiny
+    case = synth.TRAIN_CASE
+    emb, segs, gt_left, gt_right, tax_gt = synth.make_train_inputs()
+    ref = TO.train_step(sd, emb, segs, case["resize"], case["original"], gt_left, gt_right, tax_gt)
+    g = golden("train_tiny")
+
+    # LisaMetaModel.initialize_lisa_modules (LISA.py:81-90)
+    for p in sam.parameters():
+        p.requires_grad = False
+        p.grad = None
+    for dec in (sam.mask_decoder_left, sam.mask_decoder_right):
+        dec.train()
+        for p in dec.parameters():
+            p.requires_grad = True
+    try:
+        emb_d, tax_d = emb.cuda(), tax_gt.cuda()
+        segs_d = [s.cuda().requires_grad_(True) for s in segs]
+        gl, gr = [t.cuda() for t in gt_left], [t.cuda() for t in gt_right]
+        n0 = sam.launch_count()
+        pl, pr, taxes, lows = _lisa_train_forward(sam, emb_d, segs_d, case)
+        losses = _lisa_losses(T, pl, pr, taxes, gl, gr, tax_d)
+        losses["loss"].backward()
+        torch.cuda.synchronize()
+        assert sam.launch_count() - n0 > 500          # the work was done by the library's kernels
+        for k in ("loss", "mask_bce_loss", "mask_dice_loss", "taxonomy_ce_loss"):
+            assert abs(float(losses[k].detach()) - float(ref[k])) <= 5e-5 * max(1.0, abs(float(ref[k]))), k
+            assert abs(float(losses[k].detach()) - float(g[k])) <= 5e-5 * max(1.0, abs(float(g[k]))), k   # the reference itself
+        _close(torch.cat([l[0] for l in lows]), ref["low_res_left"], "low_res_left")
+        _close(torch.cat([l[1] for l in lows]), ref["low_res_right"], "low_res_right")
+        _close(torch.cat(taxes), ref["taxonomy"], "taxonomy")
+        gmax = max(float(v.abs().max()) for v in ref["grads"].values() if v is not None)
+        for i, s in enumerate(segs_d):
+            _close(s.grad, ref["d_seg"][i], f"d_seg{i}")
+            _close(s.grad, torch.from_numpy(g[f"d_seg{i}"]), f"d_seg{i} vs reference")
+        named = dict(sam.named_parameters())
+        checked = 0
+        for name, gref in ref["grads"].items():
+            got = named[name].grad
+            if gref is None:
+                assert got is None or float(got.abs().max()) == 0.0, name
+                continue
+            assert got is not None, name
+            # per tensor, with a floor tied to the largest gradient of the step (shift-invariant biases are ~1e-10)
+            _close(got, gref, name, floor=1e-6 * gmax)
+            dg = TO.grad_digest(got.cpu())
+            rg = torch.from_numpy(g["g:" + name])
+            assert (dg[3:] - rg[3:]).abs().max() <= 3e-4 * float(rg[2]) + 1e-6 * gmax, name
+            checked += 1
+        assert checked > 100
+        for name, p in sam.named_parameters():
+            if not name.startswith("mask_decoder_"):
+                assert p.grad is None, name       # encoder / prompt encoder stay frozen
+
+        # the batched pass (all prompts of all frames at once) gives the same outputs and gradients
+        for p in sam.parameters():
+            p.grad = None
+        segs_b = [s.detach().clone().requires_grad_(True) for s in segs_d]
+        out = sam.train_decode(emb_d, segs_b)
+        assert out["offsets"] == [0, 2, 3]
+        _close(out["low_res_left"], ref["low_res_left"], "batched low_res_left")
+        _close(out["low_res_right"], ref["low_res_right"], "batched low_res_right")
+        _close(out["taxonomy"], ref["taxonomy"], "batched taxonomy")
+        pl2 = [sam.postprocess_masks(out["low_res_left"][a:b], case["resize"][i], case["original"][i])[:, 0]
+               for i, (a, b) in enumerate(zip(out["offsets"][:-1], out["offsets"][1:]))]
+        pr2 = [sam.postprocess_masks(out["low_res_right"][a:b], case["resize"][i], case["original"][i])[:, 0]
+               for i, (a, b) in enumerate(zip(out["offsets"][:-1], out["offsets"][1:]))]
+        tx2 = [out["taxonomy"][a:b] for a, b in zip(out["offsets"][:-1], out["offsets"][1:])]
+        l2 = _lisa_losses(T, pl2, pr2, tx2, gl, gr, tax_d)
+        l2["loss"].backward()
+        assert abs(float(l2["loss"].detach()) - float(ref["loss"])) <= 5e-5 * abs(float(ref["loss"]))
+        for i, s in enumerate(segs_b):
+            _close(s.grad, ref["d_seg"][i], f"batched d_seg{i}")
+        for name in ("mask_decoder_left.transformer.layers.1.cross_attn_image_to_token.q_proj.weight",
+                     "mask_decoder_right.output_upscaling.0.weight", "mask_decoder_left.taxonomy_embed.layers.0.weight",
+                     "mask_decoder_left.mask_tokens.weight"):
+            _close(named[name].grad, ref["grads"][name], "batched " + name, floor=1e-6 * gmax)
+
+        # an optimizer step on the decoders is picked up by the inference path (validate() between epochs)
+        with torch.no_grad():
+            for dec in (sam.mask_decoder_left, sam.mask_decoder_right):
+                for p in dec.parameters():
+                    if p.grad is not None:          # the IoU head is not reached by the loss
+                        p.add_(p.grad, alpha=-1e-3)
+            before = ref["low_res_left"][:2]
+            sam.mask_decoder_left.eval()
+            sparse, dense = sam.prompt_encoder(points=None, boxes=None, masks=None, text_embeds=segs_d[0].detach().unsqueeze(1))
+            ml, _, _ = sam.mask_decoder_left(image_embeddings=emb_d[0:1], image_pe=None, sparse_prompt_embeddings=sparse,
+                                             dense_prompt_embeddings=dense, multimask_output=False)
+            assert float((ml.cpu() - before).abs().max()) > 1e-4       # the weights moved and the library saw it
+    finally:
+        sam.load_state_dict(sd, strict=True)
+        for p in sam.parameters():
+            p.grad = None
+        sam.eval()
+
+
+def test_frozen_entry_points_still_refuse_grad(tiny):
+    sam, _, _ = tiny
+    frames = synth.make_frames(0, 1).cuda().requires_grad_(True)
+    with pytest.raises(NotImplementedError):
+        sam.image_encoder(frames)
+    emb = torch.zeros((1, 256, 64, 64), device="cuda", requires_grad=True)
+    sparse = torch.zeros((1, 1, 256), device="cuda", requires_grad=True)
+    with pytest.raises(NotImplementedError):
+        sam.mask_decoder_left(image_embeddings=emb, image_pe=None, sparse_prompt_embeddings=sparse,
+                              dense_prompt_embeddings=None, multimask_output=False)

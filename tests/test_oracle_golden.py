@@ -93,3 +93,38 @@ def test_postprocess_matches_formula_edges():
         torch.nn.functional.interpolate(low, (1024, 1024), mode="bilinear", align_corners=False)[..., :1024, :683],
         (1, 1), mode="bilinear", align_corners=False)
     assert torch.allclose(out, ref, atol=1e-5)
+
+
+def test_train_oracle_matches_reference_autograd(golden):
+    """oracle/train_oracle.py (restated forward + losses, torch.autograd on the CPU) against the unmodified
+    reference's training forward / backward (tests/golden/make_golden_train.py): losses, outputs, the gradient of
+    the [SEG] embeddings and the digest of every decoder parameter gradient."""
+    from oracle import train_oracle as TO
+    g = golden("train_tiny")
+    w = synth.make_state_dict(synth.ARCHS["tiny64"], seed=0)
+    emb, segs, gt_left, gt_right, tax = synth.make_train_inputs()
+    case = synth.TRAIN_CASE
+    r = TO.train_step(w, emb, segs, case["resize"], case["original"], gt_left, gt_right, tax)
+    for k in ("loss", "mask_bce_loss", "mask_dice_loss", "taxonomy_ce_loss"):
+        assert abs(float(r[k]) - float(g[k])) <= 2e-5 * max(1.0, abs(float(g[k]))), k
+    for k in ("low_res_left", "low_res_right", "taxonomy"):
+        assert O.logit_rel_err(r[k], torch.from_numpy(g[k])) < 2e-4, k
+    for i, d in enumerate(r["d_seg"]):
+        ref = torch.from_numpy(g[f"d_seg{i}"])
+        assert (d - ref).abs().max() <= 2e-4 * ref.abs().max() + 1e-9, i
+    names = [str(n) for n in g["param_names"]]
+    assert set(names) == set(r["grads"])
+    checked = 0
+    for n in names:
+        ref = torch.from_numpy(g["g:" + n])
+        got = r["grads"][n]
+        if ref.numel() == 0:          # not reached by the loss in the reference (IoU head)
+            assert got is None or float(got.abs().max()) == 0.0, n
+            continue
+        dg = TO.grad_digest(got)
+        scale = float(ref[2])         # max |grad|
+        assert (dg[3:] - ref[3:]).abs().max() <= 3e-4 * scale + 1e-7, n
+        # k_proj.bias gradients are mathematically zero (softmax is shift invariant): 1e-10 rounding noise both sides
+        assert abs(float(dg[1] - ref[1])) <= 3e-4 * float(ref[1]) + 1e-7, n
+        checked += 1
+    assert checked > 100
