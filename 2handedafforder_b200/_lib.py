@@ -47,6 +47,8 @@ SYMBOLS = [
     # include/b200sam_train.h (fp32 forward / backward primitives of the decoder training graph)
     ("b200sam_train_gemm", _I, [_P, _P, C.POINTER(_L), _P, C.POINTER(_L), _P, C.POINTER(_L), _P, _I, _I, _I, _I, _I, _I,
                                 _F, _F, _I, _P]),
+    ("b200sam_train_gemm_tc", _I, [_P, _P, _L, _P, _L, _P, _L, _P, _I, _I, _I, _I, _P]),
+    ("b200sam_train_transpose", _I, [_P, _P, _L, _I, _P, _P]),
     ("b200sam_train_layernorm_fwd", _I, [_P, _P, _P, _P, _L, _I, _F, _P, _P, _P, _P]),
     ("b200sam_train_layernorm_bwd", _I, [_P, _P, _P, _P, _P, _P, _L, _I, _P, _P, _P, _P]),
     ("b200sam_train_softmax_fwd", _I, [_P, _P, _L, _I, _P, _P]),

@@ -438,7 +438,17 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
       const long col = n0 + c * 32 + cg * 4;
       if constexpr (MODE == GM_F32) {
         if (has_add) add4(x, cur[i]);
-        if (st) *reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + orow[i] * (long)e.ld_out + col) = x;
+        float* op = reinterpret_cast<float*>(e.out) + orow[i] * (long)e.ld_out + col;
+        if (e.ksplit > 1) {          // partial product of one K range: combine in place
+          if (st) {
+            atomicAdd(op, x.x);
+            atomicAdd(op + 1, x.y);
+            atomicAdd(op + 2, x.z);
+            atomicAdd(op + 3, x.w);
+          }
+        } else if (st) {
+          *reinterpret_cast<float4*>(op) = x;
+        }
       } else if constexpr (MODE == GM_F16) {
         const float ws = (e.rowmap == RM_RELW_SHIFT && col >= 128) ? e.relw_scale : 1.f;
         bool hit = false;
@@ -500,8 +510,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int m_tiles = (M + kBM - 1) / kBM;
   const int n_tiles = (N + BN - 1) / BN;
   const int tiles_per_batch = m_tiles * n_tiles;
-  const int num_tiles = tiles_per_batch * e.batch;
   const int kblocks = (K + kBK - 1) / kBK;
+  // split-K (GM_F32, weight gradients of the training path): the "batch" index enumerates K ranges of kper blocks whose
+  // partial products are combined with fp32 atomics by the epilogue (the launcher guarantees no range is empty)
+  const bool ksplit = e.ksplit > 1;
+  const int kper = ksplit ? (kblocks + e.ksplit - 1) / e.ksplit : kblocks;
+  const int num_tiles = tiles_per_batch * (ksplit ? e.ksplit : e.batch);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -531,8 +545,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int bidx = tile / tiles_per_batch, trem = tile - bidx * tiles_per_batch;
         const int m_blk = trem / n_tiles, n_blk = trem % n_tiles;
-        const int a_col0 = bidx * e.a_batch_off;
-        for (int kb = 0; kb < kblocks; ++kb) {
+        const int a_col0 = ksplit ? 0 : bidx * e.a_batch_off;
+        const int kb0 = ksplit ? bidx * kper : 0, kb1 = ksplit ? min(kblocks, kb0 + kper) : kblocks;
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sA = smem + stage * Cfg::kStageBytes;
           uint8_t* sB = sA + kBM * 128;
@@ -564,7 +579,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_wait(&tmem_empty[as], aph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < kblocks; ++kb) {
+        const int ks = tile / tiles_per_batch;
+        const int kb0 = ksplit ? ks * kper : 0, kb1 = ksplit ? min(kblocks, kb0 + kper) : kblocks;
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t a0 = smem_u32(smem + stage * Cfg::kStageBytes);
@@ -572,7 +589,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
           for (int k = 0; k < 4; ++k) {   // 4 MMAs of K=16 (bf16) / K=8 (tf32): 32 bytes of K each
             umma_ss<kTf32>(d_tmem, umma_desc_sw128(a0 + k * 32), umma_desc_sw128(b0 + k * 32), kIdesc,
-                           (kb | k) != 0 ? 1u : 0u);
+                           (kb != kb0 || k != 0) ? 1u : 0u);
           }
           umma_commit(&empty[stage]);     // frees the smem slot when these MMAs retire
           if (++stage == kStages) {
@@ -601,7 +618,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const long row = (long)m_blk * kBM + ew * 32 + lane;
       if constexpr (kSplit)
         epilogue_warp<MODE, BN>(e, src, (long)m_blk * kBM + ew * 32, lane, M, N, n_blk * BN,
-                                (long)bidx * e.out_batch_off, eh, 2, wait_acc,
+                                ksplit ? 0L : (long)bidx * e.out_batch_off, eh, 2, wait_acc,
                                 reinterpret_cast<float4*>(smem + kStages * Cfg::kStageBytes + 256) + (warp - 4) * 256);
       else if (eh == 0)
         epilogue_row<MODE, BN>(e, src, row, M, N, n_blk * BN, (long)bidx * e.out_batch_off, 0, 1, wait_acc);
@@ -846,7 +863,7 @@ cudaError_t launch(const void* A, int lda, const void* W, int ldw, int M, int N,
   if (err != cudaSuccess) return err;
   err = make_tmap(&tmB, W, kTf32, N, K, ldw, BN);
   if (err != cudaSuccess) return err;
-  const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * e.batch;
+  const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * (e.ksplit > 1 ? e.ksplit : e.batch);
   const int n_sm = gemm_num_sms();
   const int grid = tiles < n_sm ? tiles : n_sm;
   gemm_tc_kernel<kTf32, MODE, BN><<<grid, kThreads, TileCfg<BN>::kSmemBytes, stream>>>(tmA, tmB, M, N, K, e);
@@ -933,9 +950,15 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
   if (e.batch != 1 && (mode != GM_F16 || tf32 || dbg || e.batch < 1)) return cudaErrorInvalidValue;
   if ((mode == GM_LN || mode == GM_UPS1) && N != 256) return cudaErrorInvalidValue;
   if (e.a_mode != AM_PLAIN && (dbg || tf32)) return cudaErrorInvalidValue;   // the SIMT bisect path reads a plain A
+  if (e.ksplit > 1) {
+    const int kblocks = (K + (tf32 ? 32 : 64) - 1) / (tf32 ? 32 : 64), kper = (kblocks + e.ksplit - 1) / e.ksplit;
+    if (mode != GM_F32 || dbg || e.batch != 1 || e.bias || e.addend || e.a_mode != AM_PLAIN || e.rowmap != RM_IDENT ||
+        (long)(e.ksplit - 1) * kper >= kblocks)      // every K range must hold at least one block
+      return cudaErrorInvalidValue;
+  }
   if (e.a_mode == AM_PATCH16 && !(e.batch == 1 && M >= 1024 && N % 256 == 0 && mode == GM_F32)) return cudaErrorInvalidValue;
   if (mode == GM_UPS2 && N != 128) return cudaErrorInvalidValue;
-  if (!tf32 && !dbg && e.batch == 1 && M >= 1024 && N % 256 == 0 && e.a_mode != AM_CONV3 &&
+  if (!tf32 && !dbg && e.batch == 1 && e.ksplit <= 1 && M >= 1024 && N % 256 == 0 && e.a_mode != AM_CONV3 &&
       (kernel_variant(VK_GEMM_PAIR) != 0 || e.a_mode == AM_PATCH16)) {
     switch (mode) {
       case GM_BIAS_BF16: return launch2<GM_BIAS_BF16>(A, lda, W, ldw, M, N, K, e, s);

@@ -60,6 +60,10 @@ struct GemmEpi {
   int batch = 1;
   int a_batch_off = 0;
   int out_batch_off = 0;
+  // GM_F32 only, > 1: the K range is cut into `ksplit` pieces computed by different CTAs and combined with fp32 atomicAdd
+  // into `out`, which the caller has zeroed (no bias / addend / rowmap / batch); every piece must be non-empty.  For
+  // products with a huge K and a small output (weight gradients: K = all rows of the batch).
+  int ksplit = 1;
 };
 
 // A: (M, K) row-major with leading dimension lda (elements); W: (N, K) row-major, ldw.

@@ -525,6 +525,20 @@ __global__ void __launch_bounds__(256) mask_loss_bwd_kernel(const float* __restr
   }
 }
 
+// y (cols, rows) = x (rows, cols)^T, 32 x 32 tiles through shared memory (both sides coalesced)
+__global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict__ x, long rows, int cols,
+                                                        float* __restrict__ y) {
+  __shared__ float tile[32][33];
+  const long r0 = (long)blockIdx.x * 32;
+  const int c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int j = ty; j < 32; j += 8)
+    if (r0 + j < rows && c0 + tx < cols) tile[j][tx] = x[(r0 + j) * cols + c0 + tx];
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8)
+    if (c0 + j < cols && r0 + tx < rows) y[(long)(c0 + j) * rows + r0 + tx] = tile[tx][j];
+}
+
 int tfail(b200sam_t* h, int code, const char* fmt, ...) {
   char buf[512];
   va_list ap;
@@ -775,4 +789,48 @@ extern "C" int b200sam_train_mask_loss_bwd(b200sam_t* h, const float* logits, co
   dim3 grid((unsigned)gx, P);
   mask_loss_bwd_kernel<<<grid, 256, 0, s>>>(logits, gt, weight, sums, g_bce, g_dice, hw, scale, eps, dlogits);
   T_DONE(1);
+}
+
+extern "C" int b200sam_train_transpose(b200sam_t* h, const float* x, int64_t rows, int cols, float* y, void* stream) {
+  T_ENTER();
+  if (!x || !y || rows < 0 || cols <= 0) return tfail(h, B200SAM_ERR_INVALID, "train_transpose: bad arguments");
+  if (rows == 0) return 0;
+  const long gx = (rows + 31) / 32;
+  if (gx > 0x7fffffffL || (cols + 31) / 32 > 65535) return tfail(h, B200SAM_ERR_INVALID, "train_transpose: too large");
+  dim3 grid((unsigned)gx, (unsigned)((cols + 31) / 32));
+  transpose_kernel<<<grid, 256, 0, s>>>(x, rows, cols, y);
+  T_DONE(1);
+}
+
+extern "C" int b200sam_train_gemm_tc(b200sam_t* h, const float* A, int64_t lda, const float* W, int64_t ldw, float* out,
+                                     int64_t ldo, const float* bias, int M, int N, int K, int split_k, void* stream) {
+  T_ENTER();
+  if (!A || !W || !out || M < 0 || N <= 0 || K <= 0 || N % 32 || K % 8 || lda < K || ldw < K || ldo < N ||
+      lda > 0x7fffffffL || ldw > 0x7fffffffL || ldo > 0x7fffffffL)
+    return tfail(h, B200SAM_ERR_INVALID, "train_gemm_tc: bad arguments (N %% 32 == 0, K %% 8 == 0)");
+  if (M == 0) return 0;
+  GemmEpi e;
+  e.out = out;
+  e.ld_out = (int)ldo;
+  int nl = 1;
+  if (split_k) {
+    // long reduction into a small output: one K range per CTA, about two CTAs per SM, combined with atomics
+    if (bias) return tfail(h, B200SAM_ERR_INVALID, "train_gemm_tc: split_k has no bias");
+    const int bn = N <= 128 ? 128 : 256;
+    const long tiles = (long)((M + 127) / 128) * ((N + bn - 1) / bn);
+    const int kblocks = (K + 31) / 32;
+    long want = (2L * gemm_num_sms() + tiles - 1) / tiles;
+    if (want > kblocks / 4) want = kblocks / 4;
+    if (want > 1) {
+      const int kper = (int)((kblocks + want - 1) / want);
+      e.ksplit = (kblocks + kper - 1) / kper;
+      if (cudaMemset2DAsync(out, (size_t)ldo * sizeof(float), 0, (size_t)N * sizeof(float), M, s) != cudaSuccess)
+        return tfail(h, B200SAM_ERR_CUDA, "train_gemm_tc: memset failed");
+      ++nl;
+    }
+  }
+  e.bias = bias;
+  cudaError_t err = gemm_tc(true, GM_F32, A, (int)lda, W, (int)ldw, M, N, K, e, s, false);
+  if (err != cudaSuccess) return tfail(h, B200SAM_ERR_CUDA, "train_gemm_tc: %s", cudaGetErrorString(err));
+  T_DONE(nl);
 }

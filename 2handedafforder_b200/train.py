@@ -66,10 +66,61 @@ def _check(rc: int, what: str) -> None:
 def _gemm(a: torch.Tensor, sa, b: torch.Tensor, sb, c: torch.Tensor, sc, nb1: int, nb2: int, m: int, n: int, k: int,
           alpha: float = 1.0, beta: float = 0.0, bias: Optional[torch.Tensor] = None, bias_mode: int = 0,
           relu: bool = False) -> None:
+    ev = None
+    if GEMM_PROFILE is not None:      # measurement aid (scripts/prof_train.py): device time per problem shape
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        ev[0].record()
     rc = _lib.load().b200sam_train_gemm(_Ctx.h(), _p(a), _I64x4(*sa), _p(b), _I64x4(*sb), _p(c), _I64x4(*sc), _p(bias),
                                         bias_mode, nb1, nb2, m, n, k, C.c_float(alpha), C.c_float(beta), int(relu),
                                         _stream())
     _check(rc, "train_gemm")
+    if ev is not None:
+        ev[1].record()
+        GEMM_PROFILE.append(((nb1 * nb2, m, n, k, tuple(sa[2:]), tuple(sb[2:]), tuple(sc[2:])), ev))
+
+
+# Arithmetic of the big Linear layers (rows >= TC_MIN_ROWS: the image-side projections over P * 4096 tokens and the two
+# ConvTranspose2d).  "tf32": tcgen05 tensor cores, TF32 operands, fp32 accumulation - above the reference's own training
+# precision (train_ds.py runs bf16 autocast) - for the forward, dX and dW.  "fp32": the exact SIMT kernel for
+# everything (bit-for-bit reproducible forward; used by the tight-tolerance parity tests).  Token-side layers (a few
+# rows) always run in fp32.
+_PRECISION = "tf32"
+TC_MIN_ROWS = 1024
+GEMM_PROFILE: Optional[list] = None
+
+
+def set_precision(mode: str) -> str:
+    """Select "tf32" (default) or "fp32" for the big Linear layers; returns the previous mode."""
+    global _PRECISION
+    if mode not in ("tf32", "fp32"):
+        raise ValueError("precision must be 'tf32' or 'fp32'")
+    prev, _PRECISION = _PRECISION, mode
+    return prev
+
+
+def _gemm_tc(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, bias: Optional[torch.Tensor] = None,
+             split_k: bool = False) -> None:
+    """out (M, N) = a (M, K) @ w (N, K)^T (+ bias) on the tensor cores; all row-major 2-D with unit column stride."""
+    M, K = a.shape
+    N = w.shape[0]
+    assert w.shape[1] == K and out.shape == (M, N) and a.stride(1) == 1 and w.stride(1) == 1 and out.stride(1) == 1
+    rc = _lib.load().b200sam_train_gemm_tc(_Ctx.h(), _p(a), a.stride(0), _p(w), w.stride(0), _p(out), out.stride(0),
+                                           _p(bias), M, N, K, int(split_k), _stream())
+    _check(rc, "train_gemm_tc")
+
+
+def _transpose(x: torch.Tensor) -> torch.Tensor:
+    """(rows, cols) contiguous -> (cols, rows) contiguous."""
+    rows, cols = x.shape
+    assert x.is_contiguous()
+    y = torch.empty((cols, rows), dtype=torch.float32, device=x.device)
+    _check(_lib.load().b200sam_train_transpose(_Ctx.h(), _p(x), rows, cols, _p(y), _stream()), "train_transpose")
+    return y
+
+
+def _tc_ok(rows: int, K: int, N: int, *tensors: torch.Tensor) -> bool:
+    return (_PRECISION == "tf32" and rows >= TC_MIN_ROWS and rows % 8 == 0 and K % 32 == 0 and N % 32 == 0
+            and all(t.data_ptr() % 16 == 0 for t in tensors))
 
 
 def _mm4(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, alpha: float = 1.0) -> None:
@@ -112,22 +163,28 @@ class LinearFn(torch.autograd.Function):
         assert x2.data_ptr() == x.data_ptr(), "linear input must be viewable as rows without a copy"
         rows = x2.shape[0]
         y = torch.empty((rows, N), dtype=torch.float32, device=x.device)
-        sb = (0, 0, N, 1) if w_kn else (0, 0, 1, K)
-        _gemm(x2, (0, 0, x2.stride(0), 1), w, sb, y, (0, 0, N, 1), 1, 1, rows, N, K, bias=b,
-              bias_mode=1 if b is not None else 0, relu=relu)
+        tc = (not relu) and x2.stride(0) == K and _tc_ok(rows, K, N, x2, w)
+        if tc:
+            _gemm_tc(x2, _transpose(w) if w_kn else w, y, b)
+        else:
+            sb = (0, 0, N, 1) if w_kn else (0, 0, 1, K)
+            _gemm(x2, (0, 0, x2.stride(0), 1), w, sb, y, (0, 0, N, 1), 1, 1, rows, N, K, bias=b,
+                  bias_mode=1 if b is not None else 0, relu=relu)
         ctx.save_for_backward(x2, w, y if relu else None)
-        ctx.cfg = (relu, w_kn, tuple(x.shape[:-1]), b is not None)
+        ctx.cfg = (relu, w_kn, tuple(x.shape[:-1]), b is not None, tc)
         return y.view(*x.shape[:-1], N)
 
     @staticmethod
     def backward(ctx, dy):
         x2, w, y = ctx.saved_tensors
-        relu, w_kn, lead, has_b = ctx.cfg
+        relu, w_kn, lead, has_b, tc = ctx.cfg
         rows, K = x2.shape
         N = w.shape[1] if w_kn else w.shape[0]
         dy = dy.reshape(rows, N)
         if not dy.is_contiguous():
             dy = dy.contiguous()
+        if tc and dy.data_ptr() % 16:
+            dy = dy.clone()
         if relu:
             d2 = torch.empty_like(dy)
             _check(_lib.load().b200sam_train_act_bwd(_Ctx.h(), 0, _p(dy), _p(y), dy.numel(), _p(d2), _stream()),
@@ -137,12 +194,21 @@ class LinearFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = torch.empty((rows, K), dtype=torch.float32, device=dy.device)
             # dx = dy W (N,K)  /  dy W^T for the (K,N) storage
-            sb = (0, 0, 1, N) if w_kn else (0, 0, K, 1)
-            _gemm(dy, (0, 0, N, 1), w, sb, dx, (0, 0, K, 1), 1, 1, rows, K, N)
+            if tc:      # the tensor-core kernel wants the second operand as (out features, contraction) rows
+                _gemm_tc(dy, w if w_kn else _transpose(w), dx)
+            else:
+                sb = (0, 0, 1, N) if w_kn else (0, 0, K, 1)
+                _gemm(dy, (0, 0, N, 1), w, sb, dx, (0, 0, K, 1), 1, 1, rows, K, N)
             dx = dx.view(*lead, K)
         if ctx.needs_input_grad[1]:
             dw = torch.empty_like(w)
-            if w_kn:    # dW (K,N) = x^T dy
+            if tc:      # contraction over the rows: both operands transposed once, K split over the CTAs
+                dyt, xt = _transpose(dy), _transpose(x2)
+                if w_kn:
+                    _gemm_tc(xt, dyt, dw, split_k=True)       # dW (K,N) = x^T dy
+                else:
+                    _gemm_tc(dyt, xt, dw, split_k=True)       # dW (N,K) = dy^T x
+            elif w_kn:    # dW (K,N) = x^T dy
                 _gemm(x2, (0, 0, 1, x2.stride(0)), dy, (0, 0, N, 1), dw, (0, 0, N, 1), 1, 1, K, N, rows)
             else:       # dW (N,K) = dy^T x
                 _gemm(dy, (0, 0, 1, N), x2, (0, 0, x2.stride(0), 1), dw, (0, 0, K, 1), 1, 1, N, K, rows)

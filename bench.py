@@ -549,10 +549,27 @@ def run_gpu_arm(args):
         aux = measure_callers(torch, sam, dev, out_u8, B, NP)
         del out_u8
 
+    sd_cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        sd_cpu = {k: v.detach().float().cpu() for k, v in sam.state_dict().items()}
+
+    # ---- the trainable part of the branch (both decoders forward + backward, postprocess, mask
+    # losses) for the same 8 frames x 3 prompts; an extra key, not part of the headline metric
+    train = None
+    if rank == 0 and world == 1 and not args.no_train:
+        import types
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        bench_train = __import__("bench_train")
+        del sam
+        torch.cuda.empty_cache()
+        train = bench_train.run(types.SimpleNamespace(
+            frames=B, prompts=NP, steps=3, warmup=2, original=list(original[0]), no_eager=args.no_cpu_baseline,
+            precision="tf32", cpu_sample=0 if args.no_cpu_baseline else 1))
+        sam = None
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        sd = {k: v.detach().float().cpu() for k, v in sam.state_dict().items()}
-        cpu = cpu_baseline_block(torch, sd, NP)
+        cpu = cpu_baseline_block(torch, sd_cpu, NP)
 
     if rank == 0:
         line = {
@@ -563,6 +580,7 @@ def run_gpu_arm(args):
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "kernels": kernels, "callers": aux, "latency_b1_ms": latency, "gather_verified": gather_verified,
+            "train_step": train,
         }
         print(json.dumps(line))
     if world > 1:
@@ -579,6 +597,7 @@ def main():
     ap.add_argument("--batch", type=int, default=8, help="frames per step per GPU (configs[1]: 8)")
     ap.add_argument("--prompts", type=int, default=3, help="[SEG] prompts per frame")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the decoder-training timing (extra key train_step)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)

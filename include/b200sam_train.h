@@ -31,6 +31,17 @@ int b200sam_train_gemm(b200sam_t* h, const float* A, const int64_t* sa, const fl
                        const int64_t* sc, const float* bias, int bias_mode, int nb1, int nb2, int M, int N, int K,
                        float alpha, float beta, int relu, void* stream);
 
+/* out (M x N, row pitch ldo) = A (M x K, pitch lda) * W^T (W: N x K, pitch ldw) (+ bias[n]) on the tensor cores
+ * (tcgen05, TF32 operands, fp32 accumulation in TMEM; the TMA-fed kernel of the inference decoder).  N % 32 == 0,
+ * K % 8 == 0, 16-byte aligned rows.  The image-side Linear layers (rows = P * 4096) and both ConvTranspose2d use it
+ * for the forward, the input gradient (W^T supplied transposed) and - with split_k != 0: K cut into one range per
+ * CTA, partial products combined with fp32 atomics, no bias - the weight gradient dW = dY^T X on transposed copies. */
+int b200sam_train_gemm_tc(b200sam_t* h, const float* A, int64_t lda, const float* W, int64_t ldw, float* out,
+                          int64_t ldo, const float* bias, int M, int N, int K, int split_k, void* stream);
+
+/* y (cols x rows) = x (rows x cols)^T. */
+int b200sam_train_transpose(b200sam_t* h, const float* x, int64_t rows, int cols, float* y, void* stream);
+
 /* nn.LayerNorm over the last dimension (transformer.py:97-107; LayerNorm2d of common.py:31-43 on channels-last
  * rows).  C % 32 == 0, C <= 1024.  Saves mean / rstd per row for the backward.  dgamma / dbeta are overwritten. */
 int b200sam_train_layernorm_fwd(b200sam_t* h, const float* x, const float* gamma, const float* beta, int64_t rows,

@@ -189,7 +189,7 @@ def encode(w: W, arch: Arch, frames: torch.Tensor, prec: Precision = FP32,
 def dense_pe(w: W) -> torch.Tensor:
     """PromptEncoder.get_dense_pe (prompt_encoder.py:67-76, 203-229) -> (1,256,64,64)."""
     G = w["prompt_encoder.pe_layer.positional_encoding_gaussian_matrix"]
-    c = (torch.arange(GRID, dtype=torch.float32) + 0.5) / GRID
+    c = (torch.arange(GRID, dtype=torch.float32, device=G.device) + 0.5) / GRID
     xy = torch.stack([c[None, :].expand(GRID, GRID), c[:, None].expand(GRID, GRID)], dim=-1)
     ang = (2.0 * math.pi) * ((2.0 * xy - 1.0) @ G)
     return torch.cat([torch.sin(ang), torch.cos(ang)], dim=-1).permute(2, 0, 1)[None]
@@ -303,13 +303,13 @@ def decode(w: W, side: str, emb: torch.Tensor, seg_embeds: torch.Tensor,
 
 # --------------------------------------------------------------------------- postprocess
 
-def _bilinear_axis(n_in: int, n_out: int):
+def _bilinear_axis(n_in: int, n_out: int, device=None):
     """ATen upsample_bilinear2d source index, align_corners=False (sam.py:177-189).
 
     src = max(0, (dst + 0.5) * in/out - 0.5); i0 = floor; i1 = min(i0+1, in-1); lam = src - i0.
     """
-    scale = torch.tensor(n_in / n_out, dtype=torch.float32)
-    dst = torch.arange(n_out, dtype=torch.float32)
+    scale = torch.tensor(n_in / n_out, dtype=torch.float32, device=device)
+    dst = torch.arange(n_out, dtype=torch.float32, device=device)
     src = torch.clamp(scale * (dst + 0.5) - 0.5, min=0.0)
     i0 = src.floor().long().clamp(max=n_in - 1)
     i1 = torch.clamp(i0 + 1, max=n_in - 1)
@@ -320,8 +320,8 @@ def _bilinear_axis(n_in: int, n_out: int):
 def bilinear_resize(x: torch.Tensor, out_hw: Tuple[int, int]) -> torch.Tensor:
     """F.interpolate(x, out_hw, mode='bilinear', align_corners=False) on (..., H, W)."""
     H, Wd = x.shape[-2:]
-    y0, y1, ly = _bilinear_axis(H, int(out_hw[0]))
-    x0, x1, lx = _bilinear_axis(Wd, int(out_hw[1]))
+    y0, y1, ly = _bilinear_axis(H, int(out_hw[0]), x.device)
+    x0, x1, lx = _bilinear_axis(Wd, int(out_hw[1]), x.device)
     top, bot = x[..., y0, :], x[..., y1, :]
     def lerp_x(r):
         return (1.0 - lx) * r[..., x0] + lx * r[..., x1]

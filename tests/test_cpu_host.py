@@ -115,3 +115,30 @@ def test_product_package_never_imports_oracle():
         for f in files:
             if f.endswith((".py", ".cu", ".cuh")):
                 assert "oracle" not in open(os.path.join(root, f)).read().replace("the oracle", ""), f
+
+
+def test_training_module_has_no_cpu_path():
+    """2handedafforder_b200/train.py composes CUDA primitives only: CPU tensors are refused by type, and nothing runs
+    before a library handle is bound (no PyTorch implementation of any node to fall back to)."""
+    T = importlib.import_module(G.PKG + ".train")
+    x, w = torch.randn(4, 32), torch.randn(8, 32)
+    with pytest.raises(TypeError, match="CUDA float32"):
+        T.linear(x, w)
+    with pytest.raises(TypeError, match="CUDA float32"):
+        T.softmax(x)
+    with pytest.raises(ValueError):
+        T.set_precision("bf16")
+    assert T.set_precision("fp32") in ("tf32", "fp32")
+    assert T.set_precision("tf32") == "fp32"
+    if not torch.cuda.is_available():
+        saved = T._Ctx.handle
+        T._Ctx.handle = None
+        try:
+            with pytest.raises(RuntimeError, match="before a B200Sam handle was bound"):
+                T._check(0, "x")
+        finally:
+            T._Ctx.handle = saved
+    # layout helper: a dense permutation keeps its strides, anything else becomes contiguous
+    t = torch.empty(2, 3, 4, 5).permute(0, 2, 3, 1)
+    assert T._empty_like_layout(t).stride() == t.stride()
+    assert T._empty_like_layout(torch.empty(4, 6)[:, ::2]).is_contiguous()

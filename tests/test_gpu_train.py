@@ -5,8 +5,15 @@ facade in train() mode, postprocess_masks under autograd, the mask losses of LIS
 oracle/train_oracle.py (pinned to the unmodified reference by tests/golden/train_tiny.npz): losses, outputs, the gradient
 of the [SEG] embeddings and of EVERY decoder parameter.
 
-Tolerance (floating point, stated here): fp32 kernels vs an fp32 CPU reference differ by summation order only, so
-max |got - ref| <= 2e-4 * max |ref| + 1e-7 per tensor (the observed error is ~1e-5 relative)."""
+Tolerance (floating point, stated here).  precision "fp32" (every node an fp32 kernel): only the summation order
+differs from the fp32 CPU reference, so max |got - ref| <= 2e-4 * max |ref| + 1e-7 per tensor (observed ~1e-5).
+precision "tf32" (the default: the image-side Linear layers and both ConvTranspose2d on the tensor cores with TF32
+operands, fp32 accumulation - above the bf16 autocast the reference trains in): outputs within 1e-2 * max |ref|,
+gradients within 6e-2 * max |ref| per tensor (observed: low-res logits 1e-3, parameter gradients <= 2e-2, the [SEG]
+gradient of the 1-prompt frame 3.4e-2 - a small gradient that passes through every TF32 layer twice); the observed
+maxima are written to gpurun_out/train_parity.json."""
+import json
+import os
 import math
 
 import numpy as np
@@ -21,13 +28,18 @@ from tests import gpu_util as G
 pytestmark = pytest.mark.gpu
 
 TOL = 2e-4
+TOL_TF32_OUT, TOL_TF32_GRAD = 1e-2, 6e-2
+OBSERVED = {}
 
 
-def _close(got, ref, what, tol=TOL, floor=1e-7):
+def _close(got, ref, what, tol=TOL, floor=1e-7, record=None):
     got, ref = got.detach().float().cpu(), ref.detach().float().cpu()
     assert got.shape == ref.shape, (what, got.shape, ref.shape)
     err = float((got - ref).abs().max())
     lim = tol * float(ref.abs().max()) + floor
+    if record is not None:
+        rel = err / max(float(ref.abs().max()), 1e-30)
+        OBSERVED[record] = max(OBSERVED.get(record, 0.0), rel if err > floor else 0.0)
     assert err <= lim, f"{what}: max err {err:.3e} > {lim:.3e}"
 
 
@@ -46,8 +58,17 @@ def _rand(*shape, seed=0, grad=True):
 @pytest.mark.parametrize("rows,K,N,relu,w_kn", [(6, 256, 128, False, False), (3 * 4096, 256, 128, False, False),
                                                 (18, 256, 2048, True, False), (2 * 4096, 256, 256, False, True),
                                                 (5, 1024, 4, False, False), (8192, 64, 128, False, True)])
-def test_linear_forward_backward(tiny, rows, K, N, relu, w_kn):
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+def test_linear_forward_backward(tiny, rows, K, N, relu, w_kn, prec):
     _, _, T = tiny
+    prev = T.set_precision(prec)
+    try:
+        _linear_case(T, rows, K, N, relu, w_kn, TOL if prec == "fp32" else 4e-3)
+    finally:
+        T.set_precision(prev)
+
+
+def _linear_case(T, rows, K, N, relu, w_kn, tol):
     x = _rand(rows, K, seed=1)
     w = _rand(*((K, N) if w_kn else (N, K)), seed=2)
     w.data.mul_(1.0 / math.sqrt(K))
@@ -59,9 +80,9 @@ def test_linear_forward_backward(tiny, rows, K, N, relu, w_kn):
     yr = xr @ wr + br if w_kn else F.linear(xr, wr, br)
     yr = torch.relu(yr) if relu else yr
     yr.backward(dy)
-    _close(y, yr, "y")
-    _close(x.grad, xr.grad, "dx")
-    _close(w.grad, wr.grad, "dw")     # rows = 12288: the split-K path with atomics
+    _close(y, yr, "y", tol=tol)
+    _close(x.grad, xr.grad, "dx", tol=tol)
+    _close(w.grad, wr.grad, "dw", tol=tol)     # rows >= 8192: split-K with atomics (SIMT fp32 / tcgen05 TF32)
     _close(b.grad, br.grad, "db")
 
 
@@ -141,6 +162,14 @@ def test_gelu_add_fork_pixel_shuffle(tiny):
 def test_conv_transpose_as_linear_plus_shuffle(tiny):
     """ConvTranspose2d(k=2, s=2) (mask_decoder.py:52-61) = Linear with the flat (C_in, C_out*4) weight + pixel shuffle."""
     _, _, T = tiny
+    prev = T.set_precision("fp32")
+    try:
+        _conv_transpose_case(T)
+    finally:
+        T.set_precision(prev)
+
+
+def _conv_transpose_case(T):
     ci, co, n = 64, 32, 2
     x = _rand(n, 32, 32, ci, seed=1)
     w, b = _rand(ci, co, 2, 2, seed=2), _rand(co, seed=3)
@@ -233,8 +262,23 @@ def _lisa_losses(T, pl, pr, taxes, gt_left, gt_right, tax_gt):
     return {"mask_bce_loss": bce, "mask_dice_loss": dice, "taxonomy_ce_loss": tce, "loss": bce + dice + tce}
 
 
-def test_training_step_matches_oracle_and_reference_golden(tiny, golden):
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+def test_training_step_matches_oracle_and_reference_golden(tiny, golden, prec):
     sam, sd, T = tiny
+    prev = T.set_precision(prec)
+    try:
+        _training_step_case(sam, sd, T, golden, prec)
+    finally:
+        T.set_precision(prev)
+        os.makedirs(os.path.join(G.ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(G.ROOT, "gpurun_out", "train_parity.json"), "w") as fh:
+            json.dump({"max_relative_error_vs_fp32_cpu_oracle": OBSERVED}, fh, indent=1, sort_keys=True)
+
+
+def _training_step_case(sam, sd, T, golden, prec):
+    t_out = TOL if prec == "fp32" else TOL_TF32_OUT
+    t_grad = TOL if prec == "fp32" else TOL_TF32_GRAD
+    t_loss = 5e-5 if prec == "fp32" else 2e-3
     case = synth.TRAIN_CASE
     emb, segs, gt_left, gt_right, tax_gt = synth.make_train_inputs()
     ref = TO.train_step(sd, emb, segs, case["resize"], case["original"], gt_left, gt_right, tax_gt)
@@ -259,15 +303,15 @@ def test_training_step_matches_oracle_and_reference_golden(tiny, golden):
         torch.cuda.synchronize()
         assert sam.launch_count() - n0 > 500          # the work was done by the library's kernels
         for k in ("loss", "mask_bce_loss", "mask_dice_loss", "taxonomy_ce_loss"):
-            assert abs(float(losses[k].detach()) - float(ref[k])) <= 5e-5 * max(1.0, abs(float(ref[k]))), k
-            assert abs(float(losses[k].detach()) - float(g[k])) <= 5e-5 * max(1.0, abs(float(g[k]))), k   # the reference itself
-        _close(torch.cat([l[0] for l in lows]), ref["low_res_left"], "low_res_left")
-        _close(torch.cat([l[1] for l in lows]), ref["low_res_right"], "low_res_right")
-        _close(torch.cat(taxes), ref["taxonomy"], "taxonomy")
+            assert abs(float(losses[k].detach()) - float(ref[k])) <= t_loss * max(1.0, abs(float(ref[k]))), k
+            assert abs(float(losses[k].detach()) - float(g[k])) <= t_loss * max(1.0, abs(float(g[k]))), k   # the reference itself
+        _close(torch.cat([l[0] for l in lows]), ref["low_res_left"], "low_res_left", tol=t_out, record=prec + ":low_res")
+        _close(torch.cat([l[1] for l in lows]), ref["low_res_right"], "low_res_right", tol=t_out, record=prec + ":low_res")
+        _close(torch.cat(taxes), ref["taxonomy"], "taxonomy", tol=t_out, record=prec + ":taxonomy")
         gmax = max(float(v.abs().max()) for v in ref["grads"].values() if v is not None)
         for i, s in enumerate(segs_d):
-            _close(s.grad, ref["d_seg"][i], f"d_seg{i}")
-            _close(s.grad, torch.from_numpy(g[f"d_seg{i}"]), f"d_seg{i} vs reference")
+            _close(s.grad, ref["d_seg"][i], f"d_seg{i}", tol=t_grad, record=prec + ":d_seg")
+            _close(s.grad, torch.from_numpy(g[f"d_seg{i}"]), f"d_seg{i} vs reference", tol=t_grad)
         named = dict(sam.named_parameters())
         checked = 0
         for name, gref in ref["grads"].items():
@@ -277,10 +321,10 @@ def test_training_step_matches_oracle_and_reference_golden(tiny, golden):
                 continue
             assert got is not None, name
             # per tensor, with a floor tied to the largest gradient of the step (shift-invariant biases are ~1e-10)
-            _close(got, gref, name, floor=1e-6 * gmax)
+            _close(got, gref, name, tol=t_grad, floor=1e-6 * gmax, record=prec + ":param_grads")
             dg = TO.grad_digest(got.cpu())
             rg = torch.from_numpy(g["g:" + name])
-            assert (dg[3:] - rg[3:]).abs().max() <= 3e-4 * float(rg[2]) + 1e-6 * gmax, name
+            assert (dg[3:] - rg[3:]).abs().max() <= max(3e-4, t_grad) * float(rg[2]) + 1e-6 * gmax, name
             checked += 1
         assert checked > 100
         for name, p in sam.named_parameters():
@@ -293,9 +337,9 @@ def test_training_step_matches_oracle_and_reference_golden(tiny, golden):
         segs_b = [s.detach().clone().requires_grad_(True) for s in segs_d]
         out = sam.train_decode(emb_d, segs_b)
         assert out["offsets"] == [0, 2, 3]
-        _close(out["low_res_left"], ref["low_res_left"], "batched low_res_left")
-        _close(out["low_res_right"], ref["low_res_right"], "batched low_res_right")
-        _close(out["taxonomy"], ref["taxonomy"], "batched taxonomy")
+        _close(out["low_res_left"], ref["low_res_left"], "batched low_res_left", tol=t_out)
+        _close(out["low_res_right"], ref["low_res_right"], "batched low_res_right", tol=t_out)
+        _close(out["taxonomy"], ref["taxonomy"], "batched taxonomy", tol=t_out)
         pl2 = [sam.postprocess_masks(out["low_res_left"][a:b], case["resize"][i], case["original"][i])[:, 0]
                for i, (a, b) in enumerate(zip(out["offsets"][:-1], out["offsets"][1:]))]
         pr2 = [sam.postprocess_masks(out["low_res_right"][a:b], case["resize"][i], case["original"][i])[:, 0]
@@ -303,13 +347,13 @@ def test_training_step_matches_oracle_and_reference_golden(tiny, golden):
         tx2 = [out["taxonomy"][a:b] for a, b in zip(out["offsets"][:-1], out["offsets"][1:])]
         l2 = _lisa_losses(T, pl2, pr2, tx2, gl, gr, tax_d)
         l2["loss"].backward()
-        assert abs(float(l2["loss"].detach()) - float(ref["loss"])) <= 5e-5 * abs(float(ref["loss"]))
+        assert abs(float(l2["loss"].detach()) - float(ref["loss"])) <= t_loss * abs(float(ref["loss"]))
         for i, s in enumerate(segs_b):
-            _close(s.grad, ref["d_seg"][i], f"batched d_seg{i}")
+            _close(s.grad, ref["d_seg"][i], f"batched d_seg{i}", tol=t_grad)
         for name in ("mask_decoder_left.transformer.layers.1.cross_attn_image_to_token.q_proj.weight",
                      "mask_decoder_right.output_upscaling.0.weight", "mask_decoder_left.taxonomy_embed.layers.0.weight",
                      "mask_decoder_left.mask_tokens.weight"):
-            _close(named[name].grad, ref["grads"][name], "batched " + name, floor=1e-6 * gmax)
+            _close(named[name].grad, ref["grads"][name], "batched " + name, tol=t_grad, floor=1e-6 * gmax)
 
         # an optimizer step on the decoders is picked up by the inference path (validate() between epochs)
         with torch.no_grad():
