@@ -44,31 +44,35 @@ struct GemmStrides {
 constexpr int kGT = 64;    // tile edge
 constexpr int kGK = 16;    // K step
 
-// 256 threads; each owns a 4 x 4 block of the 64 x 64 output tile.  Tiles of A (64 x 16) and B (16 x 64) are staged
-// through shared memory with the thread -> element map chosen so that the unit-stride dimension of each operand is the
-// fastest-varying one across a warp (coalesced whatever the transposition).
+// 256 threads; each owns a TM x 4 block of the BM x 64 output tile (BM = 64: TM = 4; BM = 16: TM = 1, for the thin
+// products of the decoder's attention - 6 tokens against 4096 - where a 64-row tile would be 90 % padding).  Tiles of A
+// (BM x 16) and B (16 x 64) are staged through shared memory with the thread -> element map chosen so that the
+// unit-stride dimension of each operand is the fastest-varying one across a warp (coalesced whatever the transposition).
+template <int BM>
 __global__ void __launch_bounds__(256) gemm_strided_kernel(const float* __restrict__ A, GemmStrides sa,
                                                            const float* __restrict__ B, GemmStrides sb,
                                                            float* __restrict__ Cm, GemmStrides sc,
                                                            const float* __restrict__ bias, int bias_mode, int nb2, int M,
                                                            int N, int K, float alpha, float beta, int relu, int ksplit) {
-  __shared__ float As[kGK][kGT + 4];
-  __shared__ float Bs[kGK][kGT + 4];
+  constexpr int TM = BM / 16;
+  constexpr int kALoads = BM * kGK / 256;      // 4 or 1 elements of the A tile per thread
+  __shared__ __align__(16) float As[kGK][BM + 4];
+  __shared__ __align__(16) float Bs[kGK][kGT + 4];
   const int bz = blockIdx.z / ksplit, ks = blockIdx.z - bz * ksplit;
   const int b1 = bz / nb2, b2 = bz - b1 * nb2;
   A += b1 * sa.b1 + b2 * sa.b2;
   B += b1 * sb.b1 + b2 * sb.b2;
   Cm += b1 * sc.b1 + b2 * sc.b2;
-  const int m0 = blockIdx.y * kGT, n0 = blockIdx.x * kGT;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * kGT;
   const int t = threadIdx.x;
-  const int tm = (t >> 4) * 4, tn = (t & 15) * 4;
+  const int tm = (t >> 4) * TM, tn = (t & 15) * 4;
   // K range of this split (multiples of kGK)
   const int ktiles = (K + kGK - 1) / kGK;
   const int per = (ktiles + ksplit - 1) / ksplit;
   const int kt0 = ks * per, kt1 = min(ktiles, kt0 + per);
-  float acc[4][4];
+  float acc[TM][4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < TM; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
   const bool a_kfast = sa.c == 1 || sa.r != 1;   // A(m, k): k contiguous (or neither): lanes walk k
@@ -76,15 +80,15 @@ __global__ void __launch_bounds__(256) gemm_strided_kernel(const float* __restri
   for (int kt = kt0; kt < kt1; ++kt) {
     const int k0 = kt * kGK;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < kALoads; ++i) {
       const int e = t + i * 256;
       int m, k;
       if (a_kfast) {
         m = e >> 4;
         k = e & 15;
       } else {
-        m = e & 63;
-        k = e >> 6;
+        m = e % BM;
+        k = e / BM;
       }
       float v = 0.f;
       if (m0 + m < M && k0 + k < K) v = A[(long)(m0 + m) * sa.r + (long)(k0 + k) * sa.c];
@@ -108,18 +112,25 @@ __global__ void __launch_bounds__(256) gemm_strided_kernel(const float* __restri
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < kGK; ++k) {
-      const float4 a = *reinterpret_cast<const float4*>(&As[k][tm]);
-      const float4 b = *reinterpret_cast<const float4*>(&Bs[k][tn]);
-      const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+      float av[TM];
+      if constexpr (TM == 4) {
+        const float4 a = *reinterpret_cast<const float4*>(&As[k][tm]);
+        av[0] = a.x, av[1] = a.y, av[2] = a.z, av[3] = a.w;
+      } else {
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < TM; ++i) av[i] = As[k][tm + i];
+      }
+      const float4 b = *reinterpret_cast<const float4*>(&Bs[k][tn]);
+      const float bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
     }
     __syncthreads();
   }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < TM; ++i) {
     const int m = m0 + tm + i;
     if (m >= M) continue;
 #pragma unroll
@@ -597,7 +608,25 @@ extern "C" int b200sam_train_gemm(b200sam_t* h, const float* A, const int64_t* s
   if (nb == 0 || M == 0 || N == 0) return 0;
   if (nb > 65535L) return tfail(h, B200SAM_ERR_INVALID, "train_gemm: too many batches");
   GemmStrides a{sa[0], sa[1], sa[2], sa[3]}, b{sb[0], sb[1], sb[2], sb[3]}, c{sc[0], sc[1], sc[2], sc[3]};
-  const int tx = (N + kGT - 1) / kGT, ty = (M + kGT - 1) / kGT;
+  // thin products: put the small dimension on the rows (C^T = B^T A^T is the same kernel with the operands and the
+  // row / column strides exchanged) and use the 16-row tile
+  if (N <= 16 && M > N) {
+    const float* tp = A;
+    A = B;
+    B = tp;
+    GemmStrides na{b.b1, b.b2, b.c, b.r}, nb_{a.b1, a.b2, a.c, a.r};
+    a = na;
+    b = nb_;
+    const long t2 = c.r;
+    c.r = c.c;
+    c.c = t2;
+    const int t3 = M;
+    M = N;
+    N = t3;
+    if (bias_mode) bias_mode = 3 - bias_mode;
+  }
+  const int bm = M <= 16 ? 16 : kGT;
+  const int tx = (N + kGT - 1) / kGT, ty = (M + bm - 1) / bm;
   const long tiles = (long)tx * ty * nb;
   const int ktiles = (K + kGK - 1) / kGK;
   // split K when the output has too few tiles to fill the machine and the reduction is long (weight gradients)
@@ -608,6 +637,7 @@ extern "C" int b200sam_train_gemm(b200sam_t* h, const float* A, const int64_t* s
     if (nb * want > 65535) want = 65535 / nb;
     if (want > 1) ksplit = (int)want;
   }
+  if (ty > 65535) return tfail(h, B200SAM_ERR_INVALID, "train_gemm: too many row tiles");
   int nl = 1;
   if (ksplit > 1) {
     dim3 g((unsigned)(((long)M * N + 255) / 256), 1, (unsigned)nb);
@@ -615,7 +645,10 @@ extern "C" int b200sam_train_gemm(b200sam_t* h, const float* A, const int64_t* s
     ++nl;
   }
   dim3 grid(tx, ty, (unsigned)(nb * ksplit));
-  gemm_strided_kernel<<<grid, 256, 0, s>>>(A, a, B, b, Cm, c, bias, bias_mode, nb2, M, N, K, alpha, beta, relu, ksplit);
+  if (bm == 16)
+    gemm_strided_kernel<16><<<grid, 256, 0, s>>>(A, a, B, b, Cm, c, bias, bias_mode, nb2, M, N, K, alpha, beta, relu, ksplit);
+  else
+    gemm_strided_kernel<64><<<grid, 256, 0, s>>>(A, a, B, b, Cm, c, bias, bias_mode, nb2, M, N, K, alpha, beta, relu, ksplit);
   T_DONE(nl);
 }
 

@@ -9,9 +9,13 @@ Tolerance (floating point, stated here).  precision "fp32" (every node an fp32 k
 differs from the fp32 CPU reference, so max |got - ref| <= 2e-4 * max |ref| + 1e-7 per tensor (observed ~1e-5).
 precision "tf32" (the default: the image-side Linear layers and both ConvTranspose2d on the tensor cores with TF32
 operands, fp32 accumulation - above the bf16 autocast the reference trains in): outputs within 1e-2 * max |ref|,
-gradients within 6e-2 * max |ref| per tensor (observed: low-res logits 1e-3, parameter gradients <= 2e-2, the [SEG]
-gradient of the 1-prompt frame 3.4e-2 - a small gradient that passes through every TF32 layer twice); the observed
-maxima are written to gpurun_out/train_parity.json."""
+gradients within 6e-2 * max |ref| + 3e-2 * (largest gradient of the step) per tensor.  Observed: low-res logits 1e-3, the
+[SEG] gradients 3.4e-2, parameter gradients <= 2.2 % of the largest gradient - the ill-conditioned ones (layer-0 MLP, the
+hypernetwork MLPs behind a 65536-long contraction with the TF32-rounded upscaled embedding) move by 10-18 % of their own
+small maximum.  The reference's own bf16 autocast moves the same tensors by 41-47 % of their own maximum = 6.5 % of the
+largest gradient, and the [SEG] gradients by 5.6-8.3 % (profiles/r4_train_precision_context.json).  precision "fp32" is
+the bug detector; the tf32 run checks that the faster arithmetic stays well inside the reference's own noise.
+Observed maxima: gpurun_out/train_parity.json."""
 import json
 import os
 import math
@@ -29,6 +33,7 @@ pytestmark = pytest.mark.gpu
 
 TOL = 2e-4
 TOL_TF32_OUT, TOL_TF32_GRAD = 1e-2, 6e-2
+TF32_FLOOR = 3e-2      # of the largest gradient of the step (the reference's bf16 autocast: 6.5e-2)
 OBSERVED = {}
 
 
@@ -321,10 +326,15 @@ def _training_step_case(sam, sd, T, golden, prec):
                 continue
             assert got is not None, name
             # per tensor, with a floor tied to the largest gradient of the step (shift-invariant biases are ~1e-10)
-            _close(got, gref, name, tol=t_grad, floor=1e-6 * gmax, record=prec + ":param_grads")
+            # tf32: see the module docstring for the floor (scripts/train_precision_context.py,
+            # profiles/r4_train_precision_context.json)
+            _close(got, gref, name, tol=t_grad, floor=(1e-6 if prec == "fp32" else TF32_FLOOR) * gmax,
+                   record=prec + ":param_grads")
+            OBSERVED[prec + ":param_grads_over_largest"] = max(
+                OBSERVED.get(prec + ":param_grads_over_largest", 0.0), float((got.cpu() - gref).abs().max()) / gmax)
             dg = TO.grad_digest(got.cpu())
             rg = torch.from_numpy(g["g:" + name])
-            assert (dg[3:] - rg[3:]).abs().max() <= max(3e-4, t_grad) * float(rg[2]) + 1e-6 * gmax, name
+            assert (dg[3:] - rg[3:]).abs().max() <= max(3e-4, t_grad) * float(rg[2]) + (1e-6 if prec == "fp32" else TF32_FLOOR) * gmax, name
             checked += 1
         assert checked > 100
         for name, p in sam.named_parameters():
@@ -353,7 +363,8 @@ def _training_step_case(sam, sd, T, golden, prec):
         for name in ("mask_decoder_left.transformer.layers.1.cross_attn_image_to_token.q_proj.weight",
                      "mask_decoder_right.output_upscaling.0.weight", "mask_decoder_left.taxonomy_embed.layers.0.weight",
                      "mask_decoder_left.mask_tokens.weight"):
-            _close(named[name].grad, ref["grads"][name], "batched " + name, tol=t_grad, floor=1e-6 * gmax)
+            _close(named[name].grad, ref["grads"][name], "batched " + name, tol=t_grad,
+                   floor=(1e-6 if prec == "fp32" else TF32_FLOOR) * gmax)
 
         # an optimizer step on the decoders is picked up by the inference path (validate() between epochs)
         with torch.no_grad():
