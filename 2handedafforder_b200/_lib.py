@@ -34,6 +34,7 @@ SYMBOLS = [
     ("b200sam_dense_pe", _I, [_P, _P, _P]),
     ("b200sam_preprocess", _I, [_P, _P, _I, _I, _I, _P, _I, C.POINTER(_I), _P]),
     ("b200sam_seg_project", _I, [_P, _P, _I, _I, _I, _I, _P, _I, _L, _P, _P, _P, _P, _I, _P, _I, _P, _P]),
+    ("b200sam_seg_project_noalloc", _I, [_P, _P, _I, _I, _I, _I, _P, _I, _L, _P, _P, _P, _P, _I, _P, _I, _P, _P]),
     ("b200sam_mask_metrics", _I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _P]),
     ("b200sam_launch_count", _L, [_P]),
     ("b200sam_set_debug_simt_gemm", _I, [_P, _I]),

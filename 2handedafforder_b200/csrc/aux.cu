@@ -528,3 +528,109 @@ cudaError_t launch_mask_metrics(const uint8_t* left, const uint8_t* right, const
 }
 
 }  // namespace bsam
+
+// ------------------------------------------------------------------------------------------------ no-allocation variant
+// b200sam_seg_project_noalloc: b200sam_seg_project for callers that cannot call cudaMalloc (code under CUDA graph
+// capture, tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+// The scratch b200sam_seg_project keeps in handle-owned cudaMalloc buffers ([SEG] row indices,
+// per-image counts, the ReLU(Linear1) rows) lives in ONE file-scope device array of fixed size instead: every GPU that
+// loads the library holds its ~1.26 MB until exit.
+//
+// In host code the array's NAME is a host-side stand-in, not a device address: the device address is resolved once per
+// device (with that device current) through cudaGetSymbolAddress and only that pointer is handed to the kernels.
+//
+// Every call on a device shares the array, which keeps the previous call's contents.  Nothing in it has to start at
+// zero (the scan overwrites all b + 1 counts and every row index it later reads; the first FC overwrites every hidden
+// row the second one reads), but the counts are cleared anyway so that a failed launch cannot hand the previous call's
+// totals to the caller.  Two calls that overlap on the GPU (different streams, or concurrent host threads) RACE on it.
+#include <atomic>
+
+#include "b200sam.h"
+#include "model.cuh"
+
+namespace bsam {
+namespace {
+
+constexpr int kNoAllocMaxRows = 64;        // [SEG] prompts per call
+constexpr int kNoAllocMaxHidden = 5120;    // LLM hidden size (LLaVA-7B 4096, LLaVA-13B 5120)
+constexpr int kNoAllocMaxImages = 1024;    // images per call (same limit as b200sam_seg_project)
+constexpr size_t kNoAllocCountsOff = 0;                                                   // (1024 + 1) ints
+constexpr size_t kNoAllocRowsOff = ((kNoAllocMaxImages + 1) * sizeof(int) + 255) / 256 * 256;
+constexpr size_t kNoAllocHiddenOff = kNoAllocRowsOff + (kNoAllocMaxRows * sizeof(int) + 255) / 256 * 256;
+constexpr size_t kNoAllocBytes = kNoAllocHiddenOff + (size_t)kNoAllocMaxRows * kNoAllocMaxHidden * sizeof(float);
+
+static __device__ __align__(256) unsigned char g_seg_noalloc_scratch[kNoAllocBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+std::atomic<unsigned char*> g_seg_noalloc_ptr[kNoAllocMaxDevices];   // device address of the array, per device ordinal
+
+int na_fail(b200sam_t* h, int code, const char* msg) {
+  if (h) h->err = msg;
+  return code;
+}
+
+}  // namespace
+}  // namespace bsam
+
+extern "C" int b200sam_seg_project_noalloc(b200sam_t* h, const void* hidden, int hidden_dtype, int b, int L, int hdim,
+                                           const int64_t* output_ids, int T, int64_t seg_token_idx, const void* w1,
+                                           const void* b1, const void* w2, const void* b2, int w_dtype,
+                                           float* emb_out, int max_rows, int* counts_out, void* stream) {
+  using namespace bsam;
+  if (!h) return B200SAM_ERR_INVALID;
+  if (max_rows > kNoAllocMaxRows || hdim > kNoAllocMaxHidden || b > kNoAllocMaxImages) {
+    char buf[256];
+    snprintf(buf, sizeof buf,
+             "seg_project_noalloc: max_rows=%d / hdim=%d / b=%d exceed the static scratch (max_rows <= %d, hdim <= %d, "
+             "b <= %d); use b200sam_seg_project",
+             max_rows, hdim, b, kNoAllocMaxRows, kNoAllocMaxHidden, kNoAllocMaxImages);
+    return na_fail(h, B200SAM_ERR_INVALID, buf);
+  }
+  if (b < 1 || T < 1 || hdim < 8 || hdim % 8 != 0 || max_rows < 1)
+    return na_fail(h, B200SAM_ERR_INVALID, "seg_project_noalloc: bad sizes");
+  if (L < 255 + T - 1) return na_fail(h, B200SAM_ERR_INVALID, "seg_project_noalloc: hidden length < 255 + T - 1");
+  if (hidden_dtype < 0 || hidden_dtype > 2 || (w_dtype != B200SAM_F32 && w_dtype != B200SAM_BF16))
+    return na_fail(h, B200SAM_ERR_INVALID, "seg_project_noalloc: bad dtypes");
+  if (!hidden || !output_ids || !w1 || !b1 || !w2 || !b2 || !emb_out || !counts_out)
+    return na_fail(h, B200SAM_ERR_INVALID, "seg_project_noalloc: NULL argument");
+  const int dev = h->device;
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return na_fail(h, B200SAM_ERR_INVALID, "seg_project_noalloc: device ordinal");
+  int prev = -1;
+  if (cudaGetDevice(&prev) != cudaSuccess) return na_fail(h, B200SAM_ERR_CUDA, "seg_project_noalloc: cudaGetDevice");
+  if (prev != dev && cudaSetDevice(dev) != cudaSuccess)
+    return na_fail(h, B200SAM_ERR_CUDA, "seg_project_noalloc: cudaSetDevice");
+  int rc = 0;
+  do {
+    unsigned char* base = g_seg_noalloc_ptr[dev].load(std::memory_order_acquire);
+    if (!base) {   // set-up, once per device, with that device current: resolve the array's DEVICE address
+      void* p = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress(&p, g_seg_noalloc_scratch);
+      if (e != cudaSuccess || !p) {
+        rc = na_fail(h, B200SAM_ERR_CUDA, cudaGetErrorString(e));
+        break;
+      }
+      base = static_cast<unsigned char*>(p);
+      g_seg_noalloc_ptr[dev].store(base, std::memory_order_release);
+    }
+    int* counts = reinterpret_cast<int*>(base + kNoAllocCountsOff);
+    int* rows = reinterpret_cast<int*>(base + kNoAllocRowsOff);
+    float* hid = reinterpret_cast<float*>(base + kNoAllocHiddenOff);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    cudaError_t e = cudaMemsetAsync(counts, 0, sizeof(int) * (b + 1), s);
+    if (e == cudaSuccess) e = launch_seg_scan(output_ids, b, T, L, seg_token_idx, rows, max_rows, counts, s);
+    if (e == cudaSuccess)
+      e = launch_rows_fc(hidden, hidden_dtype, hdim, rows, counts + b, max_rows, w1, b1, w_dtype, hdim, hdim, true, hid,
+                         h->n_sm, s);
+    if (e == cudaSuccess)
+      e = launch_rows_fc(hid, DT_F32, hdim, nullptr, counts + b, max_rows, w2, b2, w_dtype, hdim, kOutCh, false, emb_out,
+                         h->n_sm, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(counts_out, counts, sizeof(int) * (b + 1), cudaMemcpyDeviceToDevice, s);
+    if (e != cudaSuccess) {
+      rc = na_fail(h, B200SAM_ERR_CUDA, cudaGetErrorString(e));
+      break;
+    }
+    h->launches += 3;
+  } while (false);
+  if (prev != dev) cudaSetDevice(prev);
+  return rc;
+}

@@ -123,6 +123,20 @@ int b200sam_seg_project(b200sam_t* h, const void* hidden, int hidden_dtype, int 
                         const void* w2, const void* b2, int w_dtype, float* emb_out, int max_rows, int* counts_out,
                         void* stream);
 
+/* b200sam_seg_project without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments, same results as b200sam_seg_project; its scratch ([SEG] row indices, counts, the
+ * ReLU(Linear1) rows) is a file-scope device array of fixed size instead of handle-owned buffers, so
+ *   - sizes are limited to max_rows <= 64, hdim <= 5120, b <= 1024 (larger: B200SAM_ERR_INVALID with the limits in
+ *     b200sam_last_error; use b200sam_seg_project);
+ *   - every GPU that loads the library holds the array (~1.26 MB) until exit;
+ *   - all calls on a device share it: calls that overlap on the GPU (different streams / host threads) race.
+ * Calls no cudaMalloc / cudaFree / allocating routine; the handle `h` is created beforehand at set-up. */
+int b200sam_seg_project_noalloc(b200sam_t* h, const void* hidden, int hidden_dtype, int b, int L, int hdim,
+                                const int64_t* output_ids, int T, int64_t seg_token_idx, const void* w1,
+                                const void* b1, const void* w2, const void* b2, int w_dtype, float* emb_out,
+                                int max_rows, int* counts_out, void* stream);
+
 /* Evaluation of train_ds.py::validate on the device (train_ds.py:662-709,761-796).  masks_left / masks_right:
  * (P,H,W) u8 thresholded masks (b200sam_postprocess mask_out); taxonomy (P,4) f32; gt: (G,H,W) u8 ground-truth masks,
  * prompt p is compared with gt[gt_index[p]] (gt_index == NULL: gt[p]).  The predicted mask is left (taxonomy argmax
