@@ -1222,9 +1222,19 @@ int resample_tables(b200sam_t* h, int H, int W, const ResampleTables** out) {
     t.ident_x = ax.identity;
     t.ident_y = ay.identity;
     t.tile_rows = preprocess_tile_rows(ay, t.new_h);
+    preprocess2_extents(ax, ay, t.new_w, t.new_h, &t.span_px128, &t.rows16);
     if ((size_t)t.tile_rows * 128 * 3 > 200 * 1024)
       return fail(h, B200SAM_ERR_INVALID, "frame height %d needs a %d-row tile: downscale factor not supported", H,
                   t.tile_rows);
+    {
+      float lut[768];
+      preprocess_lut(lut);
+      std::vector<int> bits(768);
+      memcpy(bits.data(), lut, sizeof lut);
+      int* d = nullptr;
+      if (int r = upload_ints(h, bits, &d)) return r;
+      t.d_lut = reinterpret_cast<float*>(d);
+    }
     if (int r = upload_ints(h, ax.lo, &t.d_xlo)) return r;
     if (int r = upload_ints(h, ax.cnt, &t.d_xcnt)) return r;
     if (int r = upload_ints(h, ax.kk, &t.d_xkk)) return r;

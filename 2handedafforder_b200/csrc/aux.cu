@@ -12,6 +12,7 @@
 //                       copies full-resolution masks to the host.
 #include <math.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "aux.cuh"
@@ -220,7 +221,226 @@ __global__ void __launch_bounds__(kPreThreads) preprocess_kernel(PreArgs a, T* _
   }
 }
 
+
+// ---- second-generation kernel (the shipped one for horizontal windows of up to 10 taps, i.e. frames up to 4608 px) ----
+// Same arithmetic, restructured around what bounded the first kernel (one-byte global loads walked row by row at
+// 11 % of HBM): a block = one 128 x 16 tile of the 1024^2 output, 3 channels, in three phases.
+//   A  the input rows the tile's vertical windows touch, restricted to the byte span its horizontal windows touch, are
+//      copied to shared memory with 16-byte loads (each row keeps its own 0..15-byte alignment phase);
+//   B  horizontal pass from shared memory: one thread = one output column, all three channels; its window (3 * taps
+//      interleaved RGB bytes) is fetched as NW 32-bit words, re-aligned with funnel shifts and unpacked in registers;
+//      the window start and the fixed-point weights stay in registers while the thread walks down the rows.  Output:
+//      channel-planar uint8 tile (Pillow rounds to uint8 between the passes);
+//   C  vertical pass: one thread = 8 consecutive pixels of one channel and output row (two 32-bit loads per tap), then
+//      (x - mean) / std through a 3 x 256-entry table built per block with the same IEEE subtract / divide / convert as
+//      before (a uint8 has 256 values: identical bits, no division per pixel), one 16-byte (bf16 / f16) or two (f32) stores.
+constexpr int kP2W = 128, kP2H = 16;
+
+// Pillow's clip8 without the clamp: the triangle filter's fixed-point weights are >= 0 and sum to 2^22 +- (taps / 2)
+// (normalize_coeffs_8bpc rounds each to nearest), so 2^21 <= acc <= 255 * (2^22 + taps) + 2^21 < 256 * 2^22 and the
+// shifted value is already in [0, 255]  (255 * taps < 2^21 for any window this kernel accepts).
+__device__ __forceinline__ uint32_t shr8(int acc) { return (uint32_t)acc >> kResamplePrecisionBits; }
+
+struct Pre2Args {
+  PreArgs p;
+  int rows_max;      // most input rows any 16-row output tile touches
+  int raw_pitch;     // bytes per staged input row (multiple of 16; covers phase + span + window over-read)
+  long in_bytes;     // B * H * W * 3
+  const float* lut;  // [3][256] (u - mean[c]) / std[c] in fp32, built once on the host (preprocess_lut)
+};
+
+template <typename T> __device__ __forceinline__ T cvt_out(float v);
+template <> __device__ __forceinline__ float cvt_out<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 cvt_out<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ __half cvt_out<__half>(float v) { return __float2half_rn(v); }
+
+template <typename T>
+__device__ __forceinline__ void store8(T* o, const T (&v)[8]) {
+  if constexpr (sizeof(T) == 4) {
+    reinterpret_cast<float4*>(o)[0] = make_float4(v[0], v[1], v[2], v[3]);
+    reinterpret_cast<float4*>(o)[1] = make_float4(v[4], v[5], v[6], v[7]);
+  } else {
+    *reinterpret_cast<uint4*>(o) = *reinterpret_cast<const uint4*>(v);
+  }
+}
+
+// shared-memory layout: [lut 3*256 T][rshift rows_max int, padded to 16 B][raw rows_max * raw_pitch][hb 3 * rows_max * 128]
+// [ytab 16 * (2 + ky) int]
+__device__ __forceinline__ uint8_t* hb_end(uint8_t* sm, const Pre2Args& q, size_t esz) {
+  return sm + 3 * 256 * esz + ((q.rows_max * 4 + 15) & ~15) + (size_t)q.rows_max * q.raw_pitch +
+         (size_t)3 * q.rows_max * kP2W;
+}
+
+template <typename T, int NPX>     // NPX: taps of the horizontal window the instantiation can hold (3, 5, 8 or 10)
+__global__ void __launch_bounds__(kPreThreads) preprocess2_kernel(Pre2Args q, T* __restrict__ out) {
+  constexpr int NV = (3 * NPX + 3) / 4;     // aligned 32-bit words holding the 3 * NPX window bytes
+  extern __shared__ __align__(16) uint8_t sm2[];
+  const PreArgs& a = q.p;
+  const int x0 = blockIdx.x * kP2W, y0 = blockIdx.y * kP2H;
+  const long b = blockIdx.z;
+  const int tw = min(kP2W, a.new_w - x0), th = min(kP2H, a.new_h - y0);
+  const int tid = threadIdx.x;
+  if (tw <= 0 || th <= 0) {                 // tile entirely in the zero pad
+    __align__(16) T z[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) z[j] = cvt_out<T>(0.f);
+    for (int i = tid; i < 3 * kP2H * (kP2W / 8); i += kPreThreads) {
+      const int g = i & 15, y = (i >> 4) & 15, c = i >> 8;
+      store8<T>(out + ((b * 3 + c) * (long)kImg + (y0 + y)) * kImg + x0 + g * 8, z);
+    }
+    return;
+  }
+  T* lut = reinterpret_cast<T*>(sm2);                               // [3][256]
+  int* rshift = reinterpret_cast<int*>(sm2 + 3 * 256 * sizeof(T));  // [rows_max] alignment phase of each staged row
+  uint8_t* raw = sm2 + 3 * 256 * sizeof(T) + ((q.rows_max * 4 + 15) & ~15);
+  uint8_t* hb = raw + (size_t)q.rows_max * q.raw_pitch;             // [3][rows_max][128]
+  for (int i = tid; i < 3 * 256; i += kPreThreads) lut[i] = cvt_out<T>(__ldg(q.lut + i));   // inference.py:99
+  // horizontal window of this thread's output column: independent of the staged rows, so the table loads overlap phase A
+  const int bx = tid & (kP2W - 1);
+  int bn = 0, bob = 0;
+  int bk[NPX];
+#pragma unroll
+  for (int j = 0; j < NPX; ++j) bk[j] = 0;
+  if (bx < tw) {
+    const int X = x0 + bx;
+    bn = a.xcnt[X];
+    bob = a.xlo[X];
+#pragma unroll
+    for (int j = 0; j < NPX; ++j) bk[j] = j < bn ? __ldg(a.xkk + (long)X * a.kx + j) : 0;
+  }
+  // vertical windows of the tile's 16 output rows -> shared memory (phase C reads them 3 * 16 times each)
+  int* ytab = reinterpret_cast<int*>(hb_end(sm2, q, sizeof(T)));     // [16][2 + ky]: lo - r0, n, weights
+  const int r0 = a.ylo[y0];
+  for (int i = tid; i < kP2H * (2 + a.ky); i += kPreThreads) {
+    const int y = i / (2 + a.ky), f = i - y * (2 + a.ky);
+    int v = 0;
+    if (y < th) v = f == 0 ? a.ylo[y0 + y] - r0 : f == 1 ? a.ycnt[y0 + y] : __ldg(a.ykk + (long)(y0 + y) * a.ky + (f - 2));
+    ytab[i] = v;
+  }
+  const int nrows = a.ylo[y0 + th - 1] + a.ycnt[y0 + th - 1] - r0;
+  const int px0 = a.xlo[x0];
+  const int nbytes = (a.xlo[x0 + tw - 1] + a.xcnt[x0 + tw - 1] - px0) * 3;
+  // ---- phase A: one warp per staged row, one 16-byte vector per lane and trip
+  {
+    const uint8_t* frame = a.in + b * (long)a.H * a.W * 3 + (long)px0 * 3;
+    const uint8_t* lo_ok = a.in;
+    const uint8_t* hi_ok = a.in + q.in_bytes;
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int r = warp; r < nrows; r += kPreThreads / 32) {
+      const uint8_t* src = frame + (long)(r0 + r) * a.W * 3;
+      const int sh = (int)(reinterpret_cast<uintptr_t>(src) & 15);
+      if (lane == 0) rshift[r] = sh;
+      const uint8_t* base = src - sh;
+      uint8_t* dst = raw + (size_t)r * q.raw_pitch;
+      const int nvec = (sh + nbytes + 15) >> 4;
+      if (base >= lo_ok && base + nvec * 16 <= hi_ok) {      // whole staged row inside the caller's buffer (warp-uniform)
+        for (int v = lane; v < nvec; v += 32)
+          *reinterpret_cast<uint4*>(dst + v * 16) = __ldg(reinterpret_cast<const uint4*>(base + v * 16));
+      } else {                                               // first / last row of the buffer: byte by byte at the ends
+        for (int v = lane; v < nvec; v += 32) {
+          const uint8_t* p = base + v * 16;
+          __align__(16) uint8_t tmp[16];
+#pragma unroll
+          for (int jj = 0; jj < 16; ++jj) tmp[jj] = (p + jj >= lo_ok && p + jj < hi_ok) ? p[jj] : (uint8_t)0;
+          *reinterpret_cast<uint4*>(dst + v * 16) = *reinterpret_cast<const uint4*>(tmp);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  // ---- phase B
+  {
+    const int x = bx, par = tid >> 7;
+    if (x < tw) {
+      const int ob = (bob - px0) * 3;
+      const int (&k)[NPX] = bk;
+      const uint8_t* rowp = raw + (size_t)par * q.raw_pitch;
+      uint8_t* hp = hb + par * kP2W + x;
+      const int rstep = (kPreThreads / kP2W) * q.raw_pitch, plane = q.rows_max * kP2W;
+      for (int r = par; r < nrows; r += kPreThreads / kP2W, rowp += rstep, hp += (kPreThreads / kP2W) * kP2W) {
+        const int o = ob + rshift[r];
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(rowp + (o & ~3));
+        const uint32_t sh = (uint32_t)(o & 3) * 8;
+        uint32_t w[NV + 1], v[NV];
+#pragma unroll
+        for (int j = 0; j <= NV; ++j) w[j] = wp[j];
+#pragma unroll
+        for (int j = 0; j < NV; ++j) v[j] = __funnelshift_r(w[j], w[j + 1], sh);
+        int acc[3] = {1 << (kResamplePrecisionBits - 1), 1 << (kResamplePrecisionBits - 1),
+                      1 << (kResamplePrecisionBits - 1)};
+#pragma unroll
+        for (int j = 0; j < 3 * NPX; ++j) acc[j % 3] += (int)__byte_perm(v[j >> 2], 0u, 0x4440u + (j & 3)) * k[j / 3];
+        hp[0] = shr8(acc[0]);
+        hp[plane] = shr8(acc[1]);
+        hp[2 * plane] = shr8(acc[2]);
+      }
+    }
+  }
+  __syncthreads();
+  // ---- phase C
+  for (int i = tid; i < 3 * kP2H * (kP2W / 8); i += kPreThreads) {
+    const int g = i & 15, y = (i >> 4) & 15, c = i >> 8;
+    __align__(16) T o8[8];
+    if (y < th && g * 8 < tw) {
+      const int* yt = ytab + y * (2 + a.ky);
+      const int lo = yt[0], n = yt[1];
+      int acc[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = 1 << (kResamplePrecisionBits - 1);
+      const uint8_t* col = hb + ((size_t)c * q.rows_max + lo) * kP2W + g * 8;
+      for (int t = 0; t < n; ++t) {
+        const int kt = yt[2 + t];
+        const uint2 wv = *reinterpret_cast<const uint2*>(col + (size_t)t * kP2W);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          acc[j] += (int)__byte_perm(wv.x, 0u, 0x4440u + j) * kt;
+          acc[4 + j] += (int)__byte_perm(wv.y, 0u, 0x4440u + j) * kt;
+        }
+      }
+      const T* lc = lut + c * 256;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o8[j] = lc[shr8(acc[j])];
+      if (g * 8 + 8 > tw) {                       // the one group that straddles new_w: columns right of it are zero pad
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (g * 8 + j >= tw) o8[j] = cvt_out<T>(0.f);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o8[j] = cvt_out<T>(0.f);
+    }
+    store8<T>(out + ((b * 3 + c) * (long)kImg + (y0 + y)) * kImg + x0 + g * 8, o8);
+  }
+}
+
 }  // namespace
+
+// (u - mean[c]) / std[c] for every uint8 value and channel: one IEEE fp32 subtract and one IEEE fp32 divide, exactly what
+// the per-pixel form computes (inference.py:93-99), so a table lookup gives identical bits
+void preprocess_lut(float* out768) {
+  const float mean[3] = {123.675f, 116.28f, 103.53f}, stdv[3] = {58.395f, 57.12f, 57.375f};
+  for (int c = 0; c < 3; ++c)
+    for (int u = 0; u < 256; ++u) {
+      volatile float d = (float)u - mean[c];
+      volatile float v = d / stdv[c];
+      out768[c * 256 + u] = v;
+    }
+}
+
+void preprocess2_extents(const ResampleAxis& ax, const ResampleAxis& ay, int new_w, int new_h, int* span_px,
+                         int* rows) {
+  int ws = 0, wr = 0;
+  for (int x0 = 0; x0 < new_w; x0 += kP2W) {
+    const int x1 = (x0 + kP2W < new_w ? x0 + kP2W : new_w) - 1;
+    ws = std::max(ws, ax.lo[x1] + ax.cnt[x1] - ax.lo[x0]);
+  }
+  for (int y0 = 0; y0 < new_h; y0 += kP2H) {
+    const int y1 = (y0 + kP2H < new_h ? y0 + kP2H : new_h) - 1;
+    wr = std::max(wr, ay.lo[y1] + ay.cnt[y1] - ay.lo[y0]);
+  }
+  *span_px = ws;
+  *rows = wr;
+}
 
 int preprocess_tile_rows(const ResampleAxis& ay, int new_h) {
   int worst = 0;
@@ -253,6 +473,43 @@ cudaError_t launch_preprocess(const uint8_t* frames, int B, int H, int W, const 
   a.ident_y = t.ident_y;
   const float mean[3] = {123.675f, 116.28f, 103.53f}, stdv[3] = {58.395f, 57.12f, 57.375f};   // inference.py:93-94
   for (int c = 0; c < 3; ++c) a.mean[c] = mean[c], a.stdv[c] = stdv[c];
+  // second-generation kernel whenever its window registers and shared-memory stage can hold the resample
+  if (kernel_variant(VK_PREPROCESS) == 0 && t.kx <= 10 && t.span_px128 > 0 && t.rows16 > 0 && t.d_lut) {
+    Pre2Args q;
+    q.p = a;
+    q.rows_max = t.rows16;
+    q.raw_pitch = (15 + t.span_px128 * 3 + 15) & ~15;
+    q.in_bytes = (long)B * H * W * 3;
+    const size_t esz = out_dtype == DT_F32 ? 4 : 2;
+    const size_t smem2 = 3 * 256 * esz + (((size_t)q.rows_max * 4 + 15) & ~(size_t)15) +
+                         (size_t)q.rows_max * q.raw_pitch + (size_t)3 * q.rows_max * kP2W +
+                         (size_t)kP2H * (2 + t.ky) * sizeof(int) + 64;
+    q.lut = t.d_lut;
+    if (smem2 <= 200 * 1024) {
+      dim3 grid2(kImg / kP2W, kImg / kP2H, B);
+      cudaError_t e2 = cudaSuccess;
+#define BSAM_PRE2(T, NPX)                                                                                          \
+  do {                                                                                                             \
+    e2 = cudaFuncSetAttribute(preprocess2_kernel<T, NPX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2); \
+    if (e2 != cudaSuccess) return e2;                                                                              \
+    preprocess2_kernel<T, NPX><<<grid2, kPreThreads, smem2, s>>>(q, reinterpret_cast<T*>(out));                     \
+  } while (0)
+#define BSAM_PRE2_T(T)                 \
+  do {                                 \
+    if (t.kx <= 3) BSAM_PRE2(T, 3);    \
+    else if (t.kx <= 5) BSAM_PRE2(T, 5); \
+    else if (t.kx <= 8) BSAM_PRE2(T, 8); \
+    else BSAM_PRE2(T, 10);             \
+  } while (0)
+      if (out_dtype == DT_F32) BSAM_PRE2_T(float);
+      else if (out_dtype == DT_BF16) BSAM_PRE2_T(__nv_bfloat16);
+      else if (out_dtype == DT_F16) BSAM_PRE2_T(__half);
+      else return cudaErrorInvalidValue;
+#undef BSAM_PRE2_T
+#undef BSAM_PRE2
+      return cudaGetLastError();
+    }
+  }
   const size_t smem = (size_t)t.tile_rows * kTileW * 3;
   dim3 grid(kImg / kTileW, kImg / kTileH, B);
   cudaError_t e = cudaSuccess;

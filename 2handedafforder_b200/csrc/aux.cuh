@@ -22,10 +22,15 @@ struct ResampleAxis {
 void build_resample_axis(int in_size, int out_size, ResampleAxis* ax);
 // most input rows any 8-row output tile of preprocess_kernel needs (sizes its shared-memory tile)
 int preprocess_tile_rows(const ResampleAxis& ay, int new_h);
+// second-generation kernel: widest input pixel span of a 128-column output tile, most input rows of a 16-row tile
+void preprocess_lut(float* out768);
+void preprocess2_extents(const ResampleAxis& ax, const ResampleAxis& ay, int new_w, int new_h, int* span_px, int* rows);
 
 // Device copy of the two axes for one (H, W) -> (new_h, new_w); cached in the handle per input size.
 struct ResampleTables {
   int H = 0, W = 0, new_h = 0, new_w = 0, kx = 0, ky = 0, ident_x = 1, ident_y = 1, tile_rows = 0;
+  int span_px128 = 0, rows16 = 0;    // preprocess2_extents
+  float* d_lut = nullptr;            // preprocess_lut on the device
   int *d_xlo = nullptr, *d_xcnt = nullptr, *d_xkk = nullptr, *d_ylo = nullptr, *d_ycnt = nullptr, *d_ykk = nullptr;
 };
 

@@ -56,6 +56,37 @@ def test_preprocess_bit_exact_against_oracle_odd_sizes(sam, hw):
     assert torch.equal(xh.cpu(), x.cpu().half())
 
 
+@pytest.mark.parametrize("hw", [(1080, 1920), (203, 301), (4000, 300), (768, 1024), (300, 5000), (2160, 3840)])
+def test_preprocess_kernel_generations_agree_and_unaligned_input(sam, hw):
+    """The shared-memory staged kernel (shipped) and the round-1 kernel (debug variant 4 = 1; also the path for windows
+    wider than 10 taps, e.g. 5000 columns -> 1024; 4000 rows -> 1024 only widens the vertical window) give the same bits for all three output dtypes, and a frame buffer that
+    starts at an odd address (16-byte loads with a per-row alignment phase, byte loads at the buffer ends) changes
+    nothing."""
+    H, W = hw
+    frames = np.stack([synth_image(H, W, 70 + i) for i in range(3)])
+    dev = torch.from_numpy(frames).cuda()
+    flat = torch.zeros((frames.size + 7,), dtype=torch.uint8, device="cuda")
+    flat[5:5 + frames.size] = dev.reshape(-1)
+    odd = flat[5:5 + frames.size].view(3, H, W, 3)
+    assert odd.data_ptr() % 16 == 5
+    try:
+        for dt in (torch.float32, torch.bfloat16, torch.float16):
+            assert G.lib().b200sam_debug_set_variant(4, 1) == 0
+            want, r1 = sam.preprocess_frames(dev, dtype=dt)
+            assert G.lib().b200sam_debug_set_variant(4, 0) == 0
+            got, r0 = sam.preprocess_frames(dev, dtype=dt)
+            got_odd, _ = sam.preprocess_frames(odd, dtype=dt)
+            assert r0 == r1
+            assert torch.equal(got.view(torch.int16 if dt != torch.float32 else torch.int32),
+                               want.view(torch.int16 if dt != torch.float32 else torch.int32))
+            assert torch.equal(got_odd, got)
+    finally:
+        G.lib().b200sam_debug_set_variant(4, 0)
+    ref, _ = PO.preprocess_frame(frames[2])
+    x32, _ = sam.preprocess_frames(dev, dtype=torch.float32)
+    assert np.array_equal(x32[2].cpu().numpy(), ref)
+
+
 def test_preprocess_rejects_bad_input(sam):
     with pytest.raises(ValueError):
         sam.preprocess_frames(torch.zeros((4, 4, 4), dtype=torch.uint8, device="cuda"))
