@@ -385,6 +385,56 @@ def _training_step_case(sam, sd, T, golden, prec):
         sam.eval()
 
 
+def test_bf16_model_trains_like_the_fp32_one():
+    """train_ds.py casts the whole model to bf16 (--precision bf16): decoder parameters, image embeddings and the [SEG]
+    embeddings arrive as bf16.  The kernels compute in fp32 on up-cast copies (through autograd, so .grad comes back in
+    the parameter's dtype); against the fp32 model with the SAME bf16-rounded weights the gradients agree to bf16
+    resolution."""
+    sam, arch, sd = G.build_sam_from_synth("tiny64", max_batch=2, max_prompts=4)
+    sd16 = {k: v.to(torch.bfloat16) for k, v in sd.items()}
+    sam32, _, _ = G.build_sam_from_synth("tiny64", max_batch=2, max_prompts=4)
+    sam32.load_state_dict({k: v.float() for k, v in sd16.items()}, strict=True)
+    sam16 = sam.to(torch.bfloat16)
+    sam16.load_state_dict(sd16, strict=True)
+    emb, segs, gt_left, gt_right, tax_gt = synth.make_train_inputs()
+    emb16 = emb.to(torch.bfloat16).cuda()
+    outs = {}
+    for name, model, e in (("bf16", sam16, emb16), ("fp32", sam32, emb16.float())):
+        for p in model.parameters():
+            p.requires_grad = False
+        for dec in (model.mask_decoder_left, model.mask_decoder_right):
+            dec.train()
+            for p in dec.parameters():
+                p.requires_grad = True
+        T = model.train_ops(torch.device("cuda", 0))
+        prev = T.set_precision("fp32")
+        try:
+            s = [x.to(torch.bfloat16).to(e.dtype).cuda().requires_grad_(True) for x in segs]   # same bf16-rounded values
+            out = model.train_decode(e, s)
+            pl = model.postprocess_masks(out["low_res_left"], (576, 1024), (135, 240))[:, 0]
+            gt = torch.cat([gt_left[0], gt_right[0][:1]]).cuda()            # three (135, 240) label planes
+            b, d = T.mask_losses(pl, gt)
+            loss = b.sum() + d.sum() + out["taxonomy"][:, 0].sum() + out["low_res_right"].mean()
+            loss.backward()
+            torch.cuda.synchronize()
+        finally:
+            T.set_precision(prev)
+        outs[name] = (loss.detach().float().cpu(), {n: p.grad for n, p in model.named_parameters() if p.grad is not None},
+                      [x.grad for x in s])
+        model.eval()
+    l16, g16, s16 = outs["bf16"]
+    l32, g32, s32 = outs["fp32"]
+    assert abs(float(l16) - float(l32)) <= 1e-4 * abs(float(l32))          # same weights, same fp32 arithmetic
+    assert set(g16) == set(g32) and len(g16) > 100
+    for n in g16:
+        assert g16[n].dtype == torch.bfloat16 and g32[n].dtype == torch.float32
+        ref = g32[n].float().cpu()
+        assert float((g16[n].float().cpu() - ref).abs().max()) <= 2 ** -7 * float(ref.abs().max()) + 1e-9, n
+    for a, b in zip(s16, s32):
+        assert a.dtype == torch.bfloat16
+        assert float((a.float().cpu() - b.cpu()).abs().max()) <= 2 ** -7 * float(b.abs().max())
+
+
 def test_frozen_entry_points_still_refuse_grad(tiny):
     sam, _, _ = tiny
     frames = synth.make_frames(0, 1).cuda().requires_grad_(True)
