@@ -152,6 +152,120 @@ __global__ void __launch_bounds__(256) gemm_strided_kernel(const float* __restri
   }
 }
 
+// ---- thin products: two of (M, N, K) are <= 32 and one is long (the decoder's attention between 6 tokens and 4096
+// image positions with 16-wide heads; the hypernetwork product and its adjoints over 65536 pixels).  The tiled kernel
+// wastes 75-90 % of its tile on them; these two stream the long dimension instead.
+//
+// thin_expand: N long, M <= MT, K <= 32.  One thread per column n: A (M x K) sits in shared memory, the thread reads its K
+// values of B and produces M outputs.
+template <int MT>
+__global__ void __launch_bounds__(256) thin_expand_kernel(const float* __restrict__ A, GemmStrides sa,
+                                                          const float* __restrict__ B, GemmStrides sb,
+                                                          float* __restrict__ Cm, GemmStrides sc,
+                                                          const float* __restrict__ bias, int bias_mode, int nb2, int M,
+                                                          int N, int K, float alpha, float beta) {
+  __shared__ float As[32][MT + 1];       // [k][m]
+  const int bz = blockIdx.y;
+  const int b1 = bz / nb2, b2 = bz - b1 * nb2;
+  A += b1 * sa.b1 + b2 * sa.b2;
+  B += b1 * sb.b1 + b2 * sb.b2;
+  Cm += b1 * sc.b1 + b2 * sc.b2;
+  for (int i = threadIdx.x; i < 32 * MT; i += 256) {
+    const int k = i / MT, m = i - k * MT;
+    As[k][m] = (m < M && k < K) ? A[(long)m * sa.r + (long)k * sa.c] : 0.f;
+  }
+  __syncthreads();
+  const int n = blockIdx.x * 256 + threadIdx.x;
+  if (n >= N) return;
+  float acc[MT];
+#pragma unroll
+  for (int m = 0; m < MT; ++m) acc[m] = 0.f;
+  const float* bp = B + (long)n * sb.c;
+  if (sb.r == 1 && (K & 3) == 0 && ((reinterpret_cast<uintptr_t>(bp) & 15) == 0)) {   // K values contiguous per column
+    for (int k = 0; k < K; k += 4) {
+      const float4 v = *reinterpret_cast<const float4*>(bp + k);
+      const float bv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int m = 0; m < MT; ++m) acc[m] = fmaf(As[k + j][m], bv[j], acc[m]);
+    }
+  } else {
+    for (int k = 0; k < K; ++k) {
+      const float bv = bp[(long)k * sb.r];
+#pragma unroll
+      for (int m = 0; m < MT; ++m) acc[m] = fmaf(As[k][m], bv, acc[m]);
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < MT; ++m) {
+    if (m < M) {
+      float* c = Cm + (long)m * sc.r + (long)n * sc.c;
+      float v = alpha * acc[m];
+      if (bias_mode == 1) v += bias[n];
+      else if (bias_mode == 2) v += bias[m];
+      if (beta != 0.f) v += beta * *c;
+      *c = v;
+    }
+  }
+}
+
+// thin_reduce: K long, M <= MT, N <= NT (MT * NT <= 128).  A block of 64 threads owns one K chunk of one batch: each
+// thread accumulates the whole M x N result over its k values in registers, the block sums the 64 partial results
+// through shared memory and adds them to C with one atomic per element (C prepared by gemm_prepare_kernel).
+template <int MT, int NT>
+__global__ void __launch_bounds__(64) thin_reduce_kernel(const float* __restrict__ A, GemmStrides sa,
+                                                         const float* __restrict__ B, GemmStrides sb,
+                                                         float* __restrict__ Cm, GemmStrides sc, int nb2, int M, int N,
+                                                         int K, int kchunk, float alpha) {
+  __shared__ float red[MT * NT][65];
+  const int bz = blockIdx.y;
+  const int b1 = bz / nb2, b2 = bz - b1 * nb2;
+  A += b1 * sa.b1 + b2 * sa.b2;
+  B += b1 * sb.b1 + b2 * sb.b2;
+  Cm += b1 * sc.b1 + b2 * sc.b2;
+  float acc[MT][NT];
+#pragma unroll
+  for (int m = 0; m < MT; ++m)
+#pragma unroll
+    for (int n = 0; n < NT; ++n) acc[m][n] = 0.f;
+  const int k0 = blockIdx.x * kchunk, k1 = min(K, k0 + kchunk);
+  const bool bvec = sb.c == 1 && N == NT && (sb.r & 3) == 0 && (reinterpret_cast<uintptr_t>(B) & 15) == 0;
+  for (int k = k0 + threadIdx.x; k < k1; k += 64) {
+    float av[MT], bv[NT];
+#pragma unroll
+    for (int m = 0; m < MT; ++m) av[m] = m < M ? A[(long)m * sa.r + (long)k * sa.c] : 0.f;
+    const float* bp = B + (long)k * sb.r;
+    if (bvec) {
+#pragma unroll
+      for (int n = 0; n < NT; n += 4) {
+        const float4 v = *reinterpret_cast<const float4*>(bp + n);
+        bv[n] = v.x, bv[n + 1] = v.y, bv[n + 2] = v.z, bv[n + 3] = v.w;
+      }
+    } else {
+#pragma unroll
+      for (int n = 0; n < NT; ++n) bv[n] = n < N ? bp[(long)n * sb.c] : 0.f;
+    }
+#pragma unroll
+    for (int m = 0; m < MT; ++m)
+#pragma unroll
+      for (int n = 0; n < NT; ++n) acc[m][n] = fmaf(av[m], bv[n], acc[m][n]);
+  }
+#pragma unroll
+  for (int m = 0; m < MT; ++m)
+#pragma unroll
+    for (int n = 0; n < NT; ++n) red[m * NT + n][threadIdx.x] = acc[m][n];
+  __syncthreads();
+  for (int e = threadIdx.x; e < MT * NT; e += 64) {
+    const int m = e / NT, n = e - m * NT;
+    if (m >= M || n >= N) continue;
+    float sum = 0.f;
+#pragma unroll 8
+    for (int t = 0; t < 64; ++t) sum += red[e][t];     // row pitch 65: lanes hit distinct banks
+    atomicAdd(Cm + (long)m * sc.r + (long)n * sc.c, alpha * sum);
+  }
+}
+
 // first pass of a split-K product: C = beta * C + bias
 __global__ void __launch_bounds__(256) gemm_prepare_kernel(float* __restrict__ Cm, GemmStrides sc,
                                                            const float* __restrict__ bias, int bias_mode, int nb2, int M,
@@ -624,6 +738,25 @@ extern "C" int b200sam_train_gemm(b200sam_t* h, const float* A, const int64_t* s
     M = N;
     N = t3;
     if (bias_mode) bias_mode = 3 - bias_mode;
+  }
+  // thin products (see thin_expand_kernel / thin_reduce_kernel)
+  if (!relu && M <= 32 && K <= 32 && N >= 1024 && nb <= 65535) {
+    dim3 grid((unsigned)((N + 255) / 256), (unsigned)nb);
+    if (M <= 8) thin_expand_kernel<8><<<grid, 256, 0, s>>>(A, a, B, b, Cm, c, bias, bias_mode, nb2, M, N, K, alpha, beta);
+    else if (M <= 16) thin_expand_kernel<16><<<grid, 256, 0, s>>>(A, a, B, b, Cm, c, bias, bias_mode, nb2, M, N, K, alpha, beta);
+    else thin_expand_kernel<32><<<grid, 256, 0, s>>>(A, a, B, b, Cm, c, bias, bias_mode, nb2, M, N, K, alpha, beta);
+    T_DONE(1);
+  }
+  if (!relu && K >= 2048 && nb <= 65535 && ((M <= 8 && N <= 16) || (M <= 4 && N <= 32))) {
+    const int kchunk = K >= 32768 ? 4096 : 1024;
+    dim3 g0((unsigned)(((long)M * N + 255) / 256), 1, (unsigned)nb);
+    gemm_prepare_kernel<<<g0, 256, 0, s>>>(Cm, c, bias, bias_mode, nb2, M, N, beta);
+    dim3 grid((unsigned)((K + kchunk - 1) / kchunk), (unsigned)nb);
+    if (M <= 4 && N <= 16) thin_reduce_kernel<4, 16><<<grid, 64, 0, s>>>(A, a, B, b, Cm, c, nb2, M, N, K, kchunk, alpha);
+    else if (M <= 4) thin_reduce_kernel<4, 32><<<grid, 64, 0, s>>>(A, a, B, b, Cm, c, nb2, M, N, K, kchunk, alpha);
+    else if (M <= 6) thin_reduce_kernel<6, 16><<<grid, 64, 0, s>>>(A, a, B, b, Cm, c, nb2, M, N, K, kchunk, alpha);
+    else thin_reduce_kernel<8, 16><<<grid, 64, 0, s>>>(A, a, B, b, Cm, c, nb2, M, N, K, kchunk, alpha);
+    T_DONE(2);
   }
   const int bm = M <= 16 ? 16 : kGT;
   const int tx = (N + kGT - 1) / kGT, ty = (M + bm - 1) / bm;
