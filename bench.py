@@ -227,7 +227,7 @@ def run_reference_arm(args):
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit_line(json.dumps(line))
     return 0
 
 
@@ -582,13 +582,36 @@ def run_gpu_arm(args):
             "kernels": kernels, "callers": aux, "latency_b1_ms": latency, "gather_verified": gather_verified,
             "train_step": train,
         }
-        print(json.dumps(line))
+        emit_line(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries print there too (NCCL's version banner at communicator
+    creation, warnings of native extensions), so file descriptor 1 is pointed at stderr for the whole run and the
+    result line is written to the saved descriptor by emit_line()."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(text: str) -> None:
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        print(text, flush=True)
+    else:
+        os.write(_REAL_STDOUT, (text + "\n").encode())
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
