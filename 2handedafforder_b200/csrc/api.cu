@@ -374,6 +374,16 @@ int finalize_encoder(b200sam_t* h) {
     if (int r = make_bf16(h, W(h, p + "attn.proj.weight"), D * D, &b.proj_w)) return r;
     if (int r = make_bf16(h, W(h, p + "mlp.lin1.weight"), 4 * D * D, &b.lin1_w)) return r;
     if (int r = make_bf16(h, W(h, p + "mlp.lin2.weight"), 4 * D * D, &b.lin2_w)) return r;
+    CU(dalloc(h, &b.qkv_wf, (size_t)3 * D * D));
+    CU(dalloc(h, &b.qkv_c, (size_t)3 * D));
+    CU(dalloc(h, &b.qkv_d, (size_t)3 * D));
+    KL(launch_fold_ln_weights(W(h, p + "attn.qkv.weight"), b.ln1g, b.ln1b, b.qkv_b, (int)(3 * D), (int)D, b.qkv_wf, b.qkv_c,
+                              b.qkv_d, 0));
+    CU(dalloc(h, &b.lin1_wf, (size_t)4 * D * D));
+    CU(dalloc(h, &b.lin1_c, (size_t)4 * D));
+    CU(dalloc(h, &b.lin1_d, (size_t)4 * D));
+    KL(launch_fold_ln_weights(W(h, p + "mlp.lin1.weight"), b.ln2g, b.ln2b, b.lin1_b, (int)(4 * D), (int)D, b.lin1_wf,
+                              b.lin1_c, b.lin1_d, 0));
     const int S = b.global ? kGrid : kWin;
     const int RP = b.global ? 128 : 32;
     CU(dalloc(h, &b.relh, (size_t)2 * RP * h->hd));   // [relh ; relw] contiguous: one tensor map covers both
@@ -451,6 +461,8 @@ int alloc_workspace(b200sam_t* h) {
   CU(dalloc(h, &h->hid, B * kTokens * hid_cols));
   // neck.1 output in the zero-ringed (B, 66, 66, 256) layout the 3x3 convolution reads through a 4-D tensor map; the
   // ring is zeroed here once and never written again
+  h->ln_slots = 2 * (int)((D + 255) / 256);
+  CU(dalloc(h, &h->ln_stats, B * kTokens * (size_t)h->ln_slots * 2));
   CU(dalloc(h, &h->zpad, B * 66 * 66 * 256, /*zero=*/true));
   CU(cudaDeviceSynchronize());
   CU(dalloc(h, &h->emb_tok, B * kTokens * 256));
@@ -724,6 +736,10 @@ namespace {
 // pos_embed in the epilogue.  bf16 frames are read by the GEMM's own TMA loads through a 5-D tensor map (AM_PATCH16,
 // no im2col copy); fp32 / fp16 frames, widths that are not a multiple of 256 and the SIMT bisect path go through the
 // im2col index map, which also casts to bf16.  Reads the caller's frames, so it stays outside the CUDA graph.
+// LayerNorm folded into the consuming GEMMs (gemm_tc.cuh GemmEpi::stats_in): the shipped path.  Debug variant 5 = 1 and
+// the SIMT bisect path use the stand-alone LayerNorm kernel.
+bool ln_fold_on(const b200sam_t* h) { return kernel_variant(VK_LN_FOLD) == 0 && !h->debug_simt; }
+
 int encode_patch(b200sam_t* h, const void* frames, int frames_dtype, int B, cudaStream_t s) {
   const int D = h->dim;
   const long T = (long)B * kTokens;
@@ -734,17 +750,24 @@ int encode_patch(b200sam_t* h, const void* frames, int frames_dtype, int B, cuda
   e.add_mod = kTokens;
   e.out = h->X;
   e.ld_out = D;
+  const bool fold = ln_fold_on(h);
+  if (fold) {          // block 0's norm1 is folded into its qkv GEMM: emit the bf16 rows and the row sums here
+    e.xb_out = h->ln_plain;
+    e.stats_out = h->ln_stats;
+    e.stats_slots = h->ln_slots;
+  }
+  const int mode = fold ? GM_F32_FOLD : GM_F32;
   const bool implicit = frames_dtype == DT_BF16 && D % 256 == 0 && !h->debug_simt &&
                         kernel_variant(VK_IMPLICIT_CONV) == 0 && (reinterpret_cast<uintptr_t>(frames) & 15) == 0;
   if (implicit) {
     e.a_mode = AM_PATCH16;
     h->pc = B200SAM_PC_GEMM_PATCH;
-    return run_gemm(h, false, GM_F32, frames, 768, h->patch_w, 768, T, D, 768, e, s);
+    return run_gemm(h, false, mode, frames, 768, h->patch_w, 768, T, D, 768, e, s);
   }
   h->pc = B200SAM_PC_ELEMENTWISE;
   KL(launch_im2col_patch(frames, frames_dtype, B, h->hid, s));
   h->pc = B200SAM_PC_GEMM_PATCH;
-  return run_gemm(h, false, GM_F32, h->hid, 768, h->patch_w, 768, T, D, 768, e, s);
+  return run_gemm(h, false, mode, h->hid, 768, h->patch_w, 768, T, D, 768, e, s);
 }
 
 // Everything of ImageEncoderViT.forward that reads and writes only the handle's own buffers: the
@@ -754,6 +777,7 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
   const int D = h->dim, heads = h->heads, hd = h->hd;
   const long T = (long)B * kTokens;
   const int nblocks = (h->debug_stop_block >= 0 && h->debug_stop_block < h->depth) ? h->debug_stop_block : h->depth;
+  const bool fold = ln_fold_on(h);
   for (int i = 0; i < nblocks; ++i) {
     const EncBlock& b = h->blk[i];
     // norm1 in token order.  The windowed blocks never materialise the zero-padded window tensor: the qkv epilogue
@@ -761,15 +785,22 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
     // the 804 pad rows (zero after norm1 => qkv = bias, :179-183) are filled by a small kernel, and the attention
     // kernel stores straight back into token order (window_unpartition), so qkv and proj run on 4096 rows per frame.
     h->pc = B200SAM_PC_LAYERNORM;
-    KL(launch_layernorm_bf16(h->X, T, D, b.ln1g, b.ln1b, 1e-6f, h->ln_plain, false, s));
+    if (!fold) KL(launch_layernorm_bf16(h->X, T, D, b.ln1g, b.ln1b, 1e-6f, h->ln_plain, false, s));
     {
       GemmEpi e;
-      e.bias = b.qkv_b;
+      e.bias = fold ? b.qkv_d : b.qkv_b;
+      if (fold) {
+        e.stats_in = h->ln_stats;
+        e.stats_slots = h->ln_slots;
+        e.stats_dim = D;
+        e.fold_c = b.qkv_c;
+        e.fold_eps = 1e-6f;
+      }
       e.out = h->qkv;
       e.ld_out = 3 * D;
       e.rowmap = b.global ? RM_IDENT : RM_TOKEN_TO_WINDOW;
       h->pc = B200SAM_PC_GEMM_QKV;
-      if (int r = run_gemm(h, false, GM_BIAS_BF16, h->ln_plain, D, b.qkv_w, D, T, 3 * D, D, e, s)) return r;
+      if (int r = run_gemm(h, false, GM_BIAS_BF16, h->ln_plain, D, fold ? b.qkv_wf : b.qkv_w, D, T, 3 * D, D, e, s)) return r;
       if (!b.global) KL(launch_fill_pad_rows(h->qkv, b.qkv_b, h->pad_rows, h->n_pad_rows, B, 3 * D, s));
     }
     h->pc = b.global ? B200SAM_PC_ATTN_GLOBAL : B200SAM_PC_ATTN_WINDOW;
@@ -784,19 +815,31 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
       e.ld_add = D;
       e.out = h->X;
       e.ld_out = D;
+      if (fold) {
+        e.xb_out = h->ln_plain;
+        e.stats_out = h->ln_stats;
+        e.stats_slots = h->ln_slots;
+      }
       h->pc = B200SAM_PC_GEMM_PROJ;
-      if (int r = run_gemm(h, false, GM_F32, h->attn_o, D, b.proj_w, D, T, D, D, e, s)) return r;
+      if (int r = run_gemm(h, false, fold ? GM_F32_FOLD : GM_F32, h->attn_o, D, b.proj_w, D, T, D, D, e, s)) return r;
     }
     // x = x + lin2(GELU(lin1(norm2(x))))                                          (image_encoder.py:191, common.py:25-26)
     h->pc = B200SAM_PC_LAYERNORM;
-    KL(launch_layernorm_bf16(h->X, T, D, b.ln2g, b.ln2b, 1e-6f, h->ln_plain, false, s));
+    if (!fold) KL(launch_layernorm_bf16(h->X, T, D, b.ln2g, b.ln2b, 1e-6f, h->ln_plain, false, s));
     {
       GemmEpi e;
-      e.bias = b.lin1_b;
+      e.bias = fold ? b.lin1_d : b.lin1_b;
+      if (fold) {
+        e.stats_in = h->ln_stats;
+        e.stats_slots = h->ln_slots;
+        e.stats_dim = D;
+        e.fold_c = b.lin1_c;
+        e.fold_eps = 1e-6f;
+      }
       e.out = h->hid;
       e.ld_out = 4 * D;
       h->pc = B200SAM_PC_GEMM_LIN1;
-      if (int r = run_gemm(h, false, GM_BIAS_GELU_BF16, h->ln_plain, D, b.lin1_w, D, T, 4 * D, D, e, s)) return r;
+      if (int r = run_gemm(h, false, GM_BIAS_GELU_BF16, h->ln_plain, D, fold ? b.lin1_wf : b.lin1_w, D, T, 4 * D, D, e, s)) return r;
     }
     {
       GemmEpi e;
@@ -805,14 +848,19 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
       e.ld_add = D;
       e.out = h->X;
       e.ld_out = D;
+      if (fold) {          // the bf16 rows feed the next block's qkv (or the neck), the sums its norm1
+        e.xb_out = h->ln_plain;
+        e.stats_out = h->ln_stats;
+        e.stats_slots = h->ln_slots;
+      }
       h->pc = B200SAM_PC_GEMM_LIN2;
-      if (int r = run_gemm(h, false, GM_F32, h->hid, 4 * D, b.lin2_w, 4 * D, T, D, 4 * D, e, s)) return r;
+      if (int r = run_gemm(h, false, fold ? GM_F32_FOLD : GM_F32, h->hid, 4 * D, b.lin2_w, 4 * D, T, D, 4 * D, e, s)) return r;
     }
   }
   if (nblocks != h->depth) return 1;   // debug: residual stream after `nblocks` blocks is left in X
   // neck (image_encoder.py:92-108): conv1x1 -> LayerNorm2d -> conv3x3 -> LayerNorm2d, token-major
   h->pc = B200SAM_PC_NECK;
-  KL(launch_cast_f32_bf16(h->X, h->ln_plain, T * D, s));
+  if (!fold) KL(launch_cast_f32_bf16(h->X, h->ln_plain, T * D, s));     // folded: the last lin2 epilogue wrote the bf16 rows
   // neck.2 Conv2d 3x3: the GEMM gathers its A tiles from the zero-ringed neck.1 output (AM_CONV3); the SIMT bisect
   // path and variant 1 materialise the (T, 9*256) im2col rows instead
   const bool implicit3 = !h->debug_simt && kernel_variant(VK_IMPLICIT_CONV) == 0;
@@ -849,7 +897,7 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
 // debug switches and a caller who is capturing the stream himself use the plain launch sequence.
 int encode_body_graphed(b200sam_t* h, int B, cudaStream_t s) {
   const int sig = kernel_variant(VK_ATTN_WINDOW) * 10000 + kernel_variant(VK_ATTN_GLOBAL) * 100 +
-                  kernel_variant(VK_GEMM_PAIR) * 10 + kernel_variant(VK_IMPLICIT_CONV);
+                  kernel_variant(VK_GEMM_PAIR) * 10 + kernel_variant(VK_IMPLICIT_CONV) + kernel_variant(VK_LN_FOLD) * 1000000;
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
   const bool plain = h->prof_on || h->debug_simt || h->debug_stop_block >= 0 || !h->use_graphs ||
                      cudaStreamIsCapturing(s, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone;

@@ -292,6 +292,39 @@ cudaError_t launch_nchw_to_tokens(const void* in, int dtype, int B, float* tok, 
   return cudaGetLastError();
 }
 
+// LayerNorm folded into the consuming Linear (gemm_tc.cuh, GemmEpi::stats_in):  LN(x) W^T + b =
+// rstd * (x (gamma . W)^T) - rstd * mean * c + d.  One block per output feature n: Wf[n, :] = bf16(gamma . W[n, :]),
+// c[n] = sum_k float(Wf[n, k]) (the ROUNDED weights, so that a constant row still cancels exactly), d[n] = W[n, :] . beta + b[n].
+static __global__ void __launch_bounds__(128) fold_ln_weights_kernel(const float* __restrict__ Wt, const float* __restrict__ gamma,
+                                                              const float* __restrict__ beta, const float* __restrict__ bias,
+                                                              int K, __nv_bfloat16* __restrict__ Wf, float* __restrict__ c,
+                                                              float* __restrict__ d) {
+  __shared__ float red[2][4];
+  const long n = blockIdx.x;
+  float sc = 0.f, sd = 0.f;
+  for (int k = threadIdx.x; k < K; k += 128) {
+    const float w = Wt[n * K + k];
+    const __nv_bfloat16 wf = __float2bfloat16_rn(w * gamma[k]);
+    Wf[n * K + k] = wf;
+    sc += __bfloat162float(wf);
+    sd += w * beta[k];
+  }
+  sc = warp_sum(sc);
+  sd = warp_sum(sd);
+  if ((threadIdx.x & 31) == 0) red[0][threadIdx.x >> 5] = sc, red[1][threadIdx.x >> 5] = sd;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    c[n] = (red[0][0] + red[0][1]) + (red[0][2] + red[0][3]);
+    d[n] = (red[1][0] + red[1][1]) + (red[1][2] + red[1][3]) + bias[n];
+  }
+}
+
+cudaError_t launch_fold_ln_weights(const float* Wt, const float* gamma, const float* beta, const float* bias, int N, int K,
+                                   __nv_bfloat16* Wf, float* c, float* d, cudaStream_t s) {
+  fold_ln_weights_kernel<<<N, 128, 0, s>>>(Wt, gamma, beta, bias, K, Wf, c, d);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_cast_f32_bf16(const float* in, __nv_bfloat16* out, long n, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   const long nthreads = (n + 3) / 4;

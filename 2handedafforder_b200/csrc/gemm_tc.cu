@@ -359,6 +359,7 @@ template <int MODE, int BN, class Wait>
 __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& src, long row0, int lane, int M, int N,
                                               int n0, long out_off, int half, int nhalves, const Wait& wait_acc,
                                               float4* stage) {
+  constexpr bool kF32 = MODE == GM_F32 || MODE == GM_F32_FOLD;
   const int ncols = min(BN, N - n0);
   const int nchunks = ncols / 32;
   const int c_lo = (nchunks * half) / nhalves, c_hi = (nchunks * (half + 1)) / nhalves;
@@ -368,7 +369,7 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
     const long row = row0 + lane;
     bool ok = row < M;
     long orow = row;
-    if (MODE == GM_F32 && e.rowmap == RM_WINDOW_TO_TOKEN) {
+    if (kF32 && e.rowmap == RM_WINDOW_TO_TOKEN) {
       long b = row / kWinRowsPerFrame;
       int rem = (int)(row - b * kWinRowsPerFrame);
       int win = rem / kWinTokens, t = rem - win * kWinTokens;
@@ -386,25 +387,69 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
 #pragma unroll
   for (int i = 0; i < 8; ++i) orow[i] = __shfl_sync(0xffffffffu, orow_own, i * 4 + sub);
 
-  const bool has_add = MODE == GM_F32 && e.addend != nullptr;
+  const bool has_add = kF32 && e.addend != nullptr;
   float4 nxt[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  auto fetch_row = [&](int c, int i) {
+    if (orow[i] >= 0) {
+      const long arow = e.add_mod > 0 ? (orow[i] % e.add_mod) : orow[i];
+      nxt[i] = *reinterpret_cast<const float4*>(e.addend + arow * (long)e.ld_add + n0 + c * 32 + cg * 4);
+    }
+  };
   auto fetch = [&](int c) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      if (orow[i] >= 0) {
-        const long arow = e.add_mod > 0 ? (orow[i] % e.add_mod) : orow[i];
-        nxt[i] = *reinterpret_cast<const float4*>(e.addend + arow * (long)e.ld_add + n0 + c * 32 + cg * 4);
-      }
-    }
+    for (int i = 0; i < 8; ++i) fetch_row(c, i);
   };
   auto bias4 = [&](int c) {
     return (MODE != GM_F16 && e.bias) ? __ldg(reinterpret_cast<const float4*>(e.bias + n0 + c * 32 + cg * 4))
                                       : make_float4(0.f, 0.f, 0.f, 0.f);
   };
+  // folded LayerNorm, consumer side: lane L derives rstd and -rstd * mean of accumulator row row0 + L from the
+  // producer's partial sums; the row loop below fetches the pair of row i*4 + sub by shuffle
+  constexpr bool kFoldIn = MODE == GM_BIAS_BF16 || MODE == GM_BIAS_GELU_BF16;
+  const bool fold_in = kFoldIn && e.stats_in != nullptr;
+  float rs_own = 1.f, nm_own = 0.f;
+  if constexpr (kFoldIn) if (fold_in) {
+    const long row = row0 + lane;
+    if (row < M) {
+      const float2* sp = reinterpret_cast<const float2*>(e.stats_in) + row * e.stats_slots;
+      float s1 = 0.f, s2 = 0.f;
+      for (int j = 0; j < e.stats_slots; ++j) {
+        const float2 v2 = __ldg(sp + j);
+        s1 += v2.x;
+        s2 += v2.y;
+      }
+      const float inv = 1.f / (float)e.stats_dim;
+      const float mu = s1 * inv;
+      rs_own = rsqrtf(fmaxf(s2 * inv - mu * mu, 0.f) + e.fold_eps);
+      nm_own = -rs_own * mu;
+    }
+  }
+  // the pairs of this lane's eight row slices (row i*4 + sub), fetched once per tile
+  float rs_i[kFoldIn ? 8 : 1], nm_i[kFoldIn ? 8 : 1];
+  if constexpr (kFoldIn) {
+    if (fold_in) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        rs_i[i] = __shfl_sync(0xffffffffu, rs_own, i * 4 + sub);
+        nm_i[i] = __shfl_sync(0xffffffffu, nm_own, i * 4 + sub);
+      }
+    }
+  }
+  auto foldc4 = [&](int c) {
+    return fold_in ? __ldg(reinterpret_cast<const float4*>(e.fold_c + n0 + c * 32 + cg * 4))
+                   : make_float4(0.f, 0.f, 0.f, 0.f);
+  };
+  // folded LayerNorm, producer side: lane (sub, cg) keeps the running {sum, sum of squares} of row cg*4 + sub
+  constexpr bool fold_out = MODE == GM_F32_FOLD;
+  float st_s = 0.f, st_q = 0.f;
   if (has_add && c_lo < c_hi) fetch(c_lo);
   float4 b_nxt = c_lo < c_hi ? bias4(c_lo) : make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 c_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+  if constexpr (kFoldIn) {
+    if (c_lo < c_hi) c_nxt = foldc4(c_lo);
+  }
   wait_acc();
   // Software pipeline, one chunk deep: the accumulator registers are dead as soon as they sit in the transposition
   // tile, so the tcgen05.ld of chunk c+1 (and its bias / addend loads) is in flight while chunk c is finished.
@@ -412,32 +457,39 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
   uint32_t v[32];
   if (c_lo < c_hi) tmem_ld_32x32(src.taddr + c_lo * 32, v);
   for (int c = c_lo; c < c_hi; ++c) {
-    float4 cur[8];
-    if (has_add) {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) cur[i] = nxt[i];
-      if (c + 1 < c_hi) fetch(c + 1);
-    }
     tmem_wait_ld();
 #pragma unroll
     for (int g = 0; g < 8; ++g)
       sts128(stage_s + (lane * 8 + (g ^ (lane & 7))) * 16, __uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]),
              __uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
     __syncwarp();
-    const float4 b4 = b_nxt;
+    const float4 b4 = b_nxt, c4 = c_nxt;
     if (c + 1 < c_hi) {
       tmem_ld_32x32(src.taddr + (c + 1) * 32, v);
       b_nxt = bias4(c + 1);
+      if constexpr (kFoldIn) c_nxt = foldc4(c + 1);
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int r = i * 4 + sub;
       float4 x = lds128(stage_s + (r * 8 + (cg ^ (r & 7))) * 16);
+      if constexpr (kFoldIn) {
+        if (fold_in) {
+          const float rs = rs_i[i], nm = nm_i[i];
+          x.x = fmaf(rs, x.x, nm * c4.x), x.y = fmaf(rs, x.y, nm * c4.y);
+          x.z = fmaf(rs, x.z, nm * c4.z), x.w = fmaf(rs, x.w, nm * c4.w);
+        }
+      }
       add4(x, b4);
       const bool st = orow[i] >= 0;   // predicated stores (no branch: the 8 row slices interleave)
       const long col = n0 + c * 32 + cg * 4;
-      if constexpr (MODE == GM_F32) {
-        if (has_add) add4(x, cur[i]);
+      if constexpr (kF32) {
+        if (has_add) {
+          // single-buffered prefetch of the residual rows: as soon as row slice i of this chunk is consumed its
+          // register is refilled with the same rows of the next chunk (one chunk of latency cover, 32 registers)
+          add4(x, nxt[i]);
+          if (c + 1 < c_hi) fetch_row(c + 1, i);
+        }
         float* op = reinterpret_cast<float*>(e.out) + orow[i] * (long)e.ld_out + col;
         if (e.ksplit > 1) {          // partial product of one K range: combine in place
           if (st) {
@@ -448,6 +500,22 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
           }
         } else if (st) {
           *reinterpret_cast<float4*>(op) = x;
+        }
+        if constexpr (fold_out) {
+        if (st) {
+          uint2 t;
+          t.x = pack_bf16(x.x, x.y);
+          t.y = pack_bf16(x.z, x.w);
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(e.xb_out) + orow[i] * (long)e.ld_out + col) = t;
+        }
+        {
+          float ps = (x.x + x.y) + (x.z + x.w);
+          float pq = fmaf(x.x, x.x, x.y * x.y) + fmaf(x.z, x.z, x.w * x.w);
+          ps += __shfl_xor_sync(0xffffffffu, ps, 1), pq += __shfl_xor_sync(0xffffffffu, pq, 1);
+          ps += __shfl_xor_sync(0xffffffffu, ps, 2), pq += __shfl_xor_sync(0xffffffffu, pq, 2);
+          ps += __shfl_xor_sync(0xffffffffu, ps, 4), pq += __shfl_xor_sync(0xffffffffu, pq, 4);
+          if (cg == i) st_s += ps, st_q += pq;       // the eight column lanes of row i*4 + sub hold the same totals
+        }
         }
       } else if constexpr (MODE == GM_F16) {
         const float ws = (e.rowmap == RM_RELW_SHIFT && col >= 128) ? e.relw_scale : 1.f;
@@ -483,6 +551,13 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
       }
     }
     __syncwarp();
+  }
+  if constexpr (fold_out) {
+    {       // also when this half owns no chunk: the slot is then written as zeros
+      const long row = row0 + cg * 4 + sub;
+      if (row < M)
+        reinterpret_cast<float2*>(e.stats_out)[row * e.stats_slots + (n0 / BN) * nhalves + half] = make_float2(st_s, st_q);
+    }
   }
 }
 
@@ -603,7 +678,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp >= 4) {
     const int ew = warp & 3;              // TMEM lane quadrant this warp may access
     const int eh = (warp - 4) >> 2;       // which half of the tile's column chunks
-    constexpr bool kSplit = MODE == GM_BIAS_BF16 || MODE == GM_BIAS_GELU_BF16 || MODE == GM_F32 || MODE == GM_F16;
+    constexpr bool kSplit = MODE == GM_BIAS_BF16 || MODE == GM_BIAS_GELU_BF16 || MODE == GM_F32 || MODE == GM_F16 ||
+                            MODE == GM_F32_FOLD;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int bidx = tile / tiles_per_batch, trem = tile - bidx * tiles_per_batch;
@@ -950,13 +1026,26 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
   if (e.batch != 1 && (mode != GM_F16 || tf32 || dbg || e.batch < 1)) return cudaErrorInvalidValue;
   if ((mode == GM_LN || mode == GM_UPS1) && N != 256) return cudaErrorInvalidValue;
   if (e.a_mode != AM_PLAIN && (dbg || tf32)) return cudaErrorInvalidValue;   // the SIMT bisect path reads a plain A
+  if (mode == GM_F32_FOLD &&
+      (tf32 || dbg || e.rowmap != RM_IDENT || e.ksplit > 1 || e.batch != 1 || !e.xb_out || !e.stats_out ||
+       e.stats_slots != 2 * ((N + 255) / 256)))
+    return cudaErrorInvalidValue;
+  if (e.stats_out || e.xb_out) {
+    if (mode != GM_F32_FOLD) return cudaErrorInvalidValue;
+  }
+  if (e.stats_in) {
+    if ((mode != GM_BIAS_BF16 && mode != GM_BIAS_GELU_BF16) || tf32 || dbg || !e.fold_c || !e.bias || e.stats_slots < 1 ||
+        e.stats_dim < 1)
+      return cudaErrorInvalidValue;
+  }
   if (e.ksplit > 1) {
     const int kblocks = (K + (tf32 ? 32 : 64) - 1) / (tf32 ? 32 : 64), kper = (kblocks + e.ksplit - 1) / e.ksplit;
     if (mode != GM_F32 || dbg || e.batch != 1 || e.bias || e.addend || e.a_mode != AM_PLAIN || e.rowmap != RM_IDENT ||
         (long)(e.ksplit - 1) * kper >= kblocks)      // every K range must hold at least one block
       return cudaErrorInvalidValue;
   }
-  if (e.a_mode == AM_PATCH16 && !(e.batch == 1 && M >= 1024 && N % 256 == 0 && mode == GM_F32)) return cudaErrorInvalidValue;
+  if (e.a_mode == AM_PATCH16 && !(e.batch == 1 && M >= 1024 && N % 256 == 0 && (mode == GM_F32 || mode == GM_F32_FOLD)))
+    return cudaErrorInvalidValue;
   if (mode == GM_UPS2 && N != 128) return cudaErrorInvalidValue;
   if (!tf32 && !dbg && e.batch == 1 && e.ksplit <= 1 && M >= 1024 && N % 256 == 0 && e.a_mode != AM_CONV3 &&
       (kernel_variant(VK_GEMM_PAIR) != 0 || e.a_mode == AM_PATCH16)) {
@@ -964,6 +1053,7 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
       case GM_BIAS_BF16: return launch2<GM_BIAS_BF16>(A, lda, W, ldw, M, N, K, e, s);
       case GM_BIAS_GELU_BF16: return launch2<GM_BIAS_GELU_BF16>(A, lda, W, ldw, M, N, K, e, s);
       case GM_F32: return launch2<GM_F32>(A, lda, W, ldw, M, N, K, e, s);
+      case GM_F32_FOLD: return launch2<GM_F32_FOLD>(A, lda, W, ldw, M, N, K, e, s);
       default: break;
     }
   }
@@ -972,6 +1062,7 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
       case GM_BIAS_BF16: return launch<false, GM_BIAS_BF16, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
       case GM_BIAS_GELU_BF16: return launch<false, GM_BIAS_GELU_BF16, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
       case GM_F32: return launch<false, GM_F32, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
+      case GM_F32_FOLD: return launch<false, GM_F32_FOLD, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
       case GM_LN: return launch<false, GM_LN, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
       case GM_F16: return launch<false, GM_F16, 256>(A, lda, W, ldw, M, N, K, e, s, dbg);
       default: return cudaErrorInvalidValue;

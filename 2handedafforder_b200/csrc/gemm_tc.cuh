@@ -15,6 +15,7 @@ enum GemmMode : int {
   GM_UPS1 = 4,            // N == 256 = 4 x 64: per 64-group LN (eps) -> GELU -> pixel-shuffle store (ConvT k2 s2)
   GM_UPS2 = 5,            // N == 128 = 4 x 32: GELU -> dot with hyper[p, 0:32] -> pixel-shuffle store of the mask logit
   GM_F16 = 6,             // out_f16[m, n] = acc (batched over column slices of A: rel-pos projections of every head)
+  GM_F32_FOLD = 7,        // GM_F32 + the producer side of the folded LayerNorm (bf16 copy, partial row sums); bf16 operands only
 };
 
 enum RowMap : int {
@@ -64,6 +65,20 @@ struct GemmEpi {
   // into `out`, which the caller has zeroed (no bias / addend / rowmap / batch); every piece must be non-empty.  For
   // products with a huge K and a small output (weight gradients: K = all rows of the batch).
   int ksplit = 1;
+  // ---- LayerNorm folded into the GEMM that consumes it (image_encoder.py:179,191: norm1 -> qkv, norm2 -> lin1):
+  //   LN(x) W^T + b = rstd * (x (gamma . W)^T) - rstd * mean * c + d,   c[n] = sum_k gamma[k] W[n,k],  d = W beta + b
+  // Producer side (GM_F32, the residual-stream epilogues of patch / proj / lin2): besides the fp32 rows the epilogue
+  // writes a bf16 copy (the A operand of the next GEMM) and, per row and 128-column half tile, the partial sums
+  // {sum x, sum x^2} into stats_out[(row * stats_slots + slot) * 2].
+  void* xb_out = nullptr;          // bf16 (M, ld_out)
+  float* stats_out = nullptr;
+  int stats_slots = 0;             // = ceil(N / BN) * 2 of the PRODUCING GEMM
+  // Consumer side (GM_BIAS_BF16 / GM_BIAS_GELU_BF16): W already holds bf16(gamma . W), `bias` holds d, fold_c holds c;
+  // mean / rstd of input row m come from stats_in (the producer's slots) over ln_dim = K columns.
+  const float* stats_in = nullptr;
+  const float* fold_c = nullptr;
+  float fold_eps = 0.f;
+  int stats_dim = 0;               // columns the producer's sums run over (= K of the consuming GEMM)
 };
 
 // A: (M, K) row-major with leading dimension lda (elements); W: (N, K) row-major, ldw.

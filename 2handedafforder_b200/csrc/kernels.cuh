@@ -13,6 +13,8 @@ cudaError_t launch_layernorm_bf16(const float* x, long rows, int D, const float*
                                   __nv_bfloat16* out, bool windowed, cudaStream_t s);
 cudaError_t launch_im2col_patch(const void* frames, int dtype, int B, __nv_bfloat16* out, cudaStream_t s);
 cudaError_t launch_im2col_3x3(const __nv_bfloat16* z, int B, __nv_bfloat16* out, cudaStream_t s);
+cudaError_t launch_fold_ln_weights(const float* Wt, const float* gamma, const float* beta, const float* bias, int N, int K,
+                                   __nv_bfloat16* Wf, float* c, float* d, cudaStream_t s);
 cudaError_t launch_tokens_to_nchw(const float* tok, int B, void* out, int dtype, cudaStream_t s);
 cudaError_t launch_nchw_to_tokens(const void* in, int dtype, int B, float* tok, cudaStream_t s);
 // window-pad rows of the packed qkv buffer (B*4900, 3D) := bias (qkv of a zero row, image_encoder.py:179-183 pads after norm1)
@@ -45,7 +47,7 @@ cudaError_t launch_attention_window_tc(const __nv_bfloat16* qkv, int nwin, int h
                                        __nv_bfloat16* out, cudaStream_t s, bool token_out = false);
 
 // Kernel variant switches for same-box A/B measurements (include/b200sam_debug.h); 0 = the shipped default.
-enum VariantKind : int { VK_ATTN_WINDOW = 0, VK_ATTN_GLOBAL = 1, VK_GEMM_PAIR = 2, VK_IMPLICIT_CONV = 3, VK_PREPROCESS = 4, VK_COUNT = 5 };
+enum VariantKind : int { VK_ATTN_WINDOW = 0, VK_ATTN_GLOBAL = 1, VK_GEMM_PAIR = 2, VK_IMPLICIT_CONV = 3, VK_PREPROCESS = 4, VK_LN_FOLD = 5, VK_COUNT = 6 };
 int kernel_variant(int which);
 void set_kernel_variant(int which, int value);
 // device buffer of at least 16 * 16 * 10 uint64 that the tracing kernel variants fill (null: tracing variants refuse)

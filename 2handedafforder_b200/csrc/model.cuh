@@ -25,6 +25,9 @@ struct EncBlock {
   const float *ln1g, *ln1b, *ln2g, *ln2b;
   const float *qkv_b, *proj_b, *lin1_b, *lin2_b;
   __nv_bfloat16 *qkv_w, *proj_w, *lin1_w, *lin2_w;
+  // LayerNorm folded into qkv / lin1 (launch_fold_ln_weights): bf16(gamma . W), c = its row sums, d = W beta + b
+  __nv_bfloat16 *qkv_wf = nullptr, *lin1_wf = nullptr;
+  float *qkv_c = nullptr, *qkv_d = nullptr, *lin1_c = nullptr, *lin1_d = nullptr;
   __nv_bfloat16 *relh, *relw;       // padded bf16 rel-pos tables
   __nv_bfloat16* relg = nullptr;    // global blocks: (256, 128) stacked + zero padded tables (B operand of the G GEMM)
 };
@@ -146,6 +149,8 @@ struct b200sam {
   // the next API call, which then fails (an out-of-range checkpoint must not produce quietly wrong masks)
   volatile int* ovf_host = nullptr;
   int* ovf_dev = nullptr;
+  float* ln_stats = nullptr;         // (B*4096, 2*ceil(D/256), 2) partial row sums of the residual stream (folded LayerNorm)
+  int ln_slots = 0;
   __nv_bfloat16* zpad = nullptr;     // (B, 66, 66, 256) neck.1 output with a zero ring (3x3 convolution operand)
   __nv_bfloat16* hid = nullptr;      // (B*4096, 4D) MLP hidden; also im2col scratch
   float* emb_tok = nullptr;          // (B*4096, 256) fp32 image embedding, token-major

@@ -20,11 +20,25 @@ torch.set_float32_matmul_precision("highest")
 
 
 def pkg():
+    if os.path.exists(libmod().lib_path()):
+        lib()                    # applies B200SAM_TEST_VARIANTS once
     return importlib.import_module(PKG)
 
 
+_VARIANTS_APPLIED = False
+
+
 def lib():
-    return importlib.import_module(PKG + "._lib").load()
+    """The loaded library.  B200SAM_TEST_VARIANTS="5=1,0=9" (kernel variant switches of include/b200sam_debug.h) runs
+    the whole suite under non-default kernels, e.g. the folded LayerNorm."""
+    global _VARIANTS_APPLIED
+    L = importlib.import_module(PKG + "._lib").load()
+    if not _VARIANTS_APPLIED:
+        _VARIANTS_APPLIED = True
+        for kv in filter(None, os.environ.get("B200SAM_TEST_VARIANTS", "").split(",")):
+            k, v = kv.split("=")
+            assert L.b200sam_debug_set_variant(int(k), int(v)) == 0
+    return L
 
 
 def libmod():

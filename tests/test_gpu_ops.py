@@ -212,3 +212,32 @@ def test_tma_gathered_convolutions_equal_the_im2col_path(arch_name, batch):
             assert torch.equal(got, want) and torch.equal(got2, want) and torch.equal(got3, want)
     finally:
         G.lib().b200sam_debug_set_variant(3, 0)
+
+
+@pytest.mark.parametrize("arch_name,batch", [("tiny64", 2), ("tiny80", 1)])
+def test_layernorm_folded_into_qkv_and_lin1(arch_name, batch):
+    """Shipped path (debug variant 5 = 0; 1 = stand-alone LayerNorm kernel): norm1 / norm2 (image_encoder.py:179,191) are
+    folded into the GEMMs that consume them,
+    LN(x) W^T + b = rstd * (x (gamma . W)^T) - rstd * mean * c + d, with the row sums produced by the residual-stream
+    epilogues (gemm_tc.cuh GemmEpi::stats_out / stats_in).  Same mathematics, different rounding points (x instead of
+    LN(x) is rounded to bf16), so the embeddings agree to the accuracy either path has against the fp32 oracle."""
+    from oracle import sam_oracle as O
+    sam, arch, sd = G.build_sam_from_synth(arch_name, max_batch=batch, max_prompts=1)
+    frames = synth.make_frames(5, batch)
+    ref = O.encode(sd, arch, frames, O.FP32)
+    x = frames.cuda().to(torch.bfloat16)
+    try:
+        assert G.lib().b200sam_debug_set_variant(5, 1) == 0
+        base = sam.get_visual_embs(x).float().cpu()
+        assert G.lib().b200sam_debug_set_variant(5, 0) == 0
+        fold = sam.get_visual_embs(x).float().cpu()
+        fold2 = sam.get_visual_embs(x).float().cpu()          # graph replay
+        fold3 = sam.get_visual_embs(x).float().cpu()
+    finally:
+        G.lib().b200sam_debug_set_variant(5, 0)
+    ref_b = O.encode(sd, arch, frames.to(torch.bfloat16).float(), O.FP32)
+    e_base, e_fold = O.logit_rel_err(base, ref_b), O.logit_rel_err(fold, ref_b)
+    assert torch.equal(fold, fold2) and torch.equal(fold, fold3)
+    assert e_base < 1.5e-2 and e_fold < 1.5e-2 and e_fold < 1.5 * e_base + 1e-3, (e_base, e_fold)
+    assert O.logit_rel_err(fold, base) < 1.5e-2
+    del ref
