@@ -27,10 +27,29 @@ import threading
 from dataclasses import dataclass, field
 from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
+import contextlib
+
 import torch
 import torch.distributed as dist
 
 OUT_CH = 256
+
+
+@contextlib.contextmanager
+def _nvtx(name: str):
+    """NVTX range per pipeline stage (nsys timelines, `ncu --nvtx`); a no-op without CUDA."""
+    pushed = False
+    try:
+        if torch.cuda.is_available():
+            torch.cuda.nvtx.range_push(name)
+            pushed = True
+    except Exception:
+        pushed = False
+    try:
+        yield
+    finally:
+        if pushed:
+            torch.cuda.nvtx.range_pop()
 
 
 def shard_range(n_frames: int, rank: int, world: int) -> Tuple[int, int]:
@@ -238,7 +257,7 @@ def segment_clip(segment_fn: Callable[..., Dict[str, object]],
             return None
         if up is None:
             return load_frames(a, b) + (None,)
-        with torch.cuda.stream(up):
+        with torch.cuda.stream(up), _nvtx("clip.load_frames"):
             frames, segs = load_frames(a, b)
             ev = torch.cuda.Event()
             ev.record(up)
@@ -297,7 +316,8 @@ def segment_clip(segment_fn: Callable[..., Dict[str, object]],
                 counts[: b - a] = [int(s.shape[0]) for s in segs]
                 if max(counts) > max_prompts_per_frame:
                     raise ValueError(f"a frame has more than max_prompts_per_frame={max_prompts_per_frame} prompts")
-                segment_fn(frames, segs, resize, original, threshold=threshold, bits_out=bits, heads_out=heads)
+                with _nvtx("clip.segment"):
+                    segment_fn(frames, segs, resize, original, threshold=threshold, bits_out=bits, heads_out=heads)
             counts_t.copy_(torch.tensor(counts, dtype=torch.int64), non_blocking=True)
             if checksum_fn is not None:
                 checksum_fn(bits.view(2 * lay.cap, lay.H, lay.Wb), out=sums)
@@ -307,7 +327,8 @@ def segment_clip(segment_fn: Callable[..., Dict[str, object]],
                 # the one exchange step: ONE gather per round, asynchronous so the next micro-batch's kernels
                 # overlap the NVLink transfer
                 dest = [recv[k][s] for s in range(world)] if is_dst else None
-                send_work[k] = dist.gather(slot, dest, dst=dst, group=group, async_op=True)
+                with _nvtx("clip.gather"):
+                    send_work[k] = dist.gather(slot, dest, dst=dst, group=group, async_op=True)
                 if is_dst:
                     deliver(rnd, recv[k])
             elif is_dst:
@@ -373,7 +394,7 @@ class HostPipeline:
     def submit(self, host_frames: torch.Tensor, host_seg: torch.Tensor) -> int:
         s = self.k % 2
         main = torch.cuda.current_stream(self.device)
-        with torch.cuda.stream(self.up):
+        with torch.cuda.stream(self.up), _nvtx("pipeline.h2d"):
             if self.k >= 2:
                 self.up.wait_event(self.in_free[s])                  # the step that last read this slot is done
             self.d_frames[s].copy_(host_frames, non_blocking=True)
@@ -384,12 +405,13 @@ class HostPipeline:
             main.wait_event(self.down_done[s])                       # d_out[s] was downloaded (step k-2)
         segs = [self.d_seg[s][i * self.NP:(i + 1) * self.NP] for i in range(self.B)]
         bits, heads, counts, _ = self.lay.views(self.d_out[s])
-        self.segment_fn(self.d_frames[s], segs, self.resize, self.original, threshold=self.threshold, bits_out=bits,
-                        heads_out=heads)
+        with _nvtx("pipeline.segment"):
+            self.segment_fn(self.d_frames[s], segs, self.resize, self.original, threshold=self.threshold, bits_out=bits,
+                            heads_out=heads)
         if self.k < 2:
             counts.fill_(self.NP)
         self.in_free[s].record(main)
-        with torch.cuda.stream(self.down):
+        with torch.cuda.stream(self.down), _nvtx("pipeline.d2h"):
             self.down.wait_event(self.in_free[s])
             self.host_out[s].copy_(self.d_out[s], non_blocking=True)
             self.down_done[s].record(self.down)

@@ -14,6 +14,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/b200sam.h"
 #include "../../include/b200sam_debug.h"
 #include "common.cuh"
@@ -35,6 +37,16 @@ int fail(b200sam_t* h, int code, const char* fmt, ...) {
   if (h) h->err = buf;
   return code;
 }
+
+// NVTX range per stage of the path ("Tracing / profiling"): visible to nsys timelines and usable as
+// an ncu filter (`ncu --nvtx --nvtx-include "b200sam_decode/" ...`).  Header-only NVTX3: a no-op costing a few
+// nanoseconds when no tool is attached.
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 #define CU(call)                                                                                   \
   do {                                                                                             \
@@ -354,6 +366,7 @@ int finalize_side(b200sam_t* h, int s) {
 
 // bf16 GEMM operand packs, padded rel-pos tables and the permuted neck conv weight of the image encoder
 int finalize_encoder(b200sam_t* h) {
+  NvtxRange nvtx_("finalize_encoder");
   free_list(h->derived_enc);
   AllocScope scope(h, &h->derived_enc);
   const long D = h->dim;
@@ -415,6 +428,7 @@ int finalize_encoder(b200sam_t* h) {
 
 // prompt-encoder constants + both mask decoders
 int finalize_decoders(b200sam_t* h) {
+  NvtxRange nvtx_("finalize_decoders");
   free_list(h->derived_dec);
   AllocScope scope(h, &h->derived_dec);
   // prompt encoder constants (prompt_encoder.py:67-76,182-184): dense PE once, in fp32
@@ -741,6 +755,7 @@ namespace {
 bool ln_fold_on(const b200sam_t* h) { return kernel_variant(VK_LN_FOLD) == 0 && !h->debug_simt; }
 
 int encode_patch(b200sam_t* h, const void* frames, int frames_dtype, int B, cudaStream_t s) {
+  NvtxRange nvtx_("patch_embed");
   const int D = h->dim;
   const long T = (long)B * kTokens;
   GemmEpi e;
@@ -780,6 +795,7 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
   const bool fold = ln_fold_on(h);
   for (int i = 0; i < nblocks; ++i) {
     const EncBlock& b = h->blk[i];
+    NvtxRange nvtx_blk(b.global ? "block_global" : "block_windowed");
     // norm1 in token order.  The windowed blocks never materialise the zero-padded window tensor: the qkv epilogue
     // scatters the 4096 real rows of a frame into the 4900-row window layout (window_partition, image_encoder.py:263-288),
     // the 804 pad rows (zero after norm1 => qkv = bias, :179-183) are filled by a small kernel, and the attention
@@ -859,6 +875,7 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
   }
   if (nblocks != h->depth) return 1;   // debug: residual stream after `nblocks` blocks is left in X
   // neck (image_encoder.py:92-108): conv1x1 -> LayerNorm2d -> conv3x3 -> LayerNorm2d, token-major
+  NvtxRange nvtx_neck("neck");
   h->pc = B200SAM_PC_NECK;
   if (!fold) KL(launch_cast_f32_bf16(h->X, h->ln_plain, T * D, s));     // folded: the last lin2 epilogue wrote the bf16 rows
   // neck.2 Conv2d 3x3: the GEMM gathers its A tiles from the zero-ringed neck.1 output (AM_CONV3); the SIMT bisect
@@ -949,6 +966,7 @@ int encode_body_graphed(b200sam_t* h, int B, cudaStream_t s) {
 
 extern "C" int b200sam_encode(b200sam_t* h, const void* frames, int frames_dtype, int B, void* emb_out, int emb_dtype,
                               void* stream) {
+  NvtxRange nvtx_("b200sam_encode");
   if (int r = check_ready(h)) return r;
   if (B < 0 || B > h->max_batch) return fail(h, B200SAM_ERR_INVALID, "batch %d exceeds max_batch %d", B, h->max_batch);
   if (B == 0) return 0;
@@ -978,6 +996,7 @@ namespace {
 
 int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, int P, float* lowres, float* iou,
                 float* tax, cudaStream_t s) {
+  NvtxRange nvtx_(sidx == 0 ? "mask_decoder_left" : "mask_decoder_right");
   const DecSide& d = h->side[sidx];
   const DecWorkspace& w = h->dws[sidx];   // one workspace per side: the two decoders run concurrently
   const long rows = (long)P * kTokens;
@@ -1105,6 +1124,7 @@ int decode_side(b200sam_t* h, int sidx, const float* emb_tok, const float* seg, 
 extern "C" int b200sam_decode(b200sam_t* h, const void* emb, int emb_dtype, int B, const float* seg_embeds,
                               const int* host_prompt_offsets, float* lowres_left, float* lowres_right, float* iou_left,
                               float* iou_right, float* taxonomy, void* stream) {
+  NvtxRange nvtx_("b200sam_decode");
   if (int r = check_ready(h)) return r;
   if (B < 0 || B > h->max_batch) return fail(h, B200SAM_ERR_INVALID, "batch %d exceeds max_batch %d", B, h->max_batch);
   if (!host_prompt_offsets) return fail(h, B200SAM_ERR_INVALID, "host_prompt_offsets is NULL");
@@ -1158,6 +1178,7 @@ extern "C" int b200sam_decode(b200sam_t* h, const void* emb, int emb_dtype, int 
 
 extern "C" int b200sam_postprocess(b200sam_t* h, const float* lowres, int n_masks, int in_h, int in_w, int out_h,
                                    int out_w, float* logits_out, uint8_t* mask_out, float threshold, void* stream) {
+  NvtxRange nvtx_("b200sam_postprocess");
   if (!h) return B200SAM_ERR_INVALID;
   if (n_masks < 0 || in_h < 1 || in_w < 1 || in_h > kImg || in_w > kImg || out_h < 1 || out_w < 1)
     return fail(h, B200SAM_ERR_INVALID, "bad postprocess sizes n=%d in=(%d,%d) out=(%d,%d)", n_masks, in_h, in_w, out_h,
@@ -1174,6 +1195,7 @@ extern "C" int b200sam_postprocess(b200sam_t* h, const float* lowres, int n_mask
 
 extern "C" int b200sam_postprocess_bits(b200sam_t* h, const float* lowres, int n_masks, int in_h, int in_w, int out_h,
                                         int out_w, uint8_t* bits_out, float threshold, void* stream) {
+  NvtxRange nvtx_("b200sam_postprocess");
   if (!h) return B200SAM_ERR_INVALID;
   if (n_masks < 0 || in_h < 1 || in_w < 1 || in_h > kImg || in_w > kImg || out_h < 1 || out_w < 1)
     return fail(h, B200SAM_ERR_INVALID, "bad postprocess sizes n=%d in=(%d,%d) out=(%d,%d)", n_masks, in_h, in_w, out_h,
@@ -1193,6 +1215,7 @@ extern "C" int b200sam_postprocess_pair(b200sam_t* h, const float* lowres_left, 
                                         uint8_t* bits_right, float threshold, const float* taxonomy,
                                         const uint8_t* gt, const int* gt_index, int64_t* counts_out,
                                         uint8_t* pred_bits_out, void* stream) {
+  NvtxRange nvtx_("b200sam_postprocess");
   if (!h) return B200SAM_ERR_INVALID;
   if (P < 0 || in_h < 1 || in_w < 1 || in_h > kImg || in_w > kImg || out_h < 1 || out_w < 1)
     return fail(h, B200SAM_ERR_INVALID, "bad postprocess sizes P=%d in=(%d,%d) out=(%d,%d)", P, in_h, in_w, out_h, out_w);
@@ -1211,6 +1234,7 @@ extern "C" int b200sam_postprocess_pair(b200sam_t* h, const float* lowres_left, 
 
 extern "C" int b200sam_checksum64(b200sam_t* h, const void* data, int n_items, int64_t bytes, int64_t stride,
                                   uint64_t* out, void* stream) {
+  NvtxRange nvtx_("b200sam_checksum64");
   if (!h) return B200SAM_ERR_INVALID;
   if (n_items < 0 || n_items > 65535 || bytes < 0 || stride < bytes)
     return fail(h, B200SAM_ERR_INVALID, "bad checksum sizes n=%d bytes=%lld stride=%lld", n_items, (long long)bytes,
@@ -1299,6 +1323,7 @@ int resample_tables(b200sam_t* h, int H, int W, const ResampleTables** out) {
 
 extern "C" int b200sam_preprocess(b200sam_t* h, const uint8_t* frames_rgb, int B, int H, int W, void* out,
                                   int out_dtype, int* host_resize_hw, void* stream) {
+  NvtxRange nvtx_("b200sam_preprocess");
   if (!h) return B200SAM_ERR_INVALID;
   if (B < 0 || H < 1 || W < 1 || H > 16384 || W > 16384)
     return fail(h, B200SAM_ERR_INVALID, "bad preprocess sizes B=%d H=%d W=%d", B, H, W);
@@ -1321,6 +1346,7 @@ extern "C" int b200sam_seg_project(b200sam_t* h, const void* hidden, int hidden_
                                    const int64_t* output_ids, int T, int64_t seg_token_idx, const void* w1,
                                    const void* b1, const void* w2, const void* b2, int w_dtype, float* emb_out,
                                    int max_rows, int* counts_out, void* stream) {
+  NvtxRange nvtx_("b200sam_seg_project");
   if (!h) return B200SAM_ERR_INVALID;
   if (b < 1 || b > 1024 || T < 1 || hdim < 8 || hdim % 8 != 0 || max_rows < 1)
     return fail(h, B200SAM_ERR_INVALID, "bad seg_project sizes b=%d T=%d hdim=%d max_rows=%d", b, T, hdim, max_rows);
@@ -1357,6 +1383,7 @@ extern "C" int b200sam_seg_project(b200sam_t* h, const void* hidden, int hidden_
 extern "C" int b200sam_mask_metrics(b200sam_t* h, const uint8_t* masks_left, const uint8_t* masks_right,
                                     const float* taxonomy, const uint8_t* gt, const int* gt_index, int P, int H,
                                     int W, int64_t* counts_out, uint8_t* pred_out, void* stream) {
+  NvtxRange nvtx_("b200sam_mask_metrics");
   if (!h) return B200SAM_ERR_INVALID;
   if (P < 0 || P > 65535 || H < 1 || W < 1)
     return fail(h, B200SAM_ERR_INVALID, "bad mask_metrics sizes P=%d H=%d W=%d", P, H, W);
