@@ -97,6 +97,26 @@ def test_weights_follow_parameter_updates(tiny):
         p.copy_(keep)
     assert torch.allclose(b, a + 1.0, atol=1e-5)
     assert torch.equal(sam.image_encoder(frames), a)
+    # a LayerNorm weight of the encoder: the folded qkv / lin1 weights (gamma . W, c, d) are derived buffers and must be
+    # rebuilt; the stand-alone LayerNorm path (debug variant 5 = 1) is the reference for the new value
+    blk = sam.image_encoder.blocks._modules["0"]
+    keep_g, keep_b = blk.norm1.weight.detach().clone(), blk.norm2.bias.detach().clone()
+    try:
+        with torch.no_grad():
+            blk.norm1.weight.mul_(1.5)
+            blk.norm2.bias.add_(0.25)
+        folded = sam.image_encoder(frames).clone()
+        assert G.lib().b200sam_debug_set_variant(5, 1) == 0
+        standalone = sam.image_encoder(frames).clone()
+        assert G.lib().b200sam_debug_set_variant(5, 0) == 0
+        assert G.rel_err(folded, a) > 1e-2                       # the update is visible
+        assert G.rel_err(folded, standalone) < 1.5e-2            # and both LayerNorm paths see the same new weights
+    finally:
+        G.lib().b200sam_debug_set_variant(5, 0)
+        with torch.no_grad():
+            blk.norm1.weight.copy_(keep_g)
+            blk.norm2.bias.copy_(keep_b)
+    assert torch.equal(sam.image_encoder(frames), a)
 
 
 @pytest.mark.parametrize("resize,original", [((576, 1024), (1080, 1920)), ((1024, 683), (300, 200)),
