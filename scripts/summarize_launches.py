@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Summarise the ncu light-metrics pass of scripts/gpu_prof_r4.sh: per kernel name (B = 8 launches only for the
 encoder kernels) count, mean duration and mean DRAM read + write bytes; writes the per-class traffic that bench.py
-reports as roofline.traffic.  usage: summarize_launches.py gpurun_out/r4_launches.csv profiles/"""
+reports as roofline.traffic.  usage: summarize_launches.py gpurun_out/r4_launches.csv profiles/ [tag]"""
 import collections
 import csv
 import json
@@ -46,7 +46,7 @@ for d in L:
         key = "gemm_qkv"
     elif re.match(r"gemm_tc2_kernel<(\(int\))?1>", n):
         key = "gemm_lin1"
-    elif re.match(r"gemm_tc2_kernel<(\(int\))?2>", n):
+    elif re.match(r"gemm_tc2_kernel<(\(int\))?[27]>", n):      # 2 = GM_F32, 7 = GM_F32_FOLD (same role with the folded LayerNorm)
         # fp32-residual epilogue: proj directly follows the block's attention kernel, lin2 follows lin1 (+GELU); the
         # remaining one per encode is the patch embedding
         key = "gemm_proj" if was.startswith("attn_") else "gemm_lin2" if was.startswith("gemm_tc2_kernel") else "gemm_patch"
@@ -66,7 +66,8 @@ byname = collections.defaultdict(list)
 for d in L:
     byname[short(d["name"])].append((d.get("gpu__time_duration.sum", 0.0),
                                      d.get("dram__bytes_read.sum", 0.0) + d.get("dram__bytes_write.sum", 0.0)))
-with open(os.path.join(outdir, "r4_launch_summary.csv"), "w") as fh:
+tag = sys.argv[3] if len(sys.argv) > 3 else "r4"
+with open(os.path.join(outdir, f"{tag}_launch_summary.csv"), "w") as fh:
     fh.write("# ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none over "
              "`bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-train` (all launches of the process, warm-up, latency and "
              "profiling passes included; cold-cache serialised timings)\nkernel,launches,mean_us,total_ms,mean_dram_MB\n")
@@ -79,7 +80,7 @@ for k, v in cls.items():
     tmax = max(x[0] for x in v)
     big = [x for x in v if x[0] > 0.5 * tmax]
     traffic[k] = sum(x[1] for x in big) / len(big)
-traffic["_source"] = ("ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum --clock-control none, capture r4 "
+traffic["_source"] = (f"ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum --clock-control none, capture {tag} "
                       "(scripts/gpu_prof_r4.sh): mean per launch over the 8-frame launches of each class")
 json.dump(traffic, open(os.path.join(outdir, "ncu_traffic.json"), "w"), indent=1)
 print(json.dumps(traffic, indent=1))
