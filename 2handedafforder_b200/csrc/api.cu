@@ -914,7 +914,8 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
 // debug switches and a caller who is capturing the stream himself use the plain launch sequence.
 int encode_body_graphed(b200sam_t* h, int B, cudaStream_t s) {
   const int sig = kernel_variant(VK_ATTN_WINDOW) * 10000 + kernel_variant(VK_ATTN_GLOBAL) * 100 +
-                  kernel_variant(VK_GEMM_PAIR) * 10 + kernel_variant(VK_IMPLICIT_CONV) + kernel_variant(VK_LN_FOLD) * 1000000;
+                  kernel_variant(VK_GEMM_PAIR) * 10 + kernel_variant(VK_IMPLICIT_CONV) + kernel_variant(VK_LN_FOLD) * 1000000 +
+                  kernel_variant(VK_PDL) * 10000000;
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
   const bool plain = h->prof_on || h->debug_simt || h->debug_stop_block >= 0 || !h->use_graphs ||
                      cudaStreamIsCapturing(s, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone;

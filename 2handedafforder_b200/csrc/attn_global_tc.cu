@@ -80,6 +80,7 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
                       const __grid_constant__ CUtensorMap tmG,
                       const __half* __restrict__ G, __nv_bfloat16* __restrict__ out, int nbatch, int heads,
                       float scale, unsigned long long* __restrict__ trace) {
+  griddep_launch_dependents();
   auto mark = [&](int w, int item_it, int j, int tag) {
     if constexpr (TRACE) {
       if (blockIdx.x == 0 && item_it == 1 && j < 16) trace[(w * 16 + j) * 10 + tag] = clock64();
@@ -144,6 +145,7 @@ attn_global_tc_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  griddep_wait();     // PDL: barrier / TMEM / one-hot operand set-up overlapped the tail of the rel-pos GEMM
   // register re-allocation between the warpgroups: the softmax threads keep a 128-key score row + 64 bias values
   // (setmaxnreg at the top of every role branch)
 
@@ -509,8 +511,9 @@ cudaError_t launch_global(const __nv_bfloat16* qkv, int nbatch, int heads, const
     static std::atomic<uint64_t> attr{0};                                                                          \
     e = smem_opt_in(attn_global_tc_kernel<HD, POLY, TRACE>, C::kSmem, attr);                                       \
     if (e != cudaSuccess) return e;                                                                                \
-    attn_global_tc_kernel<HD, POLY, TRACE><<<grid, kThreadsG, C::kSmem, s>>>(tm128, tm32, tmG, G, out, nbatch,     \
-                                                                             heads, scale, TRACEPTR);              \
+    e = launch_pdl(attn_global_tc_kernel<HD, POLY, TRACE>, dim3(grid), dim3(kThreadsG), C::kSmem, s, tm128, tm32, tmG, G, \
+                   out, nbatch, heads, scale, (unsigned long long*)(TRACEPTR));                                     \
+    if (e != cudaSuccess) return e;                                                                                \
   } while (0)
   if (variant == 2) BSAM_LAUNCH_GLOBAL(true, true, tr);
   else if (variant == 1) BSAM_LAUNCH_GLOBAL(false, false, nullptr);

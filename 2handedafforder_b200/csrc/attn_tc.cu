@@ -389,6 +389,7 @@ attn_window_tc_kernel_v1(const __grid_constant__ CUtensorMap tm128, const __grid
                          const __grid_constant__ CUtensorMap tmQb128, const __grid_constant__ CUtensorMap tmQb32,
                          __nv_bfloat16* __restrict__ out, int nwin, int heads, float scale, int token_out,
                          unsigned long long* __restrict__ trace) {
+  griddep_launch_dependents();
   auto mark = [&](int w, int it, int tag) {
     if constexpr (TRACE) {
       if (blockIdx.x == 0 && it < kTraceIts) trace[(w * kTraceIts + it) * kTraceTags + tag] = clock64();
@@ -472,6 +473,7 @@ attn_window_tc_kernel_v1(const __grid_constant__ CUtensorMap tm128, const __grid
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  griddep_wait();     // PDL: the set-up above overlapped the tail of the qkv GEMM / pad-row fill
 
   if (warp == 0) {
     if (lane == 0) {
@@ -932,9 +934,10 @@ cudaError_t launch_window(const __nv_bfloat16* qkv, int nwin, int heads, const _
       static std::atomic<uint64_t> attr1{0};
       e = smem_opt_in(attn_window_tc_kernel_v1<HD, false>, C::kSmem + Win1Extra<HD>::value, attr1);
       if (e != cudaSuccess) return e;
-      attn_window_tc_kernel_v1<HD, false><<<grid, kThreadsWin1, C::kSmem + Win1Extra<HD>::value, s>>>(
-          tm128, tm32, tmR128, tmR32, tmQa128, tmQa32, tmQb128, tmQb32, out, nwin, heads, scale,
-          (token_out ? 1 : 0) | (variant == 4 ? 4 : 0), nullptr);
+      e = launch_pdl(attn_window_tc_kernel_v1<HD, false>, dim3(grid), dim3(kThreadsWin1), C::kSmem + Win1Extra<HD>::value, s,
+                     tm128, tm32, tmR128, tmR32, tmQa128, tmQa32, tmQb128, tmQb32, out, nwin, heads, scale,
+                     (token_out ? 1 : 0) | (variant == 4 ? 4 : 0), (unsigned long long*)nullptr);
+      if (e != cudaSuccess) return e;
       break;
     }
     case 3:     // variant 2 without the global stores of O (measurement only: how much of the chain is the store?)

@@ -88,6 +88,15 @@ __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
 }
+// Programmatic dependent launch (PDL): a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may
+// start while its predecessor in the stream still runs.  launch_dependents lets the successor's CTAs be scheduled as
+// soon as every CTA of this grid is resident; wait blocks until the predecessor grid has completed and its memory is
+// visible.  Everything before the wait (barrier init, TMEM allocation, descriptor prefetch) overlaps the predecessor's
+// tail; no global memory that another kernel writes or reads may be touched before it.  Both are no-ops for a kernel
+// launched without the attribute.
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // 2-D tiled load: coordinates are (inner = element column, outer = row).
 __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tm, uint64_t* bar, int c_inner,
                                             int c_outer) {

@@ -234,6 +234,8 @@ cudaError_t launch_layernorm_bf16(const float* x, long rows, int D, const float*
 __global__ void __launch_bounds__(128) fill_pad_rows_kernel(__nv_bfloat16* __restrict__ qkv,
                                                             const float* __restrict__ bias,
                                                             const int* __restrict__ pad_rows, int cols) {
+  griddep_launch_dependents();
+  griddep_wait();     // PDL: keeps the chain qkv GEMM -> fill -> attention transitive (the attention waits only on this grid)
   const int rem = pad_rows[blockIdx.x];
   uint2* o = reinterpret_cast<uint2*>(qkv + ((long)blockIdx.y * kWinRowsPerFrame + rem) * cols);
   const float4* b4 = reinterpret_cast<const float4*>(bias);
@@ -250,8 +252,7 @@ cudaError_t launch_fill_pad_rows(__nv_bfloat16* qkv, const float* bias, const in
                                  int cols, cudaStream_t s) {
   if (B <= 0 || n_pad <= 0) return cudaSuccess;
   if (cols % 4 != 0) return cudaErrorInvalidValue;
-  fill_pad_rows_kernel<<<dim3(n_pad, B), 128, 0, s>>>(qkv, bias, pad_rows, cols);
-  return cudaGetLastError();
+  return launch_pdl(fill_pad_rows_kernel, dim3(n_pad, B), dim3(128), 0, s, qkv, bias, pad_rows, cols);
 }
 
 cudaError_t launch_im2col_patch(const void* frames, int dtype, int B, __nv_bfloat16* out, cudaStream_t s) {

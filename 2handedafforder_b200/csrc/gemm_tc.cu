@@ -565,6 +565,7 @@ template <bool kTf32, int MODE, int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                GemmEpi e) {
+  griddep_launch_dependents();
   using Cfg = TileCfg<BN>;
   constexpr int kStages = Cfg::kStages;
   constexpr int kBK = kTf32 ? 32 : 64;                 // elements per 128-byte row
@@ -612,6 +613,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_wait();     // PDL: everything above overlapped the previous kernel's tail
 
   if (warp == 0) {
     if (lane == 0) {
@@ -724,6 +726,7 @@ template <int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                 GemmEpi e) {
+  griddep_launch_dependents();
   constexpr int BN = 256;
   constexpr uint32_t kIdesc = umma_idesc_bf16(256, BN, false, false);
   extern __shared__ uint8_t smem_raw[];
@@ -763,6 +766,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  griddep_wait();     // PDL: everything above overlapped the previous kernel's tail
 
   if (warp == 0) {
     if (lane == 0) {
@@ -942,8 +946,8 @@ cudaError_t launch(const void* A, int lda, const void* W, int ldw, int M, int N,
   const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * (e.ksplit > 1 ? e.ksplit : e.batch);
   const int n_sm = gemm_num_sms();
   const int grid = tiles < n_sm ? tiles : n_sm;
-  gemm_tc_kernel<kTf32, MODE, BN><<<grid, kThreads, TileCfg<BN>::kSmemBytes, stream>>>(tmA, tmB, M, N, K, e);
-  return cudaGetLastError();
+  return launch_pdl(gemm_tc_kernel<kTf32, MODE, BN>, dim3(grid), dim3(kThreads), TileCfg<BN>::kSmemBytes, stream, tmA, tmB, M, N,
+                    K, e);
 }
 
 template <int MODE>
@@ -967,8 +971,7 @@ cudaError_t launch2(const void* A, int lda, const void* W, int ldw, int M, int N
   const int tiles = ((M + 255) / 256) * ((N + 255) / 256);
   int pairs = gemm_num_sms() / 2;
   if (tiles < pairs) pairs = tiles;
-  gemm_tc2_kernel<MODE><<<2 * pairs, kThreads, kSmemBytes2, stream>>>(tmA, tmB, M, N, K, e);
-  return cudaGetLastError();
+  return launch_pdl(gemm_tc2_kernel<MODE>, dim3(2 * pairs), dim3(kThreads), kSmemBytes2, stream, tmA, tmB, M, N, K, e);
 }
 
 }  // namespace

@@ -47,11 +47,27 @@ cudaError_t launch_attention_window_tc(const __nv_bfloat16* qkv, int nwin, int h
                                        __nv_bfloat16* out, cudaStream_t s, bool token_out = false);
 
 // Kernel variant switches for same-box A/B measurements (include/b200sam_debug.h); 0 = the shipped default.
-enum VariantKind : int { VK_ATTN_WINDOW = 0, VK_ATTN_GLOBAL = 1, VK_GEMM_PAIR = 2, VK_IMPLICIT_CONV = 3, VK_PREPROCESS = 4, VK_LN_FOLD = 5, VK_COUNT = 6 };
+enum VariantKind : int { VK_ATTN_WINDOW = 0, VK_ATTN_GLOBAL = 1, VK_GEMM_PAIR = 2, VK_IMPLICIT_CONV = 3, VK_PREPROCESS = 4, VK_LN_FOLD = 5, VK_PDL = 6, VK_COUNT = 7 };
 int kernel_variant(int which);
 void set_kernel_variant(int which, int value);
 // device buffer of at least 16 * 16 * 10 uint64 that the tracing kernel variants fill (null: tracing variants refuse)
 void* debug_trace_buffer();
+
+// Launch with the programmatic-dependent-launch attribute (common.cuh griddep_*) when variant 6 is on.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = kernel_variant(VK_PDL) == 1 ? 1 : 0;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
 void set_debug_trace_buffer(void* dev_ptr);
 
 // ---- decoder.cu

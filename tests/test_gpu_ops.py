@@ -241,3 +241,20 @@ def test_layernorm_folded_into_qkv_and_lin1(arch_name, batch):
     assert e_base < 1.5e-2 and e_fold < 1.5e-2 and e_fold < 1.5 * e_base + 1e-3, (e_base, e_fold)
     assert O.logit_rel_err(fold, base) < 1.5e-2
     del ref
+
+
+def test_programmatic_dependent_launch_gives_identical_embeddings():
+    """Debug variant 6 = 1 launches the GEMMs, both attention kernels and the pad-row fill with the programmatic
+    dependent launch attribute (their barrier / TMEM set-up overlaps the previous kernel's tail; griddepcontrol.wait
+    before the first global access).  Ordering only: the embeddings are bit-identical, eager and as a CUDA graph."""
+    sam, arch, sd = G.build_sam_from_synth("tiny80", max_batch=2, max_prompts=1)
+    x = synth.make_frames(11, 2).cuda().to(torch.bfloat16)
+    try:
+        assert G.lib().b200sam_debug_set_variant(6, 0) == 0
+        want = sam.get_visual_embs(x)
+        assert G.lib().b200sam_debug_set_variant(6, 1) == 0
+        got = [sam.get_visual_embs(x) for _ in range(4)]          # eager, capture, two replays
+        torch.cuda.synchronize()
+    finally:
+        G.lib().b200sam_debug_set_variant(6, 0)
+    assert all(torch.equal(g, want) for g in got)
