@@ -84,27 +84,55 @@ constexpr int kCl = 8;
 
 // Features [rank*OUT/8, (rank+1)*OUT/8) of y = act(x W^T + b) for R rows; x in local smem; the slice is written to
 // `ys` (same smem offset) in every CTA of the cluster.  Caller must cluster.sync() before anyone reads ys.
-template <int R>
-__device__ void cl_linear(cg::cluster_group& cl, const float* __restrict__ xs, int IN, const float* __restrict__ W,
-                          const float* __restrict__ b, int OUT, float* ys, int ldy, bool relu) {
+// Each warp works on kLinU output features at a time: kLinU independent 16-byte weight loads are in flight per lane
+// (the loop used to expose one L2 latency per feature) and every activation vector read from shared memory is used
+// for kLinU dot products.  The sum of every single feature is formed in the same order as before.
+constexpr int kLinU = 4;
+
+template <int R, class Store>
+__device__ __forceinline__ void cl_linear_core(const float* __restrict__ xs, int IN, const float* __restrict__ W, int o_lo,
+                                               int o_hi, const Store& store) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-  const int per = OUT / kCl, o_lo = (int)cl.block_rank() * per;
-  float* dst = cl.map_shared_rank(ys, lane & (kCl - 1));
-  for (int o = o_lo + warp; o < o_lo + per; o += nw) {
-    const float4* wr = reinterpret_cast<const float4*>(W + (long)o * IN);
-    float acc[R];
+  for (int o0 = o_lo + warp; o0 < o_hi; o0 += nw * kLinU) {
+    const float4* wr[kLinU];
+    float acc[kLinU][R];
 #pragma unroll
-    for (int r = 0; r < R; ++r) acc[r] = 0.f;
+    for (int u = 0; u < kLinU; ++u) {
+      const int o = o0 + u * nw;
+      wr[u] = reinterpret_cast<const float4*>(W + (long)(o < o_hi ? o : o0) * IN);
+#pragma unroll
+      for (int r = 0; r < R; ++r) acc[u][r] = 0.f;
+    }
     for (int i = lane; i < IN / 4; i += 32) {
-      const float4 wv = __ldg(wr + i);
+      float4 wv[kLinU];
+#pragma unroll
+      for (int u = 0; u < kLinU; ++u) wv[u] = __ldg(wr[u] + i);
 #pragma unroll
       for (int r = 0; r < R; ++r) {
         const float4 xv = *reinterpret_cast<const float4*>(xs + r * IN + 4 * i);
-        acc[r] += wv.x * xv.x + wv.y * xv.y + wv.z * xv.z + wv.w * xv.w;
+#pragma unroll
+        for (int u = 0; u < kLinU; ++u) acc[u][r] += wv[u].x * xv.x + wv[u].y * xv.y + wv[u].z * xv.z + wv[u].w * xv.w;
       }
     }
 #pragma unroll
-    for (int r = 0; r < R; ++r) acc[r] = warp_sum(acc[r]);
+    for (int u = 0; u < kLinU; ++u) {
+      const int o = o0 + u * nw;
+      if (o < o_hi) {                      // warp-uniform
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[u][r] = warp_sum(acc[u][r]);
+        store(o, acc[u]);
+      }
+    }
+  }
+}
+
+template <int R>
+__device__ void cl_linear(cg::cluster_group& cl, const float* __restrict__ xs, int IN, const float* __restrict__ W,
+                          const float* __restrict__ b, int OUT, float* ys, int ldy, bool relu) {
+  const int lane = threadIdx.x & 31;
+  const int per = OUT / kCl, o_lo = (int)cl.block_rank() * per;
+  float* dst = cl.map_shared_rank(ys, lane & (kCl - 1));
+  cl_linear_core<R>(xs, IN, W, o_lo, o_lo + per, [&](int o, const float (&acc)[R]) {
     if (lane < kCl) {
       const float bb = b ? __ldg(b + o) : 0.f;
 #pragma unroll
@@ -113,7 +141,7 @@ __device__ void cl_linear(cg::cluster_group& cl, const float* __restrict__ xs, i
         dst[r * ldy + o] = relu ? fmaxf(v, 0.f) : v;
       }
     }
-  }
+  });
 }
 
 // Same split, result straight to global memory (row stride ldy).
@@ -121,30 +149,16 @@ template <int R>
 __device__ void cl_linear_global(cg::cluster_group& cl, const float* __restrict__ xs, int IN,
                                  const float* __restrict__ W, const float* __restrict__ b, int OUT,
                                  float* __restrict__ yg, int ldy) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31;
   const int per = (OUT + kCl - 1) / kCl, o_lo = (int)cl.block_rank() * per;
   const int o_hi = min(OUT, o_lo + per);
-  for (int o = o_lo + warp; o < o_hi; o += nw) {
-    const float4* wr = reinterpret_cast<const float4*>(W + (long)o * IN);
-    float acc[R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) acc[r] = 0.f;
-    for (int i = lane; i < IN / 4; i += 32) {
-      const float4 wv = __ldg(wr + i);
-#pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const float4 xv = *reinterpret_cast<const float4*>(xs + r * IN + 4 * i);
-        acc[r] += wv.x * xv.x + wv.y * xv.y + wv.z * xv.z + wv.w * xv.w;
-      }
-    }
-#pragma unroll
-    for (int r = 0; r < R; ++r) acc[r] = warp_sum(acc[r]);
+  cl_linear_core<R>(xs, IN, W, o_lo, o_hi, [&](int o, const float (&acc)[R]) {
     if (lane == 0) {
       const float bb = b ? __ldg(b + o) : 0.f;
 #pragma unroll
       for (int r = 0; r < R; ++r) yg[r * ldy + o] = acc[r] + bb;
     }
-  }
+  });
 }
 
 // ------------------------------------------------------------------------------------------------ stage A
