@@ -23,6 +23,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include <atomic>
 #include <mutex>
 
@@ -355,11 +357,135 @@ __device__ __forceinline__ void epilogue_row(const GemmEpi& e, const Src& src, l
 // cover 128 contiguous bytes of one row and a load/store instruction touches 4 lines instead of 32.
 constexpr int kEpiStageBytes = 8 * 32 * 32 * 4;   // one 32x32 fp32 tile per epilogue warp
 
-template <int MODE, int BN, class Wait>
+// GM_F32_FOLD (residual-stream epilogue + producer side of the folded LayerNorm).  gemm_tc() guarantees the identity
+// row map, an addend, add_mod % 32 == 0 and no K split, so the eight row slices of a lane sit at a constant stride from
+// one base pointer and the row loop has no per-slice branch: the compiler interleaves the slices (the general loop
+// below serialises them behind its row-map / modulo / split-K branches, and with two epilogue warps per scheduler
+// that chain of dependent instructions - not HBM - was what bounded the proj GEMM).  The {sum, sum of squares} of a
+// row are kept per lane over the whole half tile and combined once at the end by a transposing butterfly
+// (7 shuffles per quantity instead of 24 per chunk); lane (sub, cg) ends up with the pair of row cg * 4 + sub.
+template <int BN, int LD, class Wait>
+__device__ __forceinline__ void epilogue_warp_fold(const GemmEpi& e, const TmemSrc& src, long row0, int lane, int M,
+                                                   int N, int n0, int half, int nhalves, const Wait& wait_acc,
+                                                   float4* stage) {
+  const int ncols = min(BN, N - n0);
+  const int nchunks = ncols / 32;
+  const int c_lo = (nchunks * half) / nhalves, c_hi = (nchunks * (half + 1)) / nhalves;
+  const int sub = lane >> 3, cg = lane & 7;     // rows row0 + i*4 + sub (i < 8), columns cg*4 .. cg*4+3 of a chunk
+  const long r0 = row0 + sub;
+  const int left = (int)min(32L, max(0L, (long)M - r0));   // slice i holds a row of the matrix iff 4 i < left
+  const bool all_rows = __all_sync(0xffffffffu, left >= 29);
+  // LD > 0: the leading dimension of out / xb_out / addend is a compile-time constant, so the eight slices of a lane
+  // are immediate offsets from three running pointers (advanced by one chunk per iteration) - no address arithmetic
+  const int ld_o = LD > 0 ? LD : e.ld_out, ld_a = LD > 0 ? LD : e.ld_add;
+  const long arow0 = (e.add_mod > 0 ? row0 % e.add_mod : row0) + sub;
+  const float* ap = e.addend + arow0 * (long)ld_a + n0 + cg * 4 + c_lo * 32;
+  const long obase = r0 * (long)ld_o + n0 + cg * 4 + c_lo * 32;
+  float* op = reinterpret_cast<float*>(e.out) + obase;
+  __nv_bfloat16* xp = reinterpret_cast<__nv_bfloat16*>(e.xb_out) + obase;
+  const int astride = 4 * ld_a, ostride = 4 * ld_o;
+
+  float4 nxt[8];
+  float ps[8], pq[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    nxt[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    ps[i] = pq[i] = 0.f;
+  }
+  if (c_lo < c_hi) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (4 * i < left) nxt[i] = *reinterpret_cast<const float4*>(ap + i * astride);
+  }
+  float4 b_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (e.bias && c_lo < c_hi) b_nxt = __ldg(reinterpret_cast<const float4*>(e.bias + n0 + c_lo * 32 + cg * 4));
+  wait_acc();
+  const uint32_t stage_s = smem_u32(stage);
+  uint32_t v[32];
+  if (c_lo < c_hi) tmem_ld_32x32(src.taddr + c_lo * 32, v);
+  for (int c = c_lo; c < c_hi; ++c) {
+    tmem_wait_ld();
+#pragma unroll
+    for (int g = 0; g < 8; ++g)
+      sts128(stage_s + (lane * 8 + (g ^ (lane & 7))) * 16, __uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]),
+             __uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
+    __syncwarp();
+    const float4 b4 = b_nxt;
+    const bool more = c + 1 < c_hi;
+    if (more) {
+      tmem_ld_32x32(src.taddr + (c + 1) * 32, v);
+      if (e.bias) b_nxt = __ldg(reinterpret_cast<const float4*>(e.bias + n0 + (c + 1) * 32 + cg * 4));
+    }
+    auto rows = [&](auto all_tag) {
+      constexpr bool kAll = decltype(all_tag)::value;      // the 32 rows of this warp all exist: no store predicates
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int r = i * 4 + sub;
+        float4 x = lds128(stage_s + (r * 8 + (cg ^ (r & 7))) * 16);
+        add4(x, b4);
+        add4(x, nxt[i]);
+        const bool st = kAll || 4 * i < left;
+        // single-buffered prefetch: the register of slice i is refilled with the next chunk as soon as it is consumed
+        if (more && st) nxt[i] = *reinterpret_cast<const float4*>(ap + i * astride + 32);
+        if (st) {
+          *reinterpret_cast<float4*>(op + i * ostride) = x;
+          uint2 t;
+          t.x = pack_bf16(x.x, x.y);
+          t.y = pack_bf16(x.z, x.w);
+          *reinterpret_cast<uint2*>(xp + i * ostride) = t;
+        }
+        ps[i] += (x.x + x.y) + (x.z + x.w);
+        pq[i] = fmaf(x.x, x.x, fmaf(x.y, x.y, fmaf(x.z, x.z, fmaf(x.w, x.w, pq[i]))));
+      }
+    };
+    if constexpr (LD > 0) {
+      if (all_rows) rows(std::true_type{});
+      else rows(std::false_type{});
+    } else {
+      rows(std::false_type{});      // one instantiation only: two of them spill with run-time strides
+    }
+    ap += 32, op += 32, xp += 32;
+    __syncwarp();
+  }
+  // transposing butterfly over the eight column lanes of a row group: after the rounds (xor 4, 2, 1) lane cg holds the
+  // total of slice cg
+  {
+    const bool h4 = (cg & 4) != 0, h2 = (cg & 2) != 0, h1 = (cg & 1) != 0;
+    float s4[4], q4[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float ks = h4 ? ps[j + 4] : ps[j], ss = h4 ? ps[j] : ps[j + 4];
+      const float kq = h4 ? pq[j + 4] : pq[j], sq = h4 ? pq[j] : pq[j + 4];
+      s4[j] = ks + __shfl_xor_sync(0xffffffffu, ss, 4);
+      q4[j] = kq + __shfl_xor_sync(0xffffffffu, sq, 4);
+    }
+    float s2[2], q2[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const float ks = h2 ? s4[j + 2] : s4[j], ss = h2 ? s4[j] : s4[j + 2];
+      const float kq = h2 ? q4[j + 2] : q4[j], sq = h2 ? q4[j] : q4[j + 2];
+      s2[j] = ks + __shfl_xor_sync(0xffffffffu, ss, 2);
+      q2[j] = kq + __shfl_xor_sync(0xffffffffu, sq, 2);
+    }
+    const float st_s = (h1 ? s2[1] : s2[0]) + __shfl_xor_sync(0xffffffffu, h1 ? s2[0] : s2[1], 1);
+    const float st_q = (h1 ? q2[1] : q2[0]) + __shfl_xor_sync(0xffffffffu, h1 ? q2[0] : q2[1], 1);
+    // also when this half owns no chunk: the slot is then written as zeros
+    const long row = row0 + cg * 4 + sub;
+    if (row < M)
+      reinterpret_cast<float2*>(e.stats_out)[row * e.stats_slots + (n0 / BN) * nhalves + half] = make_float2(st_s, st_q);
+  }
+}
+
+// LD: compile-time leading dimension of the GM_F32_FOLD operands (0 = run time), see epilogue_warp_fold
+template <int MODE, int BN, int LD, class Wait>
 __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& src, long row0, int lane, int M, int N,
                                               int n0, long out_off, int half, int nhalves, const Wait& wait_acc,
                                               float4* stage) {
-  constexpr bool kF32 = MODE == GM_F32 || MODE == GM_F32_FOLD;
+  if constexpr (MODE == GM_F32_FOLD) {
+    epilogue_warp_fold<BN, LD>(e, src, row0, lane, M, N, n0, half, nhalves, wait_acc, stage);
+    return;
+  }
+  constexpr bool kF32 = MODE == GM_F32;
   const int ncols = min(BN, N - n0);
   const int nchunks = ncols / 32;
   const int c_lo = (nchunks * half) / nhalves, c_hi = (nchunks * (half + 1)) / nhalves;
@@ -382,6 +508,7 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
       orow = token_to_window_row(row);
     orow_own = ok ? (int)orow : -1;
   }
+  const bool all_rows = __all_sync(0xffffffffu, orow_own >= 0);
   const int sub = lane >> 3, cg = lane & 7;     // transposed role: rows i*4 + sub (i < 8), columns cg*4 .. cg*4+3
   int orow[8];
 #pragma unroll
@@ -441,9 +568,6 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
     return fold_in ? __ldg(reinterpret_cast<const float4*>(e.fold_c + n0 + c * 32 + cg * 4))
                    : make_float4(0.f, 0.f, 0.f, 0.f);
   };
-  // folded LayerNorm, producer side: lane (sub, cg) keeps the running {sum, sum of squares} of row cg*4 + sub
-  constexpr bool fold_out = MODE == GM_F32_FOLD;
-  float st_s = 0.f, st_q = 0.f;
   if (has_add && c_lo < c_hi) fetch(c_lo);
   float4 b_nxt = c_lo < c_hi ? bias4(c_lo) : make_float4(0.f, 0.f, 0.f, 0.f);
   float4 c_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -469,19 +593,22 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
       b_nxt = bias4(c + 1);
       if constexpr (kFoldIn) c_nxt = foldc4(c + 1);
     }
+    // the row loop, instantiated with and without the folded LayerNorm: the (uniform) choice is made once per chunk,
+    // so the eight row slices stay one branch-free block that the compiler interleaves
+    auto rows = [&](auto fold_tag, auto all_tag) {
+    constexpr bool kFold = decltype(fold_tag)::value;
+    constexpr bool kAll = decltype(all_tag)::value;      // every row of this warp is stored: no store predicate
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int r = i * 4 + sub;
       float4 x = lds128(stage_s + (r * 8 + (cg ^ (r & 7))) * 16);
-      if constexpr (kFoldIn) {
-        if (fold_in) {
-          const float rs = rs_i[i], nm = nm_i[i];
-          x.x = fmaf(rs, x.x, nm * c4.x), x.y = fmaf(rs, x.y, nm * c4.y);
-          x.z = fmaf(rs, x.z, nm * c4.z), x.w = fmaf(rs, x.w, nm * c4.w);
-        }
+      if constexpr (kFoldIn && kFold) {
+        const float rs = rs_i[i], nm = nm_i[i];
+        x.x = fmaf(rs, x.x, nm * c4.x), x.y = fmaf(rs, x.y, nm * c4.y);
+        x.z = fmaf(rs, x.z, nm * c4.z), x.w = fmaf(rs, x.w, nm * c4.w);
       }
       add4(x, b4);
-      const bool st = orow[i] >= 0;   // predicated stores (no branch: the 8 row slices interleave)
+      const bool st = kAll || orow[i] >= 0;
       const long col = n0 + c * 32 + cg * 4;
       if constexpr (kF32) {
         if (has_add) {
@@ -500,22 +627,6 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
           }
         } else if (st) {
           *reinterpret_cast<float4*>(op) = x;
-        }
-        if constexpr (fold_out) {
-        if (st) {
-          uint2 t;
-          t.x = pack_bf16(x.x, x.y);
-          t.y = pack_bf16(x.z, x.w);
-          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(e.xb_out) + orow[i] * (long)e.ld_out + col) = t;
-        }
-        {
-          float ps = (x.x + x.y) + (x.z + x.w);
-          float pq = fmaf(x.x, x.x, x.y * x.y) + fmaf(x.z, x.z, x.w * x.w);
-          ps += __shfl_xor_sync(0xffffffffu, ps, 1), pq += __shfl_xor_sync(0xffffffffu, pq, 1);
-          ps += __shfl_xor_sync(0xffffffffu, ps, 2), pq += __shfl_xor_sync(0xffffffffu, pq, 2);
-          ps += __shfl_xor_sync(0xffffffffu, ps, 4), pq += __shfl_xor_sync(0xffffffffu, pq, 4);
-          if (cg == i) st_s += ps, st_q += pq;       // the eight column lanes of row i*4 + sub hold the same totals
-        }
         }
       } else if constexpr (MODE == GM_F16) {
         const float ws = (e.rowmap == RM_RELW_SHIFT && col >= 128) ? e.relw_scale : 1.f;
@@ -550,14 +661,20 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
         if (st) *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(e.out) + orow[i] * (long)e.ld_out + col) = t;
       }
     }
-    __syncwarp();
-  }
-  if constexpr (fold_out) {
-    {       // also when this half owns no chunk: the slot is then written as zeros
-      const long row = row0 + cg * 4 + sub;
-      if (row < M)
-        reinterpret_cast<float2*>(e.stats_out)[row * e.stats_slots + (n0 / BN) * nhalves + half] = make_float2(st_s, st_q);
+    };
+    if constexpr (kFoldIn) {
+      if (fold_in) {
+        if (all_rows) rows(std::true_type{}, std::true_type{});
+        else rows(std::true_type{}, std::false_type{});
+      } else {
+        if (all_rows) rows(std::false_type{}, std::true_type{});
+        else rows(std::false_type{}, std::false_type{});
+      }
+    } else {
+      if (all_rows) rows(std::false_type{}, std::true_type{});
+      else rows(std::false_type{}, std::false_type{});
     }
+    __syncwarp();
   }
 }
 
@@ -695,7 +812,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       TmemSrc src{tmem_base + (uint32_t(ew * 32) << 16) + uint32_t(as * BN)};
       const long row = (long)m_blk * kBM + ew * 32 + lane;
       if constexpr (kSplit)
-        epilogue_warp<MODE, BN>(e, src, (long)m_blk * kBM + ew * 32, lane, M, N, n_blk * BN,
+        epilogue_warp<MODE, BN, 0>(e, src, (long)m_blk * kBM + ew * 32, lane, M, N, n_blk * BN,
                                 ksplit ? 0L : (long)bidx * e.out_batch_off, eh, 2, wait_acc,
                                 reinterpret_cast<float4*>(smem + kStages * Cfg::kStageBytes + 256) + (warp - 4) * 256);
       else if (eh == 0)
@@ -722,7 +839,7 @@ constexpr int kStages2 = 6;
 constexpr int kStageBytes2 = kBM * 128 + 128 * 128;   // A half + W half
 constexpr int kSmemBytes2 = kStages2 * kStageBytes2 + 1024 + 256 + 32768 /*epilogue transposition tiles*/;
 
-template <int MODE>
+template <int MODE, int LD = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                 GemmEpi e) {
@@ -849,7 +966,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       TmemSrc src{tmem_base + (uint32_t(ew * 32) << 16) + uint32_t(as * BN)};
       const long row = (long)m_blk * 256 + rank * 128 + ew * 32 + lane;
       (void)row;
-      epilogue_warp<MODE, BN>(e, src, (long)m_blk * 256 + rank * 128 + ew * 32, lane, M, N, n_blk * BN, 0, eh, 2,
+      epilogue_warp<MODE, BN, LD>(e, src, (long)m_blk * 256 + rank * 128 + ew * 32, lane, M, N, n_blk * BN, 0, eh, 2,
                               wait_acc, reinterpret_cast<float4*>(smem + kStages2 * kStageBytes2 + 256) + (warp - 4) * 256);
       tc_fence_before();
       mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[as]), 0));
@@ -950,11 +1067,11 @@ cudaError_t launch(const void* A, int lda, const void* W, int ldw, int M, int N,
                     K, e);
 }
 
-template <int MODE>
+template <int MODE, int LD = 0>
 cudaError_t launch2(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const GemmEpi& e,
                     cudaStream_t stream) {
   static std::atomic<uint64_t> attr_set{0};
-  cudaError_t err = smem_opt_in(gemm_tc2_kernel<MODE>, kSmemBytes2, attr_set);
+  cudaError_t err = smem_opt_in(gemm_tc2_kernel<MODE, LD>, kSmemBytes2, attr_set);
   if (err != cudaSuccess) return err;
   CUtensorMap tmA, tmB;
   if (e.a_mode == AM_PATCH16) {
@@ -971,7 +1088,7 @@ cudaError_t launch2(const void* A, int lda, const void* W, int ldw, int M, int N
   const int tiles = ((M + 255) / 256) * ((N + 255) / 256);
   int pairs = gemm_num_sms() / 2;
   if (tiles < pairs) pairs = tiles;
-  return launch_pdl(gemm_tc2_kernel<MODE>, dim3(2 * pairs), dim3(kThreads), kSmemBytes2, stream, tmA, tmB, M, N, K, e);
+  return launch_pdl(gemm_tc2_kernel<MODE, LD>, dim3(2 * pairs), dim3(kThreads), kSmemBytes2, stream, tmA, tmB, M, N, K, e);
 }
 
 }  // namespace
@@ -1031,7 +1148,7 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
   if (e.a_mode != AM_PLAIN && (dbg || tf32)) return cudaErrorInvalidValue;   // the SIMT bisect path reads a plain A
   if (mode == GM_F32_FOLD &&
       (tf32 || dbg || e.rowmap != RM_IDENT || e.ksplit > 1 || e.batch != 1 || !e.xb_out || !e.stats_out ||
-       e.stats_slots != 2 * ((N + 255) / 256)))
+       e.stats_slots != 2 * ((N + 255) / 256) || !e.addend || (e.add_mod > 0 && e.add_mod % 32 != 0)))
     return cudaErrorInvalidValue;
   if (e.stats_out || e.xb_out) {
     if (mode != GM_F32_FOLD) return cudaErrorInvalidValue;
@@ -1056,7 +1173,11 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
       case GM_BIAS_BF16: return launch2<GM_BIAS_BF16>(A, lda, W, ldw, M, N, K, e, s);
       case GM_BIAS_GELU_BF16: return launch2<GM_BIAS_GELU_BF16>(A, lda, W, ldw, M, N, K, e, s);
       case GM_F32: return launch2<GM_F32>(A, lda, W, ldw, M, N, K, e, s);
-      case GM_F32_FOLD: return launch2<GM_F32_FOLD>(A, lda, W, ldw, M, N, K, e, s);
+      case GM_F32_FOLD:      // ViT-H / ViT-L / ViT-B widths get compile-time strides in the epilogue
+        if (e.ld_out == e.ld_add && e.ld_out == 1280) return launch2<GM_F32_FOLD, 1280>(A, lda, W, ldw, M, N, K, e, s);
+        if (e.ld_out == e.ld_add && e.ld_out == 1024) return launch2<GM_F32_FOLD, 1024>(A, lda, W, ldw, M, N, K, e, s);
+        if (e.ld_out == e.ld_add && e.ld_out == 768) return launch2<GM_F32_FOLD, 768>(A, lda, W, ldw, M, N, K, e, s);
+        return launch2<GM_F32_FOLD>(A, lda, W, ldw, M, N, K, e, s);
       default: break;
     }
   }
