@@ -1,9 +1,9 @@
 #!/bin/bash
-# ncu --set full (with source) of the GM_F32_FOLD pair GEMM after the branch-free epilogue: proj and lin2 launches
+# ncu --set full (with source) of five consecutive pair GEMMs after the branch-free epilogues (lin2 / qkv / proj / lin1 ...)
 O=gpurun_out
 mkdir -p $O
 BENCH="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-train"
-ncu --set full --clock-control none --import-source on -k regex:'gemm_tc2_kernel<7' --launch-skip 400 -c 4 -o $O/r6_fold -f $BENCH > $O/r6_ncu.log 2>&1; echo "ncu rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:'gemm_tc2' --launch-skip 400 -c 5 -o $O/r6_fold -f $BENCH > $O/r6_ncu.log 2>&1; echo "ncu rc=$?"
 ncu -i $O/r6_fold.ncu-rep --page raw --csv > $O/r6_fold_raw.csv 2>/dev/null
 ncu -i $O/r6_fold.ncu-rep --page source --csv --kernel-id :::1 > $O/r6_fold_source_1.csv 2>/dev/null
 ncu -i $O/r6_fold.ncu-rep --page source --csv --kernel-id :::2 > $O/r6_fold_source_2.csv 2>/dev/null
