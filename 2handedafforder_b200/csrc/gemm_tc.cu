@@ -397,8 +397,13 @@ __device__ __forceinline__ void epilogue_warp_fold(const GemmEpi& e, const TmemS
     for (int i = 0; i < 8; ++i)
       if (4 * i < left) nxt[i] = *reinterpret_cast<const float4*>(ap + i * astride);
   }
-  float4 b_nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (e.bias && c_lo < c_hi) b_nxt = __ldg(reinterpret_cast<const float4*>(e.bias + n0 + c_lo * 32 + cg * 4));
+  // bias of the whole half tile (at most 4 chunks = 128 columns: nhalves = 2, BN <= 256) in ONE load per lane, lane L
+  // holding columns 4 L .. 4 L + 3; a chunk takes its four values by shuffle.  A per-chunk bias load inside the loop
+  // shares a scoreboard with the residual prefetches issued after it, so consuming it at the top of the next chunk made
+  // the warp wait for those prefetches too (19 % of the kernel's stall samples, profiles/r6_prof_gemm_summary.csv)
+  float4 b_own = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (e.bias && c_lo * 32 + lane * 4 < c_hi * 32)
+    b_own = __ldg(reinterpret_cast<const float4*>(e.bias + n0 + c_lo * 32 + lane * 4));
   wait_acc();
   const uint32_t stage_s = smem_u32(stage);
   uint32_t v[32];
@@ -410,12 +415,14 @@ __device__ __forceinline__ void epilogue_warp_fold(const GemmEpi& e, const TmemS
       sts128(stage_s + (lane * 8 + (g ^ (lane & 7))) * 16, __uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]),
              __uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
     __syncwarp();
-    const float4 b4 = b_nxt;
-    const bool more = c + 1 < c_hi;
-    if (more) {
-      tmem_ld_32x32(src.taddr + (c + 1) * 32, v);
-      if (e.bias) b_nxt = __ldg(reinterpret_cast<const float4*>(e.bias + n0 + (c + 1) * 32 + cg * 4));
+    float4 b4;
+    {
+      const int src_lane = (c - c_lo) * 8 + cg;
+      b4.x = __shfl_sync(0xffffffffu, b_own.x, src_lane), b4.y = __shfl_sync(0xffffffffu, b_own.y, src_lane);
+      b4.z = __shfl_sync(0xffffffffu, b_own.z, src_lane), b4.w = __shfl_sync(0xffffffffu, b_own.w, src_lane);
     }
+    const bool more = c + 1 < c_hi;
+    if (more) tmem_ld_32x32(src.taddr + (c + 1) * 32, v);
     auto rows = [&](auto all_tag) {
       constexpr bool kAll = decltype(all_tag)::value;      // the 32 rows of this warp all exist: no store predicates
 #pragma unroll
@@ -603,11 +610,15 @@ __device__ __forceinline__ void epilogue_warp(const GemmEpi& e, const TmemSrc& s
       const int r = i * 4 + sub;
       float4 x = lds128(stage_s + (r * 8 + (cg ^ (r & 7))) * 16);
       if constexpr (kFoldIn && kFold) {
-        const float rs = rs_i[i], nm = nm_i[i];
-        x.x = fmaf(rs, x.x, nm * c4.x), x.y = fmaf(rs, x.y, nm * c4.y);
-        x.z = fmaf(rs, x.z, nm * c4.z), x.w = fmaf(rs, x.w, nm * c4.w);
+        // rstd * x + (-rstd * mean * c + bias) on packed fp32x2: four FMA-pipe instructions per float4
+        const uint64_t rs2 = f32x2(rs_i[i], rs_i[i]), nm2 = f32x2(nm_i[i], nm_i[i]);
+        const uint64_t y01 = fma2(rs2, f32x2(x.x, x.y), fma2(nm2, f32x2(c4.x, c4.y), f32x2(b4.x, b4.y)));
+        const uint64_t y23 = fma2(rs2, f32x2(x.z, x.w), fma2(nm2, f32x2(c4.z, c4.w), f32x2(b4.z, b4.w)));
+        unpack2(y01, x.x, x.y);
+        unpack2(y23, x.z, x.w);
+      } else {
+        add4(x, b4);
       }
-      add4(x, b4);
       const bool st = kAll || orow[i] >= 0;
       const long col = n0 + c * 32 + cg * 4;
       if constexpr (kF32) {
