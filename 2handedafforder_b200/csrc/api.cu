@@ -1424,6 +1424,26 @@ extern "C" int b200sam_op_gemm(int device, int tf32, int mode, const void* A, in
   return err == cudaSuccess ? 0 : B200SAM_ERR_CUDA;
 }
 
+extern "C" int b200sam_op_gemm_fold_producer(int device, const void* A, int lda, const void* Wt, int ldw, int M, int N,
+                                             int K, const float* bias, const float* addend, int ld_add, int add_mod,
+                                             float* out, int ld_out, void* xb_out, float* stats_out, void* stream) {
+  DeviceGuard g(device);
+  if (gemm_tc_init(device) != cudaSuccess) return B200SAM_ERR_CUDA;
+  GemmEpi e;
+  e.bias = bias;
+  e.addend = addend;
+  e.ld_add = ld_add;
+  e.add_mod = add_mod;
+  e.out = out;
+  e.ld_out = ld_out;
+  e.xb_out = xb_out;
+  e.stats_out = stats_out;
+  e.stats_slots = 2 * ((N + 255) / 256);
+  cudaError_t err = gemm_tc(false, GM_F32_FOLD, A, lda, Wt, ldw, M, N, K, e, reinterpret_cast<cudaStream_t>(stream), false);
+  if (err == cudaErrorInvalidValue) return B200SAM_ERR_INVALID;
+  return err == cudaSuccess ? 0 : B200SAM_ERR_CUDA;
+}
+
 extern "C" int b200sam_op_layernorm(const float* x, int rows, int D, const float* g, const float* b, float eps,
                                     void* out_bf16, int windowed, void* stream) {
   cudaError_t err = launch_layernorm_bf16(x, rows, D, g, b, eps, reinterpret_cast<__nv_bfloat16*>(out_bf16),

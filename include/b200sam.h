@@ -189,6 +189,15 @@ int b200sam_op_gemm(int device, int tf32, int mode, const void* A, int lda, cons
                     int K, const float* bias, const float* addend, int ld_add, int add_mod, const float* ln_g,
                     const float* ln_b, float ln_eps, void* out, int ld_out, int rowmap, int debug_simt, void* stream);
 
+/* The residual-stream GEMM of the encoder with the producer half of the folded LayerNorm (proj / lin2 / patch embed;
+ * image_encoder.py:187-191 with norm1 / norm2 of the NEXT consumer folded), bf16 operands:
+ * out(M,N) f32 = A W^T + bias + addend[row % add_mod or row] (addend may alias out), xb_out(M,N) = bf16(out) with the
+ * same leading dimension, stats_out(M, 2*ceil(N/256)) float2 = per row and 128-column slice {sum, sum of squares} of
+ * out.  addend is required; add_mod must be 0 or a multiple of 32. */
+int b200sam_op_gemm_fold_producer(int device, const void* A, int lda, const void* W, int ldw, int M, int N, int K,
+                                  const float* bias, const float* addend, int ld_add, int add_mod, float* out,
+                                  int ld_out, void* xb_out, float* stats_out, void* stream);
+
 /* LayerNorm over the last dim of x (rows, D) f32 -> bf16; windowed != 0 scatters rows into 14x14-window order
  * (rows must then be B*4096; out has B*4900 rows whose pad rows are left untouched). */
 int b200sam_op_layernorm(const float* x, int rows, int D, const float* g, const float* b, float eps, void* out_bf16,

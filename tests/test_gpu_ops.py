@@ -50,6 +50,68 @@ def test_gemm_f32_residual_in_place(M, N, K):
     assert G.rel_err(out, ref) < 2e-4
 
 
+@pytest.mark.parametrize("M,N,K,add_mod", [
+    (4096, 1280, 256, 0),       # ViT-H width: compile-time strides, every warp full
+    (1100, 1280, 128, 0),       # last pair tile holds 76 rows: full, partial (12 rows) and empty warps
+    (1100, 768, 64, 1024),      # ViT-B width, broadcast addend wrapping inside the last tile
+    (2048, 1024, 64, 0),        # ViT-L width
+    (1100, 512, 64, 0),         # any other width: run-time strides
+    (300, 256, 64, 0),          # below 1024 rows: the single-CTA kernel
+])
+def test_gemm_fold_producer_epilogue(M, N, K, add_mod):
+    """Residual-stream epilogue with the producer half of the folded LayerNorm: fp32 row, its bf16
+    copy and the per-row partial {sum, sum of squares} of every 128-column slice, through b200sam_op_gemm_fold_producer.
+    Tolerance: bf16 operands with fp32 accumulation against fp32 torch, 2e-4 of the largest value (as the GM_F32 tests);
+    the bf16 copy must be the round-to-nearest-even of the stored fp32 row exactly; the sums within 1e-5 relative of the
+    fp64 sums of the stored row (different summation order only)."""
+    A = _rand((M, K), 31, 1.0, torch.bfloat16)
+    W = _rand((N, K), 32, 1.0 / math.sqrt(K), torch.bfloat16)
+    bias = _rand((N,), 33, 0.5)
+    if add_mod:
+        add = _rand((add_mod, N), 34)
+        ref = A.float() @ W.float().t() + bias + add[torch.arange(M, device=add.device) % add_mod]
+        out = torch.full((M, N), float("nan"), dtype=torch.float32, device="cuda")
+        addend = add
+    else:
+        X = _rand((M, N), 34)
+        ref = X + A.float() @ W.float().t() + bias
+        out = X.clone()          # in place, as proj / lin2 update the residual stream
+        addend = out
+    slots = 2 * ((N + 255) // 256)
+    pad = 7                      # rows behind M must stay untouched
+    xb = torch.full((M + pad, N), float("nan"), dtype=torch.bfloat16, device="cuda")
+    stats = torch.full((M + pad, slots, 2), float("nan"), dtype=torch.float32, device="cuda")
+    rc = G.lib().b200sam_op_gemm_fold_producer(0, G.P(A), A.stride(0), G.P(W), W.stride(0), M, N, K, G.P(bias),
+                                               G.P(addend), addend.stride(0), add_mod, G.P(out), out.stride(0),
+                                               G.P(xb), G.P(stats), G.stream())
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert G.rel_err(out, ref) < 2e-4
+    assert torch.equal(xb[:M], out.bfloat16())
+    assert torch.isnan(xb[M:].float()).all() and torch.isnan(stats[M:]).all()
+    o64 = out.double()
+    for j in range(slots):
+        sl = o64[:, j * 128:(j + 1) * 128]           # a slot beyond N (N % 256 == 128) is written as zeros
+        s1, s2 = sl.sum(1), (sl * sl).sum(1)
+        assert float((stats[:M, j, 0].double() - s1).abs().max()) <= 1e-5 * float(sl.abs().sum(1).max()) + 1e-12
+        assert float((stats[:M, j, 1].double() - s2).abs().max()) <= 1e-5 * float(s2.max()) + 1e-12
+
+
+def test_gemm_fold_producer_rejects_what_the_epilogue_does_not_handle():
+    A = _rand((1024, 64), 35, 1.0, torch.bfloat16)
+    W = _rand((256, 64), 36, 0.1, torch.bfloat16)
+    out = torch.zeros((1024, 256), dtype=torch.float32, device="cuda")
+    xb = torch.zeros((1024, 256), dtype=torch.bfloat16, device="cuda")
+    stats = torch.zeros((1024, 2, 2), dtype=torch.float32, device="cuda")
+    call = lambda addend, add_mod: G.lib().b200sam_op_gemm_fold_producer(
+        0, G.P(A), 64, G.P(W), 64, 1024, 256, 64, None, G.P(addend), 256, add_mod, G.P(out), 256, G.P(xb), G.P(stats),
+        G.stream())
+    assert call(None, 0) == -1            # B200SAM_ERR_INVALID: the addend is required
+    assert call(out, 48) == -1            # add_mod must be a multiple of 32
+    assert call(out, 0) == 0
+    torch.cuda.synchronize()
+
+
 def test_gemm_f32_broadcast_addend():
     """patch-embed epilogue: + bias + pos_embed[row % 4096] (image_encoder.py:111-113)."""
     M, N, K = 2 * 4096, 320, 768
