@@ -44,6 +44,7 @@ SYMBOLS = [
     ("b200sam_debug_read_tokens", _I, [_P, _P, _I, _P]),
     ("b200sam_op_gemm", _I, [_I, _I, _I, _P, _I, _P, _I, _I, _I, _I, _P, _P, _I, _I, _P, _P, _F, _P, _I, _I, _I, _P]),
     ("b200sam_op_gemm_fold_producer", _I, [_I, _P, _I, _P, _I, _I, _I, _I, _P, _P, _I, _I, _P, _I, _P, _P, _P]),
+    ("b200sam_op_gemm_fold_consumer", _I, [_I, _I, _P, _I, _P, _P, _P, _P, _F, _P, _I, _I, _I, _P, _P, _P, _I, _P]),
     ("b200sam_op_layernorm", _I, [_P, _I, _I, _P, _P, _F, _P, _I, _P]),
     ("b200sam_op_attention", _I, [_P, _I, _I, _I, _I, _P, _P, _P, _P]),
     # include/b200sam_train.h (fp32 forward / backward primitives of the decoder training graph)

@@ -1444,6 +1444,32 @@ extern "C" int b200sam_op_gemm_fold_producer(int device, const void* A, int lda,
   return err == cudaSuccess ? 0 : B200SAM_ERR_CUDA;
 }
 
+extern "C" int b200sam_op_gemm_fold_consumer(int device, int gelu, const void* xb, int lda, const float* W,
+                                             const float* gamma, const float* beta, const float* bias, float eps,
+                                             const float* stats, int M, int N, int K, void* wf_scratch,
+                                             float* cd_scratch, void* out, int ld_out, void* stream) {
+  DeviceGuard g(device);
+  if (gemm_tc_init(device) != cudaSuccess) return B200SAM_ERR_CUDA;
+  if (!xb || !W || !gamma || !beta || !bias || !stats || !wf_scratch || !cd_scratch || !out || M < 1 || N < 1 || K < 1)
+    return B200SAM_ERR_INVALID;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  __nv_bfloat16* wf = reinterpret_cast<__nv_bfloat16*>(wf_scratch);
+  if (launch_fold_ln_weights(W, gamma, beta, bias, N, K, wf, cd_scratch, cd_scratch + N, s) != cudaSuccess)
+    return B200SAM_ERR_CUDA;
+  GemmEpi e;
+  e.bias = cd_scratch + N;       // d
+  e.fold_c = cd_scratch;         // c
+  e.fold_eps = eps;
+  e.stats_in = stats;
+  e.stats_slots = 2 * ((K + 255) / 256);
+  e.stats_dim = K;
+  e.out = out;
+  e.ld_out = ld_out;
+  cudaError_t err = gemm_tc(false, gelu ? GM_BIAS_GELU_BF16 : GM_BIAS_BF16, xb, lda, wf, K, M, N, K, e, s, false);
+  if (err == cudaErrorInvalidValue) return B200SAM_ERR_INVALID;
+  return err == cudaSuccess ? 0 : B200SAM_ERR_CUDA;
+}
+
 extern "C" int b200sam_op_layernorm(const float* x, int rows, int D, const float* g, const float* b, float eps,
                                     void* out_bf16, int windowed, void* stream) {
   cudaError_t err = launch_layernorm_bf16(x, rows, D, g, b, eps, reinterpret_cast<__nv_bfloat16*>(out_bf16),

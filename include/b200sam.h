@@ -198,6 +198,15 @@ int b200sam_op_gemm_fold_producer(int device, const void* A, int lda, const void
                                   const float* bias, const float* addend, int ld_add, int add_mod, float* out,
                                   int ld_out, void* xb_out, float* stats_out, void* stream);
 
+/* The consuming half (qkv / lin1; image_encoder.py:179,191 + common.py:25-26): out(M,N) bf16 =
+ * [GELU](LayerNorm_{gamma,beta,eps}(x) W^T + bias), evaluated as the path evaluates it.  W (N,K) f32 is folded by the
+ * weight-finalisation kernel into caller scratch - wf_scratch (N,K) bf16 = bf16(gamma . W), cd_scratch (2N) f32 =
+ * {c[n] = sum_k wf[n,k], d = W beta + bias} - then out = rstd * (xb wf^T) - rstd * mean * c + d with xb (M,K) the
+ * bf16 copy of x and mean / rstd from stats (M, 2*ceil(K/256)) float2, the producer's per-slice {sum, sum of squares}. */
+int b200sam_op_gemm_fold_consumer(int device, int gelu, const void* xb, int lda, const float* W, const float* gamma,
+                                  const float* beta, const float* bias, float eps, const float* stats, int M, int N,
+                                  int K, void* wf_scratch, float* cd_scratch, void* out, int ld_out, void* stream);
+
 /* LayerNorm over the last dim of x (rows, D) f32 -> bf16; windowed != 0 scatters rows into 14x14-window order
  * (rows must then be B*4096; out has B*4900 rows whose pad rows are left untouched). */
 int b200sam_op_layernorm(const float* x, int rows, int D, const float* g, const float* b, float eps, void* out_bf16,

@@ -112,6 +112,52 @@ def test_gemm_fold_producer_rejects_what_the_epilogue_does_not_handle():
     torch.cuda.synchronize()
 
 
+@pytest.mark.parametrize("M,N,K,gelu", [
+    (4096, 3840, 1280, False),   # ViT-H qkv
+    (4096, 1024, 256, True),     # lin1-like with GELU
+    (1100, 512, 256, True),      # last pair tile: full, partial and empty warps
+    (1100, 512, 384, False),     # K % 256 = 128: the last stats slot is the producer's zero slot
+    (300, 256, 128, False),      # below 1024 rows: the single-CTA kernel
+])
+def test_gemm_fold_consumer_epilogue(M, N, K, gelu):
+    """qkv / lin1 with the LayerNorm in front of them folded in, through b200sam_op_gemm_fold_consumer:
+    weight folding kernel + GEMM + epilogue.  Two checks.  (1) Against the definition LayerNorm(x) W^T + b [GELU] in
+    fp32 torch: 1.5e-2 of the largest value, the bound the path tests use for one block in bf16 (x and gamma.W are
+    rounded to bf16).  (2) Against the same algebra evaluated in fp64 from the SAME rounded operands and sums, which
+    leaves only the fp32 accumulation order and the bf16 rounding of the result: 2**-8 of the largest value."""
+    eps = 1e-6
+    x = _rand((M, K), 41) + 0.3
+    W = _rand((N, K), 42, 1.0 / math.sqrt(K))
+    gamma, beta, bias = 1.0 + _rand((K,), 43, 0.2), _rand((K,), 44, 0.2), _rand((N,), 45, 0.5)
+    xb = x.bfloat16()
+    slots = 2 * ((K + 255) // 256)
+    stats = torch.zeros((M, slots, 2), dtype=torch.float32, device="cuda")
+    for j in range((K + 127) // 128):
+        sl = x[:, j * 128:(j + 1) * 128]
+        stats[:, j, 0], stats[:, j, 1] = sl.sum(1), (sl * sl).sum(1)
+    wf = torch.empty((N, K), dtype=torch.bfloat16, device="cuda")
+    cd = torch.empty((2 * N,), dtype=torch.float32, device="cuda")
+    pad = 5
+    out = torch.full((M + pad, N), float("nan"), dtype=torch.bfloat16, device="cuda")
+    rc = G.lib().b200sam_op_gemm_fold_consumer(0, int(gelu), G.P(xb), K, G.P(W), G.P(gamma), G.P(beta), G.P(bias), eps,
+                                               G.P(stats), M, N, K, G.P(wf), G.P(cd), G.P(out), N, G.stream())
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert torch.isnan(out[M:].float()).all()
+    # the folded weights
+    assert torch.equal(wf, (W * gamma).bfloat16())
+    assert G.rel_err(cd[:N], wf.double().sum(1)) < 1e-5 * math.sqrt(K)
+    assert G.rel_err(cd[N:], W.double() @ beta.double() + bias.double()) < 1e-5
+    act = torch.nn.functional.gelu if gelu else (lambda t: t)
+    ref = act(torch.nn.functional.layer_norm(x, (K,), gamma, beta, eps) @ W.t() + bias)
+    assert G.rel_err(out[:M], ref) < 1.5e-2
+    s1, s2 = stats[:, :, 0].double().sum(1), stats[:, :, 1].double().sum(1)
+    mu = s1 / K
+    rstd = 1.0 / torch.sqrt((s2 / K - mu * mu).clamp_min(0) + eps)
+    emul = rstd[:, None] * (xb.double() @ wf.double().t()) - (rstd * mu)[:, None] * cd[:N].double() + cd[N:].double()
+    assert G.rel_err(out[:M], act(emul)) < 2.0 ** -8
+
+
 def test_gemm_f32_broadcast_addend():
     """patch-embed epilogue: + bias + pos_embed[row % 4096] (image_encoder.py:111-113)."""
     M, N, K = 2 * 4096, 320, 768
