@@ -193,7 +193,8 @@ int b200sam_op_gemm(int device, int tf32, int mode, const void* A, int lda, cons
  * image_encoder.py:187-191 with norm1 / norm2 of the NEXT consumer folded), bf16 operands:
  * out(M,N) f32 = A W^T + bias + addend[row % add_mod or row] (addend may alias out), xb_out(M,N) = bf16(out) with the
  * same leading dimension, stats_out(M, 2*ceil(N/256)) float2 = per row and 128-column slice {sum, sum of squares} of
- * out.  addend is required; add_mod must be 0 or a multiple of 32. */
+ * out (two slots per 256-wide tile; a last tile of 128 columns splits them 64 + 64; consumers add all slots of a row).
+ * addend is required; add_mod must be 0 or a multiple of 32. */
 int b200sam_op_gemm_fold_producer(int device, const void* A, int lda, const void* W, int ldw, int M, int N, int K,
                                   const float* bias, const float* addend, int ld_add, int add_mod, float* out,
                                   int ld_out, void* xb_out, float* stats_out, void* stream);

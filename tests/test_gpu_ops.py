@@ -91,7 +91,7 @@ def test_gemm_fold_producer_epilogue(M, N, K, add_mod):
     assert torch.isnan(xb[M:].float()).all() and torch.isnan(stats[M:]).all()
     o64 = out.double()
     for j in range(slots):
-        sl = o64[:, j * 128:(j + 1) * 128]           # a slot beyond N (N % 256 == 128) is written as zeros
+        sl = o64[:, j * 128:(j + 1) * 128]           # every N here is a multiple of 256: one 128-column slice per slot
         s1, s2 = sl.sum(1), (sl * sl).sum(1)
         assert float((stats[:M, j, 0].double() - s1).abs().max()) <= 1e-5 * float(sl.abs().sum(1).max()) + 1e-12
         assert float((stats[:M, j, 1].double() - s2).abs().max()) <= 1e-5 * float(s2.max()) + 1e-12
