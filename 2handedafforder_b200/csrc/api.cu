@@ -793,6 +793,9 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
   const long T = (long)B * kTokens;
   const int nblocks = (h->debug_stop_block >= 0 && h->debug_stop_block < h->depth) ? h->debug_stop_block : h->depth;
   const bool fold = ln_fold_on(h);
+  // window-pad rows of a windowed block's qkv buffer: written by the idle warp of the PREVIOUS block's lin2 launch
+  // (GemmEpi::pad_dst) when that launch runs on the CTA-pair kernel, else by the small fill kernel behind the qkv GEMM
+  bool pads_written = false;
   for (int i = 0; i < nblocks; ++i) {
     const EncBlock& b = h->blk[i];
     NvtxRange nvtx_blk(b.global ? "block_global" : "block_windowed");
@@ -817,7 +820,8 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
       e.rowmap = b.global ? RM_IDENT : RM_TOKEN_TO_WINDOW;
       h->pc = B200SAM_PC_GEMM_QKV;
       if (int r = run_gemm(h, false, GM_BIAS_BF16, h->ln_plain, D, fold ? b.qkv_wf : b.qkv_w, D, T, 3 * D, D, e, s)) return r;
-      if (!b.global) KL(launch_fill_pad_rows(h->qkv, b.qkv_b, h->pad_rows, h->n_pad_rows, B, 3 * D, s));
+      if (!b.global && !pads_written) KL(launch_fill_pad_rows(h->qkv, b.qkv_b, h->pad_rows, h->n_pad_rows, B, 3 * D, s));
+      pads_written = false;
     }
     h->pc = b.global ? B200SAM_PC_ATTN_GLOBAL : B200SAM_PC_ATTN_WINDOW;
     KL(launch_attention(h->qkv, b.global ? B : B * kWinPerSide * kWinPerSide, b.global ? kGrid : kWin, heads, hd, b.relh,
@@ -870,7 +874,19 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
         e.stats_slots = h->ln_slots;
       }
       h->pc = B200SAM_PC_GEMM_LIN2;
-      if (int r = run_gemm(h, false, fold ? GM_F32_FOLD : GM_F32, h->hid, 4 * D, b.lin2_w, 4 * D, T, D, 4 * D, e, s)) return r;
+      const int lin2_mode = fold ? GM_F32_FOLD : GM_F32;
+      if (i + 1 < nblocks && !h->blk[i + 1].global && kernel_variant(VK_PAD_FILL) == 0 && !h->debug_simt &&
+          gemm_tc_is_pair(false, lin2_mode, (int)T, D, e, false)) {
+        // attention(i) is done with the qkv buffer; nothing reads it before block i + 1's attention
+        e.pad_dst = h->qkv;
+        e.pad_bias = h->blk[i + 1].qkv_b;
+        e.pad_rows = h->pad_rows;
+        e.pad_n = h->n_pad_rows;
+        e.pad_frames = B;
+        e.pad_cols = 3 * D;
+        pads_written = true;
+      }
+      if (int r = run_gemm(h, false, lin2_mode, h->hid, 4 * D, b.lin2_w, 4 * D, T, D, 4 * D, e, s)) return r;
     }
   }
   if (nblocks != h->depth) return 1;   // debug: residual stream after `nblocks` blocks is left in X
@@ -915,7 +931,7 @@ int encode_body(b200sam_t* h, int B, cudaStream_t s) {
 int encode_body_graphed(b200sam_t* h, int B, cudaStream_t s) {
   const int sig = kernel_variant(VK_ATTN_WINDOW) * 10000 + kernel_variant(VK_ATTN_GLOBAL) * 100 +
                   kernel_variant(VK_GEMM_PAIR) * 10 + kernel_variant(VK_IMPLICIT_CONV) + kernel_variant(VK_LN_FOLD) * 1000000 +
-                  kernel_variant(VK_PDL) * 10000000;
+                  kernel_variant(VK_PDL) * 10000000 + kernel_variant(VK_PAD_FILL) * 100000000;
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
   const bool plain = h->prof_on || h->debug_simt || h->debug_stop_block >= 0 || !h->use_graphs ||
                      cudaStreamIsCapturing(s, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone;

@@ -962,6 +962,24 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         umma_commit_2cta(&tmem_full[as], 3);
       }
     }
+  } else if (warp == 3) {
+    // GemmEpi::pad_dst: the idle warp writes the window-pad rows of the next block's qkv buffer (rows strided over CTAs)
+    if (e.pad_dst) {
+      const int rows = e.pad_n * e.pad_frames, cols4 = e.pad_cols >> 2;
+      const float4* b4 = reinterpret_cast<const float4*>(e.pad_bias);
+      for (int r = blockIdx.x; r < rows; r += gridDim.x) {
+        const int frame = r / e.pad_n, rem = __ldg(e.pad_rows + (r - frame * e.pad_n));
+        uint2* o = reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(e.pad_dst) +
+                                            ((long)frame * kWinRowsPerFrame + rem) * e.pad_cols);
+        for (int i = lane; i < cols4; i += 32) {
+          const float4 v = __ldg(b4 + i);
+          uint2 w;
+          w.x = pack_bf16(v.x, v.y);
+          w.y = pack_bf16(v.z, v.w);
+          o[i] = w;
+        }
+      }
+    }
   } else if (warp >= 4) {
     const int ew = warp & 3;
     const int eh = (warp - 4) >> 2;
@@ -1150,6 +1168,12 @@ int gemm_num_sms() {
   return n > 0 ? n : 148;
 }
 
+bool gemm_tc_is_pair(bool tf32, int mode, int M, int N, const GemmEpi& e, bool dbg) {
+  return !tf32 && !dbg && e.batch == 1 && e.ksplit <= 1 && M >= 1024 && N % 256 == 0 && e.a_mode != AM_CONV3 &&
+         (kernel_variant(VK_GEMM_PAIR) != 0 || e.a_mode == AM_PATCH16) &&
+         (mode == GM_BIAS_BF16 || mode == GM_BIAS_GELU_BF16 || mode == GM_F32 || mode == GM_F32_FOLD);
+}
+
 cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, int ldw, int M, int N, int K,
                     const GemmEpi& e, cudaStream_t s, bool dbg) {
   if (!g_encode.load() && !dbg) return cudaErrorInitializationError;
@@ -1169,6 +1193,9 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
         e.stats_dim < 1)
       return cudaErrorInvalidValue;
   }
+  if (e.pad_dst && (!gemm_tc_is_pair(tf32, mode, M, N, e, dbg) || !e.pad_bias || !e.pad_rows || e.pad_n < 1 ||
+                    e.pad_frames < 1 || e.pad_cols < 4 || e.pad_cols % 4 != 0))
+    return cudaErrorInvalidValue;
   if (e.ksplit > 1) {
     const int kblocks = (K + (tf32 ? 32 : 64) - 1) / (tf32 ? 32 : 64), kper = (kblocks + e.ksplit - 1) / e.ksplit;
     if (mode != GM_F32 || dbg || e.batch != 1 || e.bias || e.addend || e.a_mode != AM_PLAIN || e.rowmap != RM_IDENT ||
@@ -1178,8 +1205,7 @@ cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, 
   if (e.a_mode == AM_PATCH16 && !(e.batch == 1 && M >= 1024 && N % 256 == 0 && (mode == GM_F32 || mode == GM_F32_FOLD)))
     return cudaErrorInvalidValue;
   if (mode == GM_UPS2 && N != 128) return cudaErrorInvalidValue;
-  if (!tf32 && !dbg && e.batch == 1 && e.ksplit <= 1 && M >= 1024 && N % 256 == 0 && e.a_mode != AM_CONV3 &&
-      (kernel_variant(VK_GEMM_PAIR) != 0 || e.a_mode == AM_PATCH16)) {
+  if (gemm_tc_is_pair(tf32, mode, M, N, e, dbg)) {
     switch (mode) {
       case GM_BIAS_BF16: return launch2<GM_BIAS_BF16>(A, lda, W, ldw, M, N, K, e, s);
       case GM_BIAS_GELU_BF16: return launch2<GM_BIAS_GELU_BF16>(A, lda, W, ldw, M, N, K, e, s);

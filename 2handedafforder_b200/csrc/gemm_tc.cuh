@@ -79,6 +79,14 @@ struct GemmEpi {
   const float* fold_c = nullptr;
   float fold_eps = 0.f;
   int stats_dim = 0;               // columns the producer's sums run over (= K of the consuming GEMM)
+  // Side job for the otherwise idle fourth warp of every CTA of the pair kernel (only there: gemm_tc_is_pair()): write
+  // bf16(pad_bias) into the pad_n window-pad rows (positions pad_rows[], relative to a frame's 4900-row window layout) of
+  // pad_frames frames of pad_dst (pad_cols bf16 per row).  The lin2 launch of block i does this for the qkv buffer of a
+  // windowed block i + 1 (image_encoder.py:179-183: the padded tokens are zero after norm1, so their qkv is the bias).
+  void* pad_dst = nullptr;
+  const float* pad_bias = nullptr;
+  const int* pad_rows = nullptr;
+  int pad_n = 0, pad_frames = 0, pad_cols = 0;
 };
 
 // A: (M, K) row-major with leading dimension lda (elements); W: (N, K) row-major, ldw.
@@ -87,6 +95,9 @@ struct GemmEpi {
 // Returns cudaSuccess or an error; never falls back to another implementation.
 cudaError_t gemm_tc(bool tf32, int mode, const void* A, int lda, const void* W, int ldw, int M, int N, int K,
                     const GemmEpi& epi, cudaStream_t stream, bool debug_simt = false);
+
+// Whether gemm_tc() would run this launch on the CTA-pair kernel (the only one that takes GemmEpi::pad_dst).
+bool gemm_tc_is_pair(bool tf32, int mode, int M, int N, const GemmEpi& epi, bool debug_simt = false);
 
 // 2-D tiled tensor map over a row-major (rows, cols) matrix with leading dimension ld (elements).  elem_bytes 2 or 4,
 // swizzle_bytes in {32, 64, 128} with box_cols * elem_bytes == swizzle_bytes.  Needs gemm_tc_init.

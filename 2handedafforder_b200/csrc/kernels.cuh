@@ -47,7 +47,7 @@ cudaError_t launch_attention_window_tc(const __nv_bfloat16* qkv, int nwin, int h
                                        __nv_bfloat16* out, cudaStream_t s, bool token_out = false);
 
 // Kernel variant switches for same-box A/B measurements (include/b200sam_debug.h); 0 = the shipped default.
-enum VariantKind : int { VK_ATTN_WINDOW = 0, VK_ATTN_GLOBAL = 1, VK_GEMM_PAIR = 2, VK_IMPLICIT_CONV = 3, VK_PREPROCESS = 4, VK_LN_FOLD = 5, VK_PDL = 6, VK_COUNT = 7 };
+enum VariantKind : int { VK_ATTN_WINDOW = 0, VK_ATTN_GLOBAL = 1, VK_GEMM_PAIR = 2, VK_IMPLICIT_CONV = 3, VK_PREPROCESS = 4, VK_LN_FOLD = 5, VK_PDL = 6, VK_PAD_FILL = 7, VK_COUNT = 8 };
 int kernel_variant(int which);
 void set_kernel_variant(int which, int value);
 // device buffer of at least 16 * 16 * 10 uint64 that the tracing kernel variants fill (null: tracing variants refuse)

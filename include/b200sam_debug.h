@@ -23,7 +23,9 @@ int b200sam_debug_read_tokens(b200sam_t* h, float* out, int B, void* stream);
  * kernel (0 shipped, 1 round-1 softmax arithmetic, 2 phase trace), 2 = big-GEMM kernel (0 single CTA, 1 CTA pair = default), 3 = the encoder's two
  * convolutions (0 = A tiles gathered by TMA from the activation = default, 1 = im2col copy + plain GEMM), 4 = preprocess kernel (0 = shared-memory staged
  * second generation = default, 1 = the round-1 kernel), 5 = LayerNorm (0 = folded into the qkv / lin1 GEMMs = default,
- * 1 = stand-alone kernel), 6 = programmatic dependent launch of the encoder kernels (0 = off = default, 1 = on).
+ * 1 = stand-alone kernel), 6 = programmatic dependent launch of the encoder kernels (0 = off = default, 1 = on),
+ * 7 = window-pad rows of the qkv buffer (0 = written by the idle warp of the previous block's lin2 GEMM = default,
+ * 1 = by the fill kernel behind every windowed qkv GEMM).
  * An unknown
  * variant is an error at launch time, never a fallback. */
 int b200sam_debug_set_variant(int which, int value);

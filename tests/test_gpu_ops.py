@@ -351,6 +351,30 @@ def test_layernorm_folded_into_qkv_and_lin1(arch_name, batch):
     del ref
 
 
+def test_pad_rows_written_by_the_previous_lin2_launch_give_identical_embeddings():
+    """The 804 window-pad rows of a windowed block's qkv buffer (zero after norm1, so qkv = bias there;
+    image_encoder.py:179-183) are written by the idle warp of the PREVIOUS block's lin2 GEMM (default) instead of a fill
+    kernel behind every windowed qkv GEMM (debug variant 7 = 1).  Same bytes at the same place before the attention
+    reads them: the embeddings are bit-identical, eager and as a CUDA graph.  Three blocks of width 256 so that block
+    1 is a windowed block behind a lin2 launch on the CTA-pair kernel (the tiny golden shapes have none)."""
+    arch = synth.Arch("tiny64x3", 256, 3, 4, (2,), 3)
+    sam = G.pkg()._build_sam(arch.dim, arch.depth, arch.heads, list(arch.global_idx), max_batch=2, max_prompts=1)
+    missing, unexpected = sam.load_state_dict(synth.make_state_dict(arch, seed=0), strict=True)
+    assert not missing and not unexpected
+    sam = sam.cuda()
+    x = synth.make_frames(12, 2).cuda().to(torch.bfloat16)
+    try:
+        assert G.lib().b200sam_debug_set_variant(7, 1) == 0
+        want = sam.get_visual_embs(x)
+        assert G.lib().b200sam_debug_set_variant(7, 0) == 0
+        got = [sam.get_visual_embs(x) for _ in range(4)]          # eager, capture, two replays
+        torch.cuda.synchronize()
+    finally:
+        G.lib().b200sam_debug_set_variant(7, 0)
+    assert all(torch.equal(g, want) for g in got)
+    assert torch.isfinite(want.float()).all()
+
+
 def test_programmatic_dependent_launch_gives_identical_embeddings():
     """Debug variant 6 = 1 launches the GEMMs, both attention kernels and the pad-row fill with the programmatic
     dependent launch attribute (their barrier / TMEM set-up overlaps the previous kernel's tail; griddepcontrol.wait
