@@ -42,11 +42,11 @@ for d in L:
     by = d.get("dram__bytes_read.sum", 0.0) + d.get("dram__bytes_write.sum", 0.0)
     key = None
     was, prev = prev, n
-    if re.match(r"gemm_tc2_kernel<(\(int\))?0>", n):
+    if re.match(r"gemm_tc2_kernel<(\(int\))?0[,>]", n):
         key = "gemm_qkv"
-    elif re.match(r"gemm_tc2_kernel<(\(int\))?1>", n):
+    elif re.match(r"gemm_tc2_kernel<(\(int\))?1[,>]", n):
         key = "gemm_lin1"
-    elif re.match(r"gemm_tc2_kernel<(\(int\))?[27]>", n):      # 2 = GM_F32, 7 = GM_F32_FOLD (same role with the folded LayerNorm)
+    elif re.match(r"gemm_tc2_kernel<(\(int\))?[27][,>]", n):      # 2 = GM_F32, 7 = GM_F32_FOLD (same role with the folded LayerNorm)
         # fp32-residual epilogue: proj directly follows the block's attention kernel, lin2 follows lin1 (+GELU); the
         # remaining one per encode is the patch embedding
         key = "gemm_proj" if was.startswith("attn_") else "gemm_lin2" if was.startswith("gemm_tc2_kernel") else "gemm_patch"
