@@ -142,3 +142,44 @@ def test_training_module_has_no_cpu_path():
     t = torch.empty(2, 3, 4, 5).permute(0, 2, 3, 1)
     assert T._empty_like_layout(t).stride() == t.stride()
     assert T._empty_like_layout(torch.empty(4, 6)[:, ::2]).is_contiguous()
+
+
+def test_launch_summariser_classifies_the_pair_gemm_instantiations(tmp_path):
+    """scripts/summarize_launches.py turns the ncu launch list into profiles/ncu_traffic.json (bench.py's
+    roofline.traffic).  The pair GEMM's demangled names carry two template arguments since the epilogue got a
+    compile-time leading dimension: proj follows an attention kernel, lin2 follows lin1, the remaining launch of the
+    residual-stream mode is the patch embedding."""
+    import json
+    import subprocess
+    import sys
+
+    def rows(i, name, t_ns, rd, wr):
+        base = [str(i), "1", "python", "host", name, "1", "7", "(384, 1, 1)", "(148, 1, 1)", "0", "10.0", "sec"]
+        return [base + ["dram__bytes_read.sum", "byte", str(rd)], base + ["dram__bytes_write.sum", "byte", str(wr)],
+                base + ["gpu__time_duration.sum", "ns", str(t_ns)]]
+
+    pre = "void bsam::<unnamed>::"
+    tail = "(CUtensorMap_st, CUtensorMap_st, int, int, int, bsam::GemmEpi)"
+    seq = [("gemm_tc2_kernel<7, 1280>", 50000, 10, 20),                                                   # patch
+           ("gemm_tc2_kernel<0, 0>", 200000, 100, 200),                                                     # qkv
+           ("attn_window_tc_kernel_v1<80, 0>", 100000, 300, 60),
+           ("gemm_tc2_kernel<7, 1280>", 110000, 250, 200),                                                  # proj
+           ("gemm_tc2_kernel<1, 0>", 300000, 100, 290),                                                     # lin1
+           ("gemm_tc2_kernel<7, 1280>", 290000, 600, 270)]                                                  # lin2
+    src = tmp_path / "launches.csv"
+    with open(src, "w") as fh:
+        fh.write("==PROF== noise\n")
+        fh.write('"ID","Process ID","Process Name","Host Name","Kernel Name","Context","Stream","Block Size","Grid Size",'
+                 '"Device","CC","Section Name","Metric Name","Metric Unit","Metric Value"\n')
+        for i, (n, t, rd, wr) in enumerate(seq):
+            for r in rows(i, pre + n + tail, t, rd, wr):
+                fh.write(",".join('"%s"' % c for c in r) + "\n")
+    out = tmp_path / "out"
+    out.mkdir()
+    subprocess.run([sys.executable, os.path.join(G.ROOT, "scripts", "summarize_launches.py"), str(src), str(out), "t"],
+                   check=True, capture_output=True)
+    traffic = json.load(open(out / "ncu_traffic.json"))
+    assert traffic["gemm_qkv"] == 300 and traffic["gemm_lin1"] == 390
+    assert traffic["gemm_proj"] == 450 and traffic["gemm_lin2"] == 870 and traffic["gemm_patch"] == 30
+    assert traffic["attn_window"] == 360
+    assert os.path.exists(out / "t_launch_summary.csv")
